@@ -1,0 +1,185 @@
+"""Scenario compiler: slice_req dictionaries -> dense scenario-bank rows.
+
+The reference keeps a scenario as a dict-of-dicts `slice_req` plus three association
+matrices (`associations/mult_slice.py:58-347, 350-442`).  The device path wants plain
+structs: one `irs_scenario` row (include/irs_b200.h) per network scenario, shared by every
+env that is currently playing it.  This module is host-side only (NumPy).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+MAX_UES = 25  # env_config/mult_slice.yml:14
+MAX_SLICES = 5  # env_config/mult_slice.yml:13
+NUM_RBS = 135  # env_config/mult_slice.yml:5
+POISSON_K = 256
+
+F_ACTIVE, F_REQ, F_THR, F_REL, F_LAT = 1, 2, 4, 8, 16
+
+# Restated from associations/mult_slice.py:58-347.  Columns:
+# name, priority, reliability %, latency ms, throughput Mbps (None = intent not declared),
+# buffer_size pkts, buffer_latency ms, message_size bits, traffic Mbps, min/max UEs.
+SLICE_TYPES = [
+    ("control_case_2", 1, 99.999999, 50, None, 10240, 100, 8192, 5, 4, 5),
+    ("monitoring_case_1", 0, None, None, 10, 10240, 100, 8192, 10, 4, 5),
+    ("robotic_surgery_case_1", 1, 99.9999, 20, 30, 1024000, 40, 16000, 30, 4, 5),
+    ("robotic_diagnosis", 0, 99.999, 20, 15, 1024000, 40, 640, 15, 4, 5),
+    ("medical_monitoring", 0, 99.9999, 100, 10, 10240, 200, 8000, 10, 4, 5),
+    ("uav_app_case_1", 1, None, 200, 100, 1024000, 400, 65536, 100, 2, 4),
+    ("uav_control_non_vlos", 1, 99.99, 140, 20, 10240, 300, 65536, 20, 4, 5),
+    ("vr_gaming", 0, 99.99, 10, 100, 1024000, 20, 65536, 100, 2, 4),
+    ("cloud_gaming", 0, None, 80, 50, 10240, 160, 65536, 50, 2, 5),
+    ("video_streaming_4k", 0, None, None, 30, 10240, 100, 65536, 30, 2, 5),
+]
+SLICE_TYPE_NAMES = [t[0] for t in SLICE_TYPES]
+
+SLICE_DTYPE = np.dtype(
+    [
+        ("priority", "<f8"), ("traffic", "<f8"), ("buffer_size", "<f8"), ("buffer_latency", "<f8"),
+        ("message_size", "<f8"), ("thr_value", "<f8"), ("rel_value", "<f8"), ("lat_value", "<f8"),
+        ("flags", "<i4"), ("n_ues", "<i4"), ("lam_idx", "<i4"), ("pad", "<i4"),
+    ]
+)
+SCENARIO_DTYPE = np.dtype([("sl", SLICE_DTYPE, (MAX_SLICES,)), ("ue_slice", "i1", (32,))])
+assert SLICE_DTYPE.itemsize == 80 and SCENARIO_DTYPE.itemsize == 432
+
+
+def slice_req_from_type(type_id: int) -> dict:
+    """The reference-shaped slice_req entry of one slice type (operators as strings)."""
+    name, prio, rel, lat, thr, bsz, blat, msg, traffic, umin, umax = SLICE_TYPES[type_id]
+    params = {}
+    if rel is not None:
+        params[f"par{len(params)+1}"] = {"name": "reliability", "value": rel, "unit": "rate", "operator": "at_least"}
+    if lat is not None:
+        params[f"par{len(params)+1}"] = {"name": "latency", "value": lat, "unit": "ms", "operator": "at_most"}
+    if thr is not None:
+        params[f"par{len(params)+1}"] = {"name": "throughput", "value": thr, "unit": "Mbps", "operator": "at_least"}
+    return {
+        "name": name, "priority": prio, "parameters": params,
+        "ues": {"buffer_size": bsz, "buffer_latency": blat, "message_size": msg, "traffic": traffic,
+                "min_number_ues": umin, "max_number_ues": umax},
+    }
+
+
+def _operator_name(op) -> str:
+    if isinstance(op, str):
+        return op
+    return {"greater_equal": "at_least", "less_equal": "at_most"}.get(getattr(op, "__name__", ""), "unsupported")
+
+
+class ScenarioBank:
+    """Dense table of scenarios + the Poisson CDF tables their traffic classes need."""
+
+    def __init__(self):
+        self.rows = []
+        self.lambdas: list[float] = []
+
+    def _lam_idx(self, lam: float) -> int:
+        lam = float(lam)
+        if lam not in self.lambdas:
+            self.lambdas.append(lam)
+        return self.lambdas.index(lam)
+
+    def add(self, slice_req: dict, slice_ue_assoc: np.ndarray, basestation_slice_assoc=None) -> int:
+        """slice_req: {"slice_0": {...} or {}, ...} as returned by Association.step
+        (`sixg_radio_mgmt/sixg_radio_mgmt/association.py:60-109`)."""
+        row = np.zeros((), SCENARIO_DTYPE)
+        row["ue_slice"][:] = -1
+        sua = np.asarray(slice_ue_assoc)
+        assert sua.shape == (MAX_SLICES, MAX_UES)
+        if (sua.sum(axis=0) > 1).any():
+            raise ValueError("a UE is associated with more than one slice")
+        bsa = None if basestation_slice_assoc is None else np.asarray(basestation_slice_assoc).reshape(-1)
+        for s in range(MAX_SLICES):
+            req = slice_req.get(f"slice_{s}", {})
+            sl = row["sl"][s]
+            ues = np.flatnonzero(sua[s])
+            if len(ues) > 5:
+                raise ValueError("at most 5 UEs per slice (agents/ib_sched.py:50)")
+            row["ue_slice"][ues] = s
+            sl["n_ues"] = len(ues)
+            flags = 0
+            active = (req != {}) if bsa is None else bool(bsa[s])
+            if active:
+                flags |= F_ACTIVE
+            if req != {}:
+                flags |= F_REQ
+                ue = req["ues"]
+                sl["priority"] = req["priority"]
+                sl["traffic"] = ue["traffic"]
+                sl["buffer_size"] = ue["buffer_size"]
+                sl["buffer_latency"] = ue["buffer_latency"]
+                sl["message_size"] = ue["message_size"]
+                sl["lam_idx"] = self._lam_idx(ue["traffic"])
+                for par in req["parameters"].values():
+                    op = _operator_name(par["operator"])
+                    want = {"throughput": "at_least", "reliability": "at_least", "latency": "at_most"}[par["name"]]
+                    if op != want:
+                        raise ValueError(f"unsupported intent operator {op} for {par['name']}")
+                    if par["name"] == "throughput":
+                        flags |= F_THR
+                        sl["thr_value"] = par["value"]
+                    elif par["name"] == "reliability":
+                        flags |= F_REL
+                        sl["rel_value"] = par["value"]
+                    else:
+                        flags |= F_LAT
+                        sl["lat_value"] = par["value"]
+            elif len(ues):
+                # UEs in a slice without requirements keep the env defaults (comm_env.py:184-198)
+                sl["buffer_size"], sl["buffer_latency"], sl["message_size"] = 10240, 100, 65536
+            sl["flags"] = flags
+        self.rows.append(row)
+        return len(self.rows) - 1
+
+    def add_typed(self, slice_type, ue_slice) -> int:
+        """slice_type[5]: type id per slot (-1 unused); ue_slice[25]: slot of each UE (-1 none)."""
+        req = {f"slice_{s}": (slice_req_from_type(int(t)) if t >= 0 else {}) for s, t in enumerate(slice_type)}
+        sua = np.zeros((MAX_SLICES, MAX_UES))
+        for u, s in enumerate(ue_slice):
+            if s >= 0:
+                sua[int(s), u] = 1
+        return self.add(req, sua)
+
+    def max_depth(self) -> int:
+        arr = self.array()
+        return int(arr["sl"]["buffer_latency"].max()) + 1
+
+    def array(self) -> np.ndarray:
+        return np.stack(self.rows) if self.rows else np.zeros((0,), SCENARIO_DTYPE)
+
+    def poisson_cdf(self) -> np.ndarray:
+        """[n_lambda, POISSON_K] float64; sample = #{j : cdf[j] <= u}.  Built once on the host
+        and handed to the device (and, in tests, to the oracle) as data."""
+        out = np.ones((max(1, len(self.lambdas)), POISSON_K))
+        for i, lam in enumerate(self.lambdas):
+            if lam + 12 * np.sqrt(lam) + 10 > POISSON_K:
+                raise ValueError(f"traffic lambda {lam} too large for the {POISSON_K}-entry table")
+            p = np.exp(-lam)
+            c = 0.0
+            for j in range(POISSON_K):
+                c += p
+                out[i, j] = min(c, 1.0)
+                p = p * lam / (j + 1)
+        return out
+
+
+def generate_scenarios(n: int, seed: int = 10) -> tuple[np.ndarray, np.ndarray]:
+    """Native generator with the distribution of associations/mult_slice.py:359-416
+    (3..5 slices, slots and types without replacement, UEs/slice uniform in [min,max],
+    random UE ids).  Not stream-compatible with gen_assoc_mult_slice.py."""
+    rng = np.random.default_rng(seed)
+    st = -np.ones((n, MAX_SLICES), np.int8)
+    us = -np.ones((n, MAX_UES), np.int8)
+    for i in range(n):
+        k = int(rng.integers(3, MAX_SLICES, endpoint=True))
+        slots = rng.choice(MAX_SLICES, k, replace=False)
+        types = rng.choice(len(SLICE_TYPES), k, replace=False)
+        counts = [int(rng.integers(SLICE_TYPES[t][9], SLICE_TYPES[t][10], endpoint=True)) for t in types]
+        ues = rng.choice(MAX_UES, int(np.sum(counts)), replace=False)
+        off = 0
+        for slot, t, c in zip(slots, types, counts):
+            st[i, slot] = t
+            us[i, ues[off:off + c]] = slot
+            off += c
+    return st, us

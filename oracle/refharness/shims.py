@@ -1,0 +1,142 @@
+"""Import shims that let the UNMODIFIED reference run in this container.
+
+TEST INFRASTRUCTURE ONLY.  Used by `oracle/refharness/gen_golden.py` (which runs
+only in the build container where `/root/reference` is mounted) to record golden
+traces.  Nothing in the product package imports this file.
+
+The reference imports `gymnasium`, `pettingzoo`, `ray`, `matplotlib`, none of which
+are installed here; none of them takes part in the arithmetic of the hot path
+(SURVEY.md 8c).  The shims below only provide the names the reference touches at
+import / construction time:
+
+* `gymnasium.Env.reset(seed)` seeds `np_random = Generator(PCG64(SeedSequence(seed)))`
+  exactly like gymnasium 0.28.1 `seeding.np_random` (used at
+  `sixg_radio_mgmt/sixg_radio_mgmt/comm_env.py:413,631`).
+* `gymnasium.spaces.{Space,Box,Dict,Discrete}` are inert containers
+  (`agents/ib_sched.py:394-470`).
+* `ray.rllib.env.multi_agent_env.MultiAgentEnv` is an empty base
+  (`sixg_radio_mgmt/sixg_radio_mgmt/marl_comm_env.py:7,29`).
+
+The reference's `agents/`, `channels/`, ... directories have no `__init__.py` and
+this image ships an unrelated `site-packages/agents`; they are pre-registered as
+path-only packages.
+"""
+import sys
+import types
+
+import numpy as np
+
+REF = "/root/reference"
+
+
+def _mod(name, **attrs):
+    m = types.ModuleType(name)
+    m.__dict__.update(attrs)
+    sys.modules[name] = m
+    return m
+
+
+class _Space:
+    def __init__(self, *a, **k):
+        self.args, self.kwargs = a, k
+        self.shape = k.get("shape")
+        self.dtype = k.get("dtype")
+
+
+class _Box(_Space):
+    def __init__(self, low=None, high=None, shape=None, dtype=None, **k):
+        super().__init__(low=low, high=high, shape=shape, dtype=dtype)
+        self.low, self.high = low, high
+
+
+class _Dict(_Space):
+    def __init__(self, spaces=None, **k):
+        super().__init__()
+        self.spaces = dict(spaces or {})
+
+    def __getitem__(self, k):
+        return self.spaces[k]
+
+
+class _Discrete(_Space):
+    def __init__(self, n, **k):
+        super().__init__()
+        self.n = n
+
+
+class _Env:
+    """gymnasium.Env stand-in: only the seeding contract matters."""
+
+    _np_random = None
+
+    @property
+    def np_random(self):
+        if self._np_random is None:
+            self._np_random = np.random.Generator(np.random.PCG64(np.random.SeedSequence()))
+        return self._np_random
+
+    @np_random.setter
+    def np_random(self, v):
+        self._np_random = v
+
+    def reset(self, *, seed=None, options=None):
+        if seed is not None:
+            self._np_random = np.random.Generator(np.random.PCG64(np.random.SeedSequence(seed)))
+
+
+def install():
+    if "gymnasium" in sys.modules and getattr(sys.modules["gymnasium"], "_irs_shim", False):
+        return
+    spaces = _mod("gymnasium.spaces", Space=_Space, Box=_Box, Dict=_Dict, Discrete=_Discrete)
+    g = _mod("gymnasium", Env=_Env, spaces=spaces, _irs_shim=True)
+    g.Space = _Space
+
+    class _AEC:
+        pass
+
+    pz_utils = _mod("pettingzoo.utils", agent_selector=object, wrappers=types.SimpleNamespace())
+    _mod("pettingzoo", AECEnv=_AEC, utils=pz_utils)
+
+    class _MAE:
+        def __init__(self, *a, **k):
+            pass
+
+    _mod("ray")
+    _mod("ray.rllib")
+    _mod("ray.rllib.env")
+    _mod("ray.rllib.env.multi_agent_env", MultiAgentEnv=_MAE)
+
+    class _Any:
+        def __getattr__(self, k):
+            return _Any()
+
+        def __call__(self, *a, **k):
+            return _Any()
+
+    for name in ("matplotlib", "matplotlib.figure", "matplotlib.pyplot", "matplotlib.pylab"):
+        m = _mod(name)
+        m.__getattr__ = lambda k: _Any()  # type: ignore
+    for pkg in ("agents", "channels", "traffics", "associations", "mobilities"):
+        m = types.ModuleType(pkg)
+        m.__path__ = [f"{REF}/{pkg}"]
+        sys.modules[pkg] = m
+    for p in (REF, f"{REF}/sixg_radio_mgmt"):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+
+
+_orig_argsort = np.argsort
+
+
+def pin_stable_argsort():
+    """SURVEY.md section 7 hard part 1: the reference's np.argsort tie order is build
+    dependent (AVX-512 quicksort); the oracle pins kind='stable'."""
+
+    def stable(a, axis=-1, kind=None, order=None, **kw):
+        return _orig_argsort(a, axis=axis, kind="stable", order=order, **kw)
+
+    np.argsort = stable
+
+
+def unpin_argsort():
+    np.argsort = _orig_argsort
