@@ -1,0 +1,203 @@
+/*
+ * irs_b200.h - C ABI of the B200-native batched `CommunicationEnv.step` path.
+ *
+ * The reference (lasseufpa/intent_radio_sched_multi_slice) is pure Python: there is no FFI
+ * today.  This header is the boundary a maintainer binds (ctypes) in
+ * place of the Python call chain
+ *
+ *   CommunicationEnv.step      sixg_radio_mgmt/sixg_radio_mgmt/comm_env.py:271-373
+ *   CommunicationEnv.reset     sixg_radio_mgmt/sixg_radio_mgmt/comm_env.py:375-482
+ *   UEs.step / Buffer          sixg_radio_mgmt/sixg_radio_mgmt/ues.py:149-243, buffer.py:53-130
+ *   IBSched.action_format      agents/ib_sched.py:223-349   (+ agents/common.py:442-701)
+ *   IBSched.obs_space_format   agents/ib_sched.py:63-204    (+ agents/common.py:9-378)
+ *   IBSched.calculate_reward   agents/ib_sched.py:206-221   (+ agents/common.py:381-439)
+ *   MARR.step / MAPF.step      agents/marr.py:40-47, agents/mapf.py:41-111
+ *   MultSliceTraffic.step      traffics/mult_slice.py:15-34
+ *   MimicQuadriga/FixedSE.step channels/mimic_quadriga.py:30-58, channels/fixed_se.py:28-41
+ *   Metrics.step               sixg_radio_mgmt/sixg_radio_mgmt/metrics.py:62-100 (as accumulators)
+ *
+ * Conventions: plain pointers and sizes, no C++ or torch types; every function returns an
+ * int status (0 = OK, <0 = irs_status) and never throws; all device memory is owned by the
+ * caller (one state blob whose size irs_state_layout reports); every device call is
+ * asynchronous on the given CUDA stream (a cudaStream_t passed as void*), allocates nothing
+ * and is CUDA-graph capturable.  A handle is not thread-safe (one handle per process/device,
+ * like one reference env per Ray worker).
+ */
+#ifndef IRS_B200_H
+#define IRS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IRS_MAX_UES 25        /* env_config/mult_slice.yml:14 max_number_ues */
+#define IRS_MAX_SLICES 5      /* env_config/mult_slice.yml:13 */
+#define IRS_NUM_RBS 135       /* env_config/mult_slice.yml:5 */
+#define IRS_WINDOW 10         /* agents/ib_sched.py:49 max_obs_memory */
+#define IRS_MAX_UES_SLICE 5   /* agents/ib_sched.py:50 */
+#define IRS_RBS_PER_RBG 5     /* agents/ib_sched.py:56 */
+#define IRS_OBS0 50           /* agents/ib_sched.py:413-470: player_0 observations */
+#define IRS_OBSI 19           /* player_{s+1} observations */
+#define IRS_NUM_METRICS 16
+#define IRS_POISSON_K 256
+
+typedef enum {
+    IRS_OK = 0,
+    IRS_ERR_ARG = -1,        /* bad argument / config */
+    IRS_ERR_UNBOUND = -2,    /* irs_bind / irs_load_scenarios not called yet */
+    IRS_ERR_CUDA = -3,       /* a CUDA runtime call failed (message in irs_last_error) */
+    IRS_ERR_ENV = -4         /* irs_check_errors: a device-side invariant was violated */
+} irs_status;
+
+/* slice flags */
+enum { IRS_F_ACTIVE = 1, IRS_F_REQ = 2, IRS_F_THR = 4, IRS_F_REL = 8, IRS_F_LAT = 16 };
+
+/* One slice slot of a scenario: the dense form of one `slice_req["slice_s"]` entry
+ * (associations/mult_slice.py:58-347) plus its UE count.  80 bytes. */
+typedef struct {
+    double priority, traffic, buffer_size, buffer_latency, message_size;
+    double thr_value, rel_value, lat_value;
+    int32_t flags, n_ues, lam_idx, pad;
+} irs_slice;
+
+/* One network scenario (what one ep_N.npz of gen_assoc_mult_slice.py:229-237 holds).  432 bytes. */
+typedef struct {
+    irs_slice sl[IRS_MAX_SLICES];
+    int8_t ue_slice[32]; /* slice slot of each UE, -1 = not associated */
+} irs_scenario;
+
+typedef struct {
+    int32_t num_envs;
+    int32_t depth_cap;       /* max buffer depth (buffer_latency + 1) of any scenario row */
+    int32_t channel_mode;    /* 0 SE injected per call, 1 fixed_se (2.0), 2 native mimic_quadriga */
+    int32_t traffic_mode;    /* 0 traffic (bits) injected per call, 1 native Poisson */
+    int32_t sort_slices;     /* IBSched.enable_sort_slices (ib_sched.py:57); MARR/MAPF: 0 */
+    int32_t fixed_intra;     /* -1 per-slice action (player_1..5), 0 rr, 1 pf, 2 mt */
+    int32_t policy;          /* 0 actions supplied, 1 MARR, 2 MAPF, 3 random (device RNG) */
+    int32_t assoc_mode;      /* 0 scenario = episode % scen_mod (mult_slice.py:444-452),
+                                1 scenario = episode / scen_div (mult_slice_seq.py:38-46) */
+    int32_t scen_mod, scen_div, n_scen;
+    int32_t max_steps, max_episodes, initial_episode;
+    int32_t auto_reset;      /* step() resets a finished env in the same call (VecEnv style) */
+    int32_t env_id_base;     /* global id of env 0 of this shard: RNG key, so results do not
+                                depend on how envs are sharded over GPUs */
+    uint64_t seed;
+    double bandwidth;        /* Hz, env_config/mult_slice.yml:3 */
+} irs_config;
+
+/* Byte offsets of every array inside the caller-owned device state blob.  The caller may
+ * view them (e.g. as torch tensors) but must treat all but `out_*` as read-only. */
+typedef struct {
+    size_t total_bytes;
+    int32_t row_stride;      /* ints per buffer row: depth_cap rounded up to 4 */
+    int32_t reserved;
+    size_t buf;              /* i32 [E][25][row_stride]  age histograms (buffer.py:47) */
+    size_t occ, lat, sebar;  /* f64 [E][25]  newest window frame (win[0]) */
+    size_t tot;              /* i32 [E][25]  packets in buffer */
+    size_t sum_sent, sum_drop;   /* i32 [E][25] window sums (<=10 frames) */
+    size_t last_sent, last_drop, last_inc; /* i32 [E][25] newest frame */
+    size_t ring_sent, ring_drop; /* i32 [E][10][25] */
+    size_t thr;              /* f64 [E][25] pkt_throughputs of the newest frame */
+    size_t occ1z;            /* u8  [E][32] isclose(win[1].occ, 0) */
+    size_t rb_start, rb_count;   /* i16 [E][32] contiguous RB run of each UE */
+    size_t step, episode, scen, win_len, win_head, err; /* i32 [E] */
+    size_t sorted;           /* i8  [E][8] IBSched.sorted_slices */
+    size_t acc;              /* f64 [E][16] episode-metric accumulators */
+    size_t bank;             /* irs_scenario [n_scen] */
+    size_t cdf;              /* f64 [n_lambda][256] Poisson CDF tables */
+    size_t in_a0;            /* f64 [E][5]  staging for irs_step_host */
+    size_t in_intra;         /* i32 [E][5] */
+    /* the env surface written by every step/reset */
+    size_t out_obs0;         /* f64 [E][50] */
+    size_t out_obsi;         /* f64 [E][5][19] */
+    size_t out_mask0;        /* i8  [E][5] */
+    size_t out_maski;        /* i8  [E][5][5] */
+    size_t out_reward;       /* f64 [E][6] */
+    size_t out_done;         /* u8  [E] */
+    size_t metrics_total;    /* f64 [16] result of irs_episode_metrics */
+} irs_layout;
+
+typedef struct {
+    const double* a0;        /* [E][5] inter-slice scores in [-1,1] (player_0) */
+    const int32_t* intra;    /* [E][5] intra-slice algorithm per slice (player_1..5), may be NULL */
+} irs_actions;
+
+typedef struct {
+    const double* se;        /* [E][25][135] spectral efficiencies (channel_mode 0) */
+    const double* traffic;   /* [E][25] offered bits (traffic_mode 0) */
+} irs_inject;
+
+/* Optional extra outputs (raw per-UE step metrics of ues.py:236-243 and the inputs actually
+ * used).  Any pointer may be NULL.  Device pointers for irs_step/irs_reset. */
+typedef struct {
+    double* pkt_incoming;    /* [E][25] */
+    double* pkt_throughputs; /* [E][25] */
+    int32_t* sent;           /* [E][25] pkt_effective_thr */
+    int32_t* dropped;        /* [E][25] */
+    double* occ;             /* [E][25] buffer_occupancies */
+    double* lat;             /* [E][25] buffer_latencies */
+    int16_t* rb_start;       /* [E][25] */
+    int16_t* rb_count;       /* [E][25] */
+    int8_t* sorted_slices;   /* [E][5] */
+    double* a0_used;         /* [E][5] */
+    int32_t* intra_used;     /* [E][5] */
+    double* se_used;         /* [E][25][135] */
+    double* traffic_used;    /* [E][25] */
+} irs_raw_outputs;
+
+/* Host-side surface for irs_step_host / irs_reset_host (pinned memory recommended). */
+typedef struct {
+    double* obs0;            /* [E][50] */
+    double* obsi;            /* [E][5][19] */
+    int8_t* mask0;           /* [E][5] */
+    int8_t* maski;           /* [E][5][5] */
+    double* reward;          /* [E][6] */
+    uint8_t* done;           /* [E] */
+} irs_host_surface;
+
+typedef struct irs_env irs_env;
+
+/* Replaces CommunicationEnv.__init__ (comm_env.py:79-269) for a batch of envs. */
+int irs_create(const irs_config* cfg, int32_t n_lambda, irs_env** out);
+int irs_destroy(irs_env* env);
+/* Size and layout of the state blob the caller must allocate on the device (256-B aligned). */
+int irs_state_layout(const irs_env* env, irs_layout* out);
+/* Hand the blob to the handle and zero-initialise it (comm_env.py:616-682 create_scenario). */
+int irs_bind(irs_env* env, void* state_dev, size_t bytes, void* stream);
+/* Upload the scenario bank and Poisson tables (host pointers). Replaces
+ * MultSliceAssociation.load_episode_data (associations/mult_slice.py:490-508). */
+int irs_load_scenarios(irs_env* env, const irs_scenario* bank_host, int32_t n_scen,
+                       const double* poisson_cdf_host, int32_t n_lambda, void* stream);
+/* CommunicationEnv.reset (comm_env.py:375-482).  mask_dev: u8[E] or NULL (= all);
+ * initial_episode: options["initial_episode"] (-1 = keep counting);
+ * initial_episode_dev: optional i32[E] per-env override (NULL = use the scalar). */
+int irs_reset(irs_env* env, const uint8_t* mask_dev, int32_t initial_episode,
+              const int32_t* initial_episode_dev, const irs_inject* inject,
+              const irs_raw_outputs* raw, void* stream);
+/* CommunicationEnv.step (comm_env.py:271-373) for every env of the batch. */
+int irs_step(irs_env* env, const irs_actions* actions_dev, const irs_inject* inject_dev,
+             const irs_raw_outputs* raw_dev, void* stream);
+/* n steps back to back with the on-device policy (cfg.policy != 0) and native generators. */
+int irs_run(irs_env* env, int32_t n_steps, void* stream);
+/* Same as irs_step but actions come from host memory and the env surface is copied back to
+ * host memory; returns after the stream has drained (the call a single-process user makes). */
+int irs_step_host(irs_env* env, const irs_actions* actions_host, const irs_host_surface* out_host,
+                  void* stream);
+int irs_reset_host(irs_env* env, int32_t initial_episode, const irs_host_surface* out_host, void* stream);
+/* Sum the per-env accumulators in env order into layout.metrics_total (f64[16]) and, when
+ * host_out != NULL, copy them to the host (synchronises).  Replaces Metrics.save
+ * (metrics.py:73-100) as the source of episode statistics. */
+int irs_episode_metrics(irs_env* env, double* host_out, void* stream);
+/* debug=True of the reference (comm_env.py:313-319): synchronises, returns IRS_ERR_ENV and the
+ * index of the first env with a non-zero error word. */
+int irs_check_errors(irs_env* env, int32_t* first_env, int32_t* code, void* stream);
+const char* irs_last_error(const irs_env* env);
+int irs_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IRS_B200_H */

@@ -1,0 +1,224 @@
+// irs_common.cuh - shared device-side definitions of the batched env-step kernels.
+//
+// Everything on this path that feeds a floor(), a comparison or a tie-break is IEEE binary64
+// evaluated in the reference's (NumPy's) order; the translation unit is compiled with
+// -fmad=false so that no multiply-add is contracted (NumPy rounds twice).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/irs_b200.h"
+
+#define U IRS_MAX_UES
+#define S IRS_MAX_SLICES
+#define R IRS_NUM_RBS
+#define W IRS_WINDOW
+#define NS IRS_MAX_UES_SLICE
+#define FULL 0xffffffffu
+#define UE_LANES 0x01ffffffu /* lanes 0..24 */
+
+enum { ERR_INTRA_ACTION = 1, ERR_EPISODE_RANGE = 2, ERR_RB_SUM = 4 };
+
+// Pointers into the caller-owned state blob (see irs_layout).
+struct DevState {
+    int32_t* buf;
+    double *occ, *lat, *sebar, *thr;
+    int32_t *tot, *sum_sent, *sum_drop, *last_sent, *last_drop, *last_inc, *ring_sent, *ring_drop;
+    uint8_t* occ1z;
+    int16_t *rb_start, *rb_count;
+    int32_t *step, *episode, *scen, *win_len, *win_head, *err;
+    int8_t* sorted;
+    double* acc;
+    const irs_scenario* bank;
+    const double* cdf;
+    double* in_a0;
+    int32_t* in_intra;
+    double *out_obs0, *out_obsi, *out_reward;
+    int8_t *out_mask0, *out_maski;
+    uint8_t* out_done;
+    double* metrics_total;
+    int32_t row_stride;
+};
+
+struct StepArgs {
+    DevState st;
+    irs_config cfg;
+    const double* a0;      // actions (device) or NULL
+    const int32_t* intra;  // or NULL
+    const double* se;      // injected SE or NULL
+    const double* traffic; // injected traffic or NULL
+    irs_raw_outputs raw;   // optional extra outputs (all may be NULL)
+    const uint8_t* reset_mask;
+    const int32_t* initial_episode_dev;
+    int32_t initial_episode;
+};
+
+__device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
+__device__ __forceinline__ bool isclose0(double x) { return fabs(x) <= 1e-8; } // np.isclose(x, 0)
+
+// ---- ordered reductions over a group of lanes --------------------------------------------
+// `mask` is the set of lanes that belong to the calling lane's group (0 for idle lanes); all 32
+// lanes must call.  Members are visited in ascending lane order, which is the ascending UE /
+// slice index order NumPy iterates in.  For n < 8 np.add.reduce is a serial sum starting
+// from 0. (numpy/_core/src/umath/loops_utils.h.src, DOUBLE_pairwise_sum), then added to the
+// reduction identity: 0. + res.
+__device__ __forceinline__ double group_sum_ordered(double x, uint32_t mask)
+{
+    double res = 0.;
+    uint32_t m = mask;
+    const int lane = lane_id();
+#pragma unroll
+    for (int k = 0; k < NS; ++k) {
+        const bool valid = m != 0;
+        const int src = valid ? (__ffs(m) - 1) : lane;
+        m &= m - 1;
+        const double v = __shfl_sync(FULL, x, src);
+        if (valid) res += v;
+    }
+    return 0. + res;
+}
+__device__ __forceinline__ int group_sum_int(int x, uint32_t mask)
+{
+    int res = 0;
+    uint32_t m = mask;
+    const int lane = lane_id();
+#pragma unroll
+    for (int k = 0; k < NS; ++k) {
+        const bool valid = m != 0;
+        const int src = valid ? (__ffs(m) - 1) : lane;
+        m &= m - 1;
+        const int v = __shfl_sync(FULL, x, src);
+        if (valid) res += v;
+    }
+    return res;
+}
+__device__ __forceinline__ double group_max(double x, uint32_t mask)
+{
+    double res = x;
+    uint32_t m = mask;
+    const int lane = lane_id();
+#pragma unroll
+    for (int k = 0; k < NS; ++k) {
+        const bool valid = m != 0;
+        const int src = valid ? (__ffs(m) - 1) : lane;
+        m &= m - 1;
+        const double v = __shfl_sync(FULL, x, src);
+        if (valid && v > res) res = v;
+    }
+    return res;
+}
+
+// agents/common.py:481-505 round_int_equal_sum over the members of `mask` (one value per
+// lane).  np.argsort pinned to kind="stable" (SURVEY 7.1): the +1s go to entries in
+// descending value order, ties -> higher index first, cyclically.  Returns this lane's
+// integer share (0 for non-members and for x == 0).
+__device__ __forceinline__ int group_round_int_equal_sum(double x, uint32_t mask, int target)
+{
+    const int lane = lane_id();
+    const bool member = (mask >> lane) & 1u;
+    const bool nz = member && x != 0;
+    // the set of nonzero members of my group
+    uint32_t nzmask = 0;
+    {
+        uint32_t m = mask;
+#pragma unroll
+        for (int k = 0; k < NS; ++k) {
+            const bool valid = m != 0;
+            const int src = valid ? (__ffs(m) - 1) : lane;
+            m &= m - 1;
+            const int f = __shfl_sync(FULL, (int)nz, src);
+            if (valid && f) nzmask |= 1u << src;
+        }
+    }
+    const double sum = group_sum_ordered(x, nzmask);
+    const int cnt = __popc(nzmask);
+    int p = 0;
+    if (nz) p = (int)floor(((double)target * x) / sum);
+    const int tot = group_sum_int(p, nzmask);
+    const int adj = target - tot;
+    // rank in descending order, ties -> higher index first
+    int rank = 0;
+    {
+        uint32_t m = nzmask;
+#pragma unroll
+        for (int k = 0; k < NS; ++k) {
+            const bool valid = m != 0;
+            const int src = valid ? (__ffs(m) - 1) : lane;
+            m &= m - 1;
+            const double v = __shfl_sync(FULL, x, src);
+            if (valid && (v > x || (v == x && src > lane))) ++rank;
+        }
+    }
+    if (nz && adj > rank) p += (adj - rank - 1) / cnt + 1;
+    return p;
+}
+
+// Exclusive prefix (ascending lane order) of an int over the members of `mask`.
+__device__ __forceinline__ int group_prefix_excl(int x, uint32_t mask)
+{
+    const int lane = lane_id();
+    int res = 0;
+    uint32_t m = mask;
+#pragma unroll
+    for (int k = 0; k < NS; ++k) {
+        const bool valid = m != 0;
+        const int src = valid ? (__ffs(m) - 1) : lane;
+        m &= m - 1;
+        const int v = __shfl_sync(FULL, x, src);
+        if (valid && src < lane) res += v;
+    }
+    return res;
+}
+
+// ---- NumPy pairwise float64 sum of a 135-element row held in shared memory ----------------
+// n = 135 > 128: split at 64 | 71; each half: 8 interleaved accumulators combined as
+// ((r0+r1)+(r2+r3))+((r4+r5)+(r6+r7)), then the 7-element tail of the second half added
+// serially, halves added, then "0. +".  Lanes [g*8, g*8+8) reduce half `g&1` of row `g>>1`,
+// so one warp produces two row sums at once: result 0 valid in lane 0, result 1 in lane 16.
+// ues.py:108-116 (throughput) and np.mean(SE[0,u,:]) (ib_sched.py:111,147) depend on this order.
+__device__ __forceinline__ double np_sum135_pair(const double* rowA, const double* rowB)
+{
+    const int lane = lane_id();
+    const int j = lane & 7;
+    const int half = (lane >> 3) & 1;
+    const double* row = (lane < 16) ? rowA : rowB;
+    const double* p = row + half * 64 + j;
+    double r = p[0];
+#pragma unroll
+    for (int k = 1; k < 8; ++k) r += p[8 * k];
+    r = r + __shfl_down_sync(FULL, r, 1);
+    r = r + __shfl_down_sync(FULL, r, 2);
+    r = r + __shfl_down_sync(FULL, r, 4);
+    if (j == 0 && half == 1) {
+#pragma unroll
+        for (int k = 0; k < 7; ++k) r += row[128 + k];
+    }
+    const double other = __shfl_down_sync(FULL, r, 8);
+    return 0. + (r + other); // valid in lanes 0 and 16
+}
+
+__device__ __forceinline__ int scen_of_episode(const irs_config& c, int episode)
+{
+    const int s = c.assoc_mode == 0 ? episode % c.scen_mod : episode / c.scen_div;
+    return s % c.n_scen;
+}
+
+// per-UE buffer parameters: the UE's slice (associations/mult_slice.py:468-488 update_ues);
+// unassociated UEs keep the env defaults (comm_env.py:184-198).
+struct UeParams {
+    int depth;
+    int max_pkts;
+    double pkt_bits;
+};
+__device__ __forceinline__ UeParams ue_params(const irs_scenario* sc, int s)
+{
+    UeParams p;
+    if (s < 0) {
+        p.depth = 101; p.max_pkts = 10240; p.pkt_bits = 65536.0;
+    } else {
+        p.depth = (int)__ldg(&sc->sl[s].buffer_latency) + 1;
+        p.max_pkts = (int)__ldg(&sc->sl[s].buffer_size);
+        p.pkt_bits = __ldg(&sc->sl[s].message_size);
+    }
+    return p;
+}
