@@ -1,0 +1,58 @@
+"""Build the sm_100a shared library behind include/irs_b200.h (nvcc cross-compiles without a GPU).
+
+    python -m intent_radio_sched_multi_slice_b200.build [--force] [--verbose]
+
+The library is built in-tree (intent_radio_sched_multi_slice_b200/_lib/libirs_b200.so) so that
+it travels with the repo snapshot to the GPU box.  -fmad=false: every float64 expression on
+the path feeds a floor()/comparison of the reference, which NumPy evaluates without fused
+multiply-adds.
+"""
+from __future__ import annotations
+
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+LIB_DIR = os.path.join(HERE, "_lib")
+LIB = os.path.join(LIB_DIR, "libirs_b200.so")
+SOURCES = ["irs_capi.cu"]
+HEADERS = ["irs_common.cuh", "irs_rng.cuh", "irs_action.cuh", "irs_ue.cuh", "irs_obs.cuh", "irs_env.cuh",
+           os.path.join("..", "..", "include", "irs_b200.h")]
+
+NVCC_FLAGS = [
+    "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-fmad=false",
+    "-Xcompiler", "-fPIC", "-shared", "-cudart", "static",
+]
+
+
+def nvcc() -> str:
+    for p in (os.environ.get("NVCC"), "/usr/local/cuda/bin/nvcc", "nvcc"):
+        if p and (os.path.isabs(p) and os.path.exists(p) or not os.path.isabs(p)):
+            return p
+    raise RuntimeError("nvcc not found")
+
+
+def stale() -> bool:
+    if not os.path.exists(LIB):
+        return True
+    t = os.path.getmtime(LIB)
+    deps = [os.path.join(CSRC, f) for f in SOURCES + HEADERS] + [os.path.abspath(__file__)]
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    if not force and not stale():
+        return LIB
+    os.makedirs(LIB_DIR, exist_ok=True)
+    cmd = [nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
+          ["-o", LIB] + [os.path.join(CSRC, f) for f in SOURCES]
+    if verbose:
+        print(" ".join(cmd), file=sys.stderr)
+    subprocess.check_call(cmd)
+    return LIB
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))

@@ -1,0 +1,335 @@
+// irs_capi.cu - the C ABI declared in include/irs_b200.h: host-side handle, state-blob layout
+// and kernel launches.  No allocation, no synchronisation and no host<->device copy happens
+// in irs_step / irs_reset / irs_run (they are CUDA-graph capturable); the *_host variants add
+// the copies a single-process caller with host buffers needs.
+#include <stdio.h>
+#include <string.h>
+
+#include <new>
+
+#include "irs_action.cuh"
+#include "irs_env.cuh"
+#include "irs_ue.cuh"
+
+struct irs_env {
+    irs_config cfg;
+    irs_layout lay;
+    int32_t n_lambda;
+    bool bound, loaded;
+    DevState st;
+    char* blob;
+    char err[256];
+};
+
+static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+static void compute_layout(const irs_config& c, int32_t n_lambda, irs_layout* L)
+{
+    memset(L, 0, sizeof(*L));
+    const size_t E = (size_t)c.num_envs;
+    L->row_stride = (c.depth_cap + 3) / 4 * 4;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
+    L->buf = take(E * U * L->row_stride * 4);
+    L->occ = take(E * U * 8); L->lat = take(E * U * 8); L->sebar = take(E * U * 8);
+    L->tot = take(E * U * 4);
+    L->sum_sent = take(E * U * 4); L->sum_drop = take(E * U * 4);
+    L->last_sent = take(E * U * 4); L->last_drop = take(E * U * 4); L->last_inc = take(E * U * 4);
+    L->ring_sent = take(E * W * U * 4); L->ring_drop = take(E * W * U * 4);
+    L->thr = take(E * U * 8);
+    L->occ1z = take(E * U);
+    L->rb_start = take(E * U * 2); L->rb_count = take(E * U * 2);
+    L->step = take(E * 4); L->episode = take(E * 4); L->scen = take(E * 4);
+    L->win_len = take(E * 4); L->win_head = take(E * 4); L->err = take(E * 4);
+    L->sorted = take(E * S);
+    L->acc = take(E * IRS_NUM_METRICS * 8);
+    L->bank = take((size_t)c.n_scen * sizeof(irs_scenario));
+    L->cdf = take((size_t)(n_lambda > 0 ? n_lambda : 1) * IRS_POISSON_K * 8);
+    L->in_a0 = take(E * S * 8); L->in_intra = take(E * S * 4);
+    L->out_obs0 = take(E * IRS_OBS0 * 8);
+    L->out_obsi = take(E * S * IRS_OBSI * 8);
+    L->out_mask0 = take(E * S);
+    L->out_maski = take(E * S * NS);
+    L->out_reward = take(E * 6 * 8);
+    L->out_done = take(E);
+    L->metrics_total = take(IRS_NUM_METRICS * 8);
+    L->total_bytes = off;
+}
+
+static int fail(irs_env* env, int code, const char* msg)
+{
+    if (env) snprintf(env->err, sizeof(env->err), "%s", msg);
+    return code;
+}
+static int cuda_fail(irs_env* env, cudaError_t e, const char* where)
+{
+    if (env) snprintf(env->err, sizeof(env->err), "%s: %s", where, cudaGetErrorString(e));
+    return IRS_ERR_CUDA;
+}
+#define CK(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) return cuda_fail(env, _e, #call); } while (0)
+
+static StepArgs make_args(const irs_env* env)
+{
+    StepArgs A;
+    memset(&A, 0, sizeof(A));
+    A.st = env->st;
+    A.cfg = env->cfg;
+    A.initial_episode = -1;
+    return A;
+}
+
+extern "C" {
+
+int irs_version(void) { return 1; }
+
+int irs_create(const irs_config* cfg, int32_t n_lambda, irs_env** out)
+{
+    if (!cfg || !out) return IRS_ERR_ARG;
+    *out = nullptr;
+    if (cfg->num_envs <= 0 || cfg->depth_cap <= 0 || cfg->n_scen <= 0 || cfg->max_steps <= 0 ||
+        cfg->channel_mode < 0 || cfg->channel_mode > 2 || cfg->traffic_mode < 0 || cfg->traffic_mode > 1 ||
+        cfg->policy < 0 || cfg->policy > 3 || cfg->fixed_intra < -1 || cfg->fixed_intra > 2 ||
+        (cfg->assoc_mode == 0 && cfg->scen_mod <= 0) || (cfg->assoc_mode == 1 && cfg->scen_div <= 0) ||
+        cfg->assoc_mode < 0 || cfg->assoc_mode > 1 || !(cfg->bandwidth > 0) ||
+        (cfg->traffic_mode == 1 && n_lambda <= 0))
+        return IRS_ERR_ARG;
+    irs_env* env = new (std::nothrow) irs_env;
+    if (!env) return IRS_ERR_ARG;
+    memset(env, 0, sizeof(*env));
+    env->cfg = *cfg;
+    env->n_lambda = n_lambda;
+    compute_layout(env->cfg, n_lambda, &env->lay);
+    *out = env;
+    return IRS_OK;
+}
+
+int irs_destroy(irs_env* env)
+{
+    delete env;
+    return IRS_OK;
+}
+
+int irs_state_layout(const irs_env* env, irs_layout* out)
+{
+    if (!env || !out) return IRS_ERR_ARG;
+    *out = env->lay;
+    return IRS_OK;
+}
+
+const char* irs_last_error(const irs_env* env) { return env ? env->err : "null handle"; }
+
+int irs_bind(irs_env* env, void* state_dev, size_t bytes, void* stream)
+{
+    if (!env || !state_dev) return IRS_ERR_ARG;
+    if (bytes < env->lay.total_bytes) return fail(env, IRS_ERR_ARG, "state blob smaller than irs_state_layout().total_bytes");
+    if (((uintptr_t)state_dev & 255) != 0) return fail(env, IRS_ERR_ARG, "state blob must be 256-byte aligned");
+    char* b = (char*)state_dev;
+    const irs_layout& L = env->lay;
+    DevState& s = env->st;
+    env->blob = b;
+    s.buf = (int32_t*)(b + L.buf);
+    s.occ = (double*)(b + L.occ); s.lat = (double*)(b + L.lat); s.sebar = (double*)(b + L.sebar);
+    s.thr = (double*)(b + L.thr);
+    s.tot = (int32_t*)(b + L.tot);
+    s.sum_sent = (int32_t*)(b + L.sum_sent); s.sum_drop = (int32_t*)(b + L.sum_drop);
+    s.last_sent = (int32_t*)(b + L.last_sent); s.last_drop = (int32_t*)(b + L.last_drop);
+    s.last_inc = (int32_t*)(b + L.last_inc);
+    s.ring_sent = (int32_t*)(b + L.ring_sent); s.ring_drop = (int32_t*)(b + L.ring_drop);
+    s.occ1z = (uint8_t*)(b + L.occ1z);
+    s.rb_start = (int16_t*)(b + L.rb_start); s.rb_count = (int16_t*)(b + L.rb_count);
+    s.step = (int32_t*)(b + L.step); s.episode = (int32_t*)(b + L.episode); s.scen = (int32_t*)(b + L.scen);
+    s.win_len = (int32_t*)(b + L.win_len); s.win_head = (int32_t*)(b + L.win_head); s.err = (int32_t*)(b + L.err);
+    s.sorted = (int8_t*)(b + L.sorted);
+    s.acc = (double*)(b + L.acc);
+    s.bank = (const irs_scenario*)(b + L.bank);
+    s.cdf = (const double*)(b + L.cdf);
+    s.in_a0 = (double*)(b + L.in_a0); s.in_intra = (int32_t*)(b + L.in_intra);
+    s.out_obs0 = (double*)(b + L.out_obs0); s.out_obsi = (double*)(b + L.out_obsi);
+    s.out_mask0 = (int8_t*)(b + L.out_mask0); s.out_maski = (int8_t*)(b + L.out_maski);
+    s.out_reward = (double*)(b + L.out_reward); s.out_done = (uint8_t*)(b + L.out_done);
+    s.metrics_total = (double*)(b + L.metrics_total);
+    s.row_stride = L.row_stride;
+    cudaStream_t st = (cudaStream_t)stream;
+    CK(cudaMemsetAsync(b, 0, L.total_bytes, st));
+    StepArgs A = make_args(env);
+    k_init<<<(env->cfg.num_envs + 255) / 256, 256, 0, st>>>(A);
+    CK(cudaGetLastError());
+    env->bound = true;
+    env->loaded = false;
+    return IRS_OK;
+}
+
+int irs_load_scenarios(irs_env* env, const irs_scenario* bank_host, int32_t n_scen, const double* cdf_host,
+                       int32_t n_lambda, void* stream)
+{
+    if (!env || !bank_host) return IRS_ERR_ARG;
+    if (!env->bound) return fail(env, IRS_ERR_UNBOUND, "irs_bind first");
+    if (n_scen != env->cfg.n_scen || n_lambda != env->n_lambda) return fail(env, IRS_ERR_ARG, "bank size differs from irs_create");
+    for (int i = 0; i < n_scen; ++i) {
+        for (int s = 0; s < S; ++s) {
+            const irs_slice& sl = bank_host[i].sl[s];
+            if (sl.n_ues > NS) return fail(env, IRS_ERR_ARG, "more than 5 UEs in a slice (agents/ib_sched.py:50)");
+            if (sl.n_ues > 0 && ((int)sl.buffer_latency + 1 > env->cfg.depth_cap || sl.buffer_size < 1 || sl.message_size < 1))
+                return fail(env, IRS_ERR_ARG, "slice buffer parameters out of range (depth_cap too small?)");
+            if ((sl.flags & IRS_F_REQ) && env->cfg.traffic_mode == 1 && (sl.lam_idx < 0 || sl.lam_idx >= n_lambda))
+                return fail(env, IRS_ERR_ARG, "lam_idx outside the Poisson tables");
+        }
+        for (int u = 0; u < U; ++u)
+            if (bank_host[i].ue_slice[u] < -1 || bank_host[i].ue_slice[u] >= S) return fail(env, IRS_ERR_ARG, "ue_slice out of range");
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    CK(cudaMemcpyAsync(env->blob + env->lay.bank, bank_host, (size_t)n_scen * sizeof(irs_scenario), cudaMemcpyHostToDevice, st));
+    if (n_lambda > 0 && cdf_host)
+        CK(cudaMemcpyAsync(env->blob + env->lay.cdf, cdf_host, (size_t)n_lambda * IRS_POISSON_K * 8, cudaMemcpyHostToDevice, st));
+    CK(cudaStreamSynchronize(st)); // the host arrays may be freed on return
+    env->loaded = true;
+    return IRS_OK;
+}
+
+static int check_ready(irs_env* env, const irs_inject* inj)
+{
+    if (!env) return IRS_ERR_ARG;
+    if (!env->bound || !env->loaded) return fail(env, IRS_ERR_UNBOUND, "irs_bind and irs_load_scenarios first");
+    if (env->cfg.channel_mode == 0 && !(inj && inj->se)) return fail(env, IRS_ERR_ARG, "channel_mode 0 needs inject.se");
+    return IRS_OK;
+}
+
+int irs_reset(irs_env* env, const uint8_t* mask_dev, int32_t initial_episode, const int32_t* initial_episode_dev,
+              const irs_inject* inject, const irs_raw_outputs* raw, void* stream)
+{
+    int rc = check_ready(env, inject);
+    if (rc) return rc;
+    StepArgs A = make_args(env);
+    if (inject) { A.se = inject->se; A.traffic = inject->traffic; }
+    if (raw) A.raw = *raw;
+    A.reset_mask = mask_dev;
+    A.initial_episode = initial_episode;
+    A.initial_episode_dev = initial_episode_dev;
+    const int E = env->cfg.num_envs;
+    k_reset<<<(E + ENV_WARPS - 1) / ENV_WARPS, ENV_WARPS * 32, 0, (cudaStream_t)stream>>>(A);
+    CK(cudaGetLastError());
+    return IRS_OK;
+}
+
+static int launch_step(irs_env* env, const StepArgs& A, cudaStream_t st)
+{
+    const int E = env->cfg.num_envs;
+    k_action<<<(E + 7) / 8, 256, 0, st>>>(A);
+    const long long rows = (long long)E * U;
+    k_ue_step<<<(unsigned)((rows + UE_WARPS - 1) / UE_WARPS), UE_WARPS * 32, 0, st>>>(A);
+    k_env_tail<<<(E + ENV_WARPS - 1) / ENV_WARPS, ENV_WARPS * 32, 0, st>>>(A);
+    CK(cudaGetLastError());
+    return IRS_OK;
+}
+
+int irs_step(irs_env* env, const irs_actions* actions, const irs_inject* inject, const irs_raw_outputs* raw, void* stream)
+{
+    int rc = check_ready(env, inject);
+    if (rc) return rc;
+    if (env->cfg.policy == 0 && !(actions && actions->a0)) return fail(env, IRS_ERR_ARG, "policy 0 needs actions.a0");
+    if (env->cfg.policy == 0 && env->cfg.fixed_intra < 0 && !actions->intra) return fail(env, IRS_ERR_ARG, "fixed_intra -1 needs actions.intra");
+    if (env->cfg.traffic_mode == 0 && !(inject && inject->traffic)) return fail(env, IRS_ERR_ARG, "traffic_mode 0 needs inject.traffic");
+    StepArgs A = make_args(env);
+    if (actions) { A.a0 = actions->a0; A.intra = actions->intra; }
+    if (inject) { A.se = inject->se; A.traffic = inject->traffic; }
+    if (raw) A.raw = *raw;
+    return launch_step(env, A, (cudaStream_t)stream);
+}
+
+int irs_run(irs_env* env, int32_t n_steps, void* stream)
+{
+    int rc = check_ready(env, nullptr);
+    if (rc) return rc;
+    if (env->cfg.policy == 0 || env->cfg.traffic_mode == 0) return fail(env, IRS_ERR_ARG, "irs_run needs an on-device policy and native generators");
+    StepArgs A = make_args(env);
+    for (int i = 0; i < n_steps; ++i) {
+        rc = launch_step(env, A, (cudaStream_t)stream);
+        if (rc) return rc;
+    }
+    return IRS_OK;
+}
+
+static int copy_surface(irs_env* env, const irs_host_surface* o, bool with_reward, cudaStream_t st)
+{
+    const size_t E = (size_t)env->cfg.num_envs;
+    const irs_layout& L = env->lay;
+    char* b = env->blob;
+    if (o->obs0) CK(cudaMemcpyAsync(o->obs0, b + L.out_obs0, E * IRS_OBS0 * 8, cudaMemcpyDeviceToHost, st));
+    if (o->obsi) CK(cudaMemcpyAsync(o->obsi, b + L.out_obsi, E * S * IRS_OBSI * 8, cudaMemcpyDeviceToHost, st));
+    if (o->mask0) CK(cudaMemcpyAsync(o->mask0, b + L.out_mask0, E * S, cudaMemcpyDeviceToHost, st));
+    if (o->maski) CK(cudaMemcpyAsync(o->maski, b + L.out_maski, E * S * NS, cudaMemcpyDeviceToHost, st));
+    if (with_reward && o->reward) CK(cudaMemcpyAsync(o->reward, b + L.out_reward, E * 6 * 8, cudaMemcpyDeviceToHost, st));
+    if (with_reward && o->done) CK(cudaMemcpyAsync(o->done, b + L.out_done, E, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return IRS_OK;
+}
+
+int irs_step_host(irs_env* env, const irs_actions* actions_host, const irs_host_surface* out_host, void* stream)
+{
+    int rc = check_ready(env, nullptr);
+    if (rc) return rc;
+    if (env->cfg.channel_mode == 0 || env->cfg.traffic_mode == 0) return fail(env, IRS_ERR_ARG, "irs_step_host needs native or fixed generators");
+    if (!out_host) return IRS_ERR_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t E = (size_t)env->cfg.num_envs;
+    StepArgs A = make_args(env);
+    if (env->cfg.policy == 0) {
+        if (!(actions_host && actions_host->a0)) return fail(env, IRS_ERR_ARG, "policy 0 needs actions.a0");
+        CK(cudaMemcpyAsync(env->st.in_a0, actions_host->a0, E * S * 8, cudaMemcpyHostToDevice, st));
+        A.a0 = env->st.in_a0;
+        if (actions_host->intra) {
+            CK(cudaMemcpyAsync(env->st.in_intra, actions_host->intra, E * S * 4, cudaMemcpyHostToDevice, st));
+            A.intra = env->st.in_intra;
+        } else if (env->cfg.fixed_intra < 0) return fail(env, IRS_ERR_ARG, "fixed_intra -1 needs actions.intra");
+    }
+    rc = launch_step(env, A, st);
+    if (rc) return rc;
+    return copy_surface(env, out_host, true, st);
+}
+
+int irs_reset_host(irs_env* env, int32_t initial_episode, const irs_host_surface* out_host, void* stream)
+{
+    int rc = irs_reset(env, nullptr, initial_episode, nullptr, nullptr, nullptr, stream);
+    if (rc) return rc;
+    if (!out_host) return IRS_ERR_ARG;
+    return copy_surface(env, out_host, false, (cudaStream_t)stream);
+}
+
+int irs_episode_metrics(irs_env* env, double* host_out, void* stream)
+{
+    if (!env || !env->bound) return IRS_ERR_UNBOUND;
+    cudaStream_t st = (cudaStream_t)stream;
+    StepArgs A = make_args(env);
+    k_metrics<<<1, 32, 0, st>>>(A);
+    CK(cudaGetLastError());
+    if (host_out) {
+        CK(cudaMemcpyAsync(host_out, env->st.metrics_total, IRS_NUM_METRICS * 8, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+    }
+    return IRS_OK;
+}
+
+int irs_check_errors(irs_env* env, int32_t* first_env, int32_t* code, void* stream)
+{
+    if (!env || !env->bound) return IRS_ERR_UNBOUND;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int E = env->cfg.num_envs;
+    int32_t* h = new (std::nothrow) int32_t[E];
+    if (!h) return IRS_ERR_ARG;
+    cudaError_t e = cudaMemcpyAsync(h, env->st.err, (size_t)E * 4, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) { delete[] h; return cuda_fail(env, e, "irs_check_errors"); }
+    int rc = IRS_OK;
+    for (int i = 0; i < E; ++i)
+        if (h[i]) {
+            if (first_env) *first_env = i;
+            if (code) *code = h[i];
+            snprintf(env->err, sizeof(env->err), "env %d error word %d", i, h[i]);
+            rc = IRS_ERR_ENV;
+            break;
+        }
+    delete[] h;
+    return rc;
+}
+
+} // extern "C"

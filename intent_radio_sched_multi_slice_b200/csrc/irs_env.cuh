@@ -1,0 +1,233 @@
+// irs_env.cuh - per-env tail of a step (reward, episode metrics, done, rollover) and reset.
+// One warp per env.  See irs_obs.cuh for the reference symbols replaced.
+#pragma once
+#include "irs_obs.cuh"
+
+#define ENV_WARPS 4 /* envs per block in k_env_tail / k_reset */
+
+// CommunicationEnv.reset (comm_env.py:375-482) for env e, by the whole warp.  `se_row` is a
+// 136-double shared-memory scratch row owned by the warp.  The observation window is NOT
+// cleared (ib_sched.py:51,64: the deque lives in the agent) - the zero frame of the reset is
+// pushed into it (comm_env.py:474-482), quirk Q1 of SURVEY 7.4.
+__device__ __forceinline__ void reset_env_warp(const StepArgs& A, int e, int initial_episode, double* se_row)
+{
+    const DevState& st = A.st;
+    const irs_config& c = A.cfg;
+    const int lane = lane_id();
+    int step = st.step[e], ep = st.episode[e];
+    const int init = initial_episode != -1 ? initial_episode : c.initial_episode;
+    if ((step == 0 && ep == 0) || (step == c.max_steps && ep == c.max_episodes - 1) || initial_episode != -1) {
+        ep = init;                                              // comm_env.py:416-421
+    } else if (step == 0 && ep <= c.max_episodes - 1) {         // :422-425
+    } else if (ep < c.max_episodes - 1) {
+        ep += 1;                                                // :426-427
+    } else {
+        if (lane == 0) atomicOr(&st.err[e], ERR_EPISODE_RANGE); // :428-433
+        return;
+    }
+    const int scen = scen_of_episode(c, ep);
+    const irs_scenario* sc = st.bank + scen;
+    __syncwarp();
+    if (lane == 0) { st.step[e] = 0; st.episode[e] = ep; st.scen[e] = scen; }
+    // fresh UEs: empty buffers (comm_env.py:620-625, associations/mult_slice.py:468-488)
+    {
+        int4* rows = reinterpret_cast<int4*>(st.buf + (size_t)e * U * st.row_stride);
+        const int n4 = U * st.row_stride / 4;
+        for (int i = lane; i < n4; i += 32) rows[i] = make_int4(0, 0, 0, 0);
+    }
+    // channel frame 0 of the new episode -> mean SE per UE (comm_env.py:449-451)
+    double sebar = 0;
+    for (int u = 0; u < U; ++u) {
+        channel_row(A, e, u, sc->ue_slice[u] >= 0, 0, ep, se_row);
+        __syncwarp();
+        if (A.raw.se_used)
+            for (int r = lane; r < R; r += 32) A.raw.se_used[((size_t)e * U + u) * R + r] = se_row[r];
+        const double sum = __shfl_sync(FULL, np_sum135_pair(se_row, se_row), 0);
+        if (lane == u) sebar = sum / (double)R;
+        __syncwarp();
+    }
+    // push the all-zero metrics frame (comm_env.py:474-478)
+    const int win_len = st.win_len[e];
+    const int p = (st.win_head[e] + 1) % W;
+    UeFrame f;
+    f.occ = 0; f.lat = 0; f.sebar = sebar; f.sent = 0; f.rb_count = 0;
+    f.sum_sent = 0; f.sum_drop = 0; f.occ1z = false;
+    if (lane < U) {
+        const size_t eu = (size_t)e * U + lane;
+        const size_t ri = ((size_t)e * W + p) * U + lane;
+        int ss = st.sum_sent[eu], sd = st.sum_drop[eu];
+        if (win_len == W) { ss -= st.ring_sent[ri]; sd -= st.ring_drop[ri]; }
+        st.ring_sent[ri] = 0;
+        st.ring_drop[ri] = 0;
+        st.sum_sent[eu] = ss;
+        st.sum_drop[eu] = sd;
+        f.sum_sent = ss; f.sum_drop = sd;
+        f.occ1z = isclose0(st.occ[eu]);
+        st.occ1z[eu] = f.occ1z ? 1 : 0;
+        st.occ[eu] = 0; st.lat[eu] = 0; st.sebar[eu] = sebar; st.thr[eu] = 0;
+        st.tot[eu] = 0; st.last_sent[eu] = 0; st.last_drop[eu] = 0; st.last_inc[eu] = 0;
+        st.rb_start[eu] = 0; st.rb_count[eu] = 0;
+    }
+    const int win_len_new = win_len < W ? win_len + 1 : W;
+    __syncwarp();
+    if (lane == 0) { st.win_len[e] = win_len_new; st.win_head[e] = p; }
+    format_obs_warp(A, e, sc, f, win_len_new);
+}
+
+// Everything of CommunicationEnv.step after UEs.step (comm_env.py:339-373).
+__device__ __forceinline__ void env_tail_warp(const StepArgs& A, int e, double* se_row)
+{
+    const DevState& st = A.st;
+    const irs_config& c = A.cfg;
+    const int lane = lane_id();
+    const size_t eu = (size_t)e * U + (lane < U ? lane : 0);
+    UeFrame f;
+    f.occ = st.occ[eu]; f.lat = st.lat[eu]; f.sebar = st.sebar[eu];
+    f.sent = st.last_sent[eu]; f.sum_sent = st.sum_sent[eu]; f.sum_drop = st.sum_drop[eu];
+    f.rb_count = st.rb_count[eu]; f.occ1z = st.occ1z[eu] != 0;
+    int dropped = st.last_drop[eu], inc = st.last_inc[eu];
+    if (lane >= U) { f.sent = 0; f.rb_count = 0; dropped = 0; inc = 0; }
+    // the per-UE part of the window push was done by k_ue_step; finish the per-env part
+    const int win_len_old = st.win_len[e];
+    const int win_len = win_len_old < W ? win_len_old + 1 : W;
+    const int head = (st.win_head[e] + 1) % W;
+    const int step = st.step[e] + 1; // comm_env.py:339
+    const irs_scenario* sc = st.bank + st.scen[e];
+    __syncwarp();
+    if (lane == 0) { st.win_len[e] = win_len; st.win_head[e] = head; st.step[e] = step; }
+
+    const SliceView v = format_obs_warp(A, e, sc, f, win_len); // comm_env.py:340
+
+    // ---- calculate_reward (ib_sched.py:206-221, common.py:381-439) ----------------------
+    const double prio_raw = __ldg(&sc->sl[lane < S ? lane : 0].priority);
+    double a_s = 0, p_s = 0;
+    if (v.active) { // common.py:400-408; inactive metrics are already 0 (quirk Q4)
+        p_s = prio_raw;
+        double mn = v.dsl[0];
+        mn = v.dsl[1] < mn ? v.dsl[1] : mn;
+        mn = v.dsl[2] < mn ? v.dsl[2] : mn;
+        a_s = mn;
+    }
+    double Aa[S], Pp[S];
+    int nneg = 0, npneg = 0;
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+        Aa[s] = __shfl_sync(FULL, a_s, s);
+        Pp[s] = __shfl_sync(FULL, p_s, s);
+        nneg += Aa[s] < 0;
+        npneg += (Pp[s] * Aa[s]) < 0;
+    }
+    double r0;
+    {
+        double res = 0.;
+        int m = 0;
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+            const bool sel = nneg == 0 ? true : (npneg ? (Aa[s] * Pp[s] < 0) : (Aa[s] < 0));
+            if (sel) { res += Aa[s]; ++m; }
+        }
+        r0 = (0. + res) / (double)m - ((nneg != 0 && npneg) ? 1 : 0); // common.py:410-426
+    }
+    double r_intra = 0; // common.py:428-437
+    {
+        bool any = false;
+        double mn = 0;
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+            if (v.act[k] != 0) { mn = any ? (v.dsl[k] < mn ? v.dsl[k] : mn) : v.dsl[k]; any = true; }
+        if (any) r_intra = mn;
+    }
+    if (lane == 0) st.out_reward[(size_t)e * 6] = r0;
+    if (lane < S) st.out_reward[(size_t)e * 6 + 1 + lane] = r_intra;
+
+    // ---- episode metrics (metrics.py:62-71 as running sums; definitions from
+    //      results/gen_results.py:791-809, 874-970, 973-1022) -----------------------------
+    long long t_sent = f.sent, t_drop = dropped, t_inc = inc;
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        t_sent += __shfl_xor_sync(FULL, t_sent, d);
+        t_drop += __shfl_xor_sync(FULL, t_drop, d);
+        t_inc += __shfl_xor_sync(FULL, t_inc, d);
+    }
+    bool viol = false;
+    double vmn = 0;
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+        if (v.act[k] != 0 && v.dsl[k] < 0) { vmn = viol ? (v.dsl[k] < vmn ? v.dsl[k] : vmn) : v.dsl[k]; viol = true; }
+    double add10 = 0, add11 = 0;
+    double ri[S];
+#pragma unroll
+    for (int s = 0; s < S; ++s) ri[s] = __shfl_sync(FULL, r_intra, s);
+    double* acc = st.acc + (size_t)e * IRS_NUM_METRICS;
+    double a9 = acc[9], a12 = acc[12], a13 = acc[13];
+#pragma unroll
+    for (int pos = 0; pos < S; ++pos) { // sorted order, like the observation vector
+        const uint32_t b = __ballot_sync(FULL, lane < S && v.pos == pos);
+        const int sl = __ffs(b) - 1;
+        const bool act_s = __shfl_sync(FULL, (int)v.active, sl);
+        const long long snt = __shfl_sync(FULL, v.snt, sl);
+        const double msg = __shfl_sync(FULL, v.msg, sl);
+        const double pr = __shfl_sync(FULL, prio_raw, sl);
+        const bool vi = __shfl_sync(FULL, (int)viol, sl);
+        const double mn = __shfl_sync(FULL, vmn, sl);
+        if (!act_s) continue;
+        a9 += ((double)snt * msg) / 1e6;
+        if (vi) {
+            add10 += 1; a12 += mn;
+            if (pr != 0) { add11 += 1; a13 += mn; }
+        }
+    }
+    const bool done = step == c.max_steps; // comm_env.py:370
+    if (lane == 0) {
+        acc[0] += r0;
+#pragma unroll
+        for (int s = 0; s < S; ++s) acc[1 + s] += ri[s];
+        acc[6] += (double)t_sent; acc[7] += (double)t_drop; acc[8] += (double)t_inc;
+        acc[9] = a9; acc[10] += add10; acc[11] += add11; acc[12] = a12; acc[13] = a13;
+        acc[14] += 1;
+        if (done) acc[15] += 1;
+        st.out_done[e] = done ? 1 : 0;
+    }
+    if (done && c.auto_reset) {
+        __syncwarp();
+        reset_env_warp(A, e, -1, se_row);
+    }
+}
+
+__global__ void __launch_bounds__(ENV_WARPS * 32) k_env_tail(const __grid_constant__ StepArgs A)
+{
+    __shared__ double sm[ENV_WARPS][136];
+    const int e = blockIdx.x * ENV_WARPS + (threadIdx.x >> 5);
+    if (e >= A.cfg.num_envs) return;
+    env_tail_warp(A, e, sm[threadIdx.x >> 5]);
+}
+
+__global__ void __launch_bounds__(ENV_WARPS * 32) k_reset(const __grid_constant__ StepArgs A)
+{
+    __shared__ double sm[ENV_WARPS][136];
+    const int e = blockIdx.x * ENV_WARPS + (threadIdx.x >> 5);
+    if (e >= A.cfg.num_envs) return;
+    if (A.reset_mask && !A.reset_mask[e]) return;
+    const int init = A.initial_episode_dev ? A.initial_episode_dev[e] : A.initial_episode;
+    reset_env_warp(A, e, init, sm[threadIdx.x >> 5]);
+}
+
+// state right after irs_bind: episode counter at its initial value, identity slice order
+// (ib_sched.py:58), everything else zero.
+__global__ void k_init(const __grid_constant__ StepArgs A)
+{
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= A.cfg.num_envs) return;
+    A.st.episode[e] = A.cfg.initial_episode;
+    for (int s = 0; s < S; ++s) A.st.sorted[(size_t)e * S + s] = (int8_t)s;
+}
+
+// Sum of the per-env accumulators in env order (fixed order -> reproducible bits).
+__global__ void k_metrics(const __grid_constant__ StepArgs A)
+{
+    const int k = threadIdx.x;
+    if (k >= IRS_NUM_METRICS) return;
+    double t = 0;
+    for (int e = 0; e < A.cfg.num_envs; ++e) t += A.st.acc[(size_t)e * IRS_NUM_METRICS + k];
+    A.st.metrics_total[k] = t;
+}

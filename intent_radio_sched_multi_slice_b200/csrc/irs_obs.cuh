@@ -1,0 +1,175 @@
+// irs_obs.cuh - K4: observation, action masks, reward, episode metrics and episode rollover,
+// one warp per env: lane u = UE u, and lanes 0..4 double as slice 0..4.
+//
+// Replaces
+//   intent_drift_calc + get_metric_value     agents/common.py:9-340
+//   calculate_slice_ue_obs                   agents/common.py:343-378
+//   IBSched.obs_space_format / sort_slices   agents/ib_sched.py:63-204, 351-370
+//   IBSched.calculate_reward / unsort_slices agents/ib_sched.py:206-221, 372-392
+//   calculate_reward_no_mask                 agents/common.py:381-439
+//   Metrics.step (as running sums)           sixg_radio_mgmt/sixg_radio_mgmt/metrics.py:62-71
+//   CommunicationEnv.reset                   sixg_radio_mgmt/sixg_radio_mgmt/comm_env.py:375-482
+#pragma once
+#include "irs_common.cuh"
+#include "irs_rng.cuh"
+#include "irs_ue.cuh"
+
+struct UeFrame { // newest window frame of this lane's UE (+ window sums)
+    double occ, lat, sebar;
+    int sent, sum_sent, sum_drop, rb_count;
+    bool occ1z;
+};
+struct SliceView { // valid on lanes 0..4 (slice = lane)
+    double dsl[3], act[3];
+    double prio, msg;
+    long long snt;
+    int n, pos;
+    bool active;
+};
+
+// common.py:9-65 + 68-340 for one UE; r = intent_overfulfillment_rate 0.2 (ib_sched.py:53)
+__device__ __forceinline__ void intent_drift_ue(const irs_slice* sl, int flags, const UeFrame& f, int win_len,
+                                                double (&drift)[3])
+{
+    const double r = 0.2;
+    drift[0] = drift[1] = drift[2] = 0;
+    if (flags & IRS_F_THR) {
+        const double v = __ldg(&sl->thr_value);
+        double m = (double)((long long)f.sent * (long long)__ldg(&sl->message_size)) / 1e6; // :26-31
+        bool zero = isclose0(f.occ);                                                        // :104-107
+        if (win_len > 1) zero = zero || f.occ1z;                                            // :108-116
+        if (zero) m = v * (1.1 + r);                                                        // :117-119
+        if (m >= v) {
+            if (m > v * (1 + r)) drift[0] += 1;        // :164-168
+            else drift[0] += (m - v) / (v * r);        // :154-162
+        } else {
+            drift[0] -= (v - m) / v;                   // :172-181
+        }
+    }
+    if (flags & IRS_F_REL) {
+        const double v = __ldg(&sl->rel_value);
+        const double den = (f.occ * __ldg(&sl->buffer_size) + (double)f.sum_drop) + (double)f.sum_sent; // :40-47
+        const double m = den != 0 ? (double)f.sum_drop / den : 0.0;                                      // :48-53
+        const double t = (100 - v) / 100;
+        if (100 * (1 - m) >= v) {                      // :124-126
+            if (m < t * (1 - r)) drift[1] += 1;        // :188-220
+            else drift[1] += (t - m) / (t * r);
+        } else {
+            drift[1] -= (m - t) / (v / 100);           // :223-233
+        }
+    }
+    if (flags & IRS_F_LAT) {
+        const double v = __ldg(&sl->lat_value);
+        const double m = f.lat;
+        if (m <= v) {
+            if (m < v * (1 - r)) drift[2] += 1;        // :290-319
+            else drift[2] += (v - m) / (v * r);
+        } else {
+            drift[2] -= (m - v) / (__ldg(&sl->buffer_latency) - v); // :322-335
+        }
+    }
+}
+
+// ib_sched.py:63-204.  Writes obs0/obs_i/masks/sorted for env e; returns the slice view the
+// reward needs.  `sc` is the scenario the env is playing; all 32 lanes must call.
+__device__ __forceinline__ SliceView format_obs_warp(const StepArgs& A, int e, const irs_scenario* sc,
+                                                     const UeFrame& f, int win_len)
+{
+    const DevState& st = A.st;
+    const int lane = lane_id();
+    const int s_mine = lane < U ? (int)sc->ue_slice[lane] : -1;
+    uint32_t smask[S], gmask = 0;
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+        smask[s] = __ballot_sync(FULL, s_mine == s);
+        if (s_mine == s) gmask = smask[s];
+    }
+    const bool member = s_mine >= 0;
+    const int n_mine = __popc(gmask);
+    const irs_slice* sl_u = &sc->sl[member ? s_mine : 0];
+    const int fl_u = member ? __ldg(&sl_u->flags) : 0;
+
+    // per-UE drift, then the slice means (common.py:371-373 np.mean over the slice's UEs)
+    double drift[3] = {0, 0, 0};
+    if (member && (fl_u & IRS_F_REQ)) intent_drift_ue(sl_u, fl_u, f, win_len, drift);
+    double dsl_u[3];
+    const int fbit[3] = {IRS_F_THR, IRS_F_REL, IRS_F_LAT};
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const double mean = group_sum_ordered(drift[k], gmask) / (double)n_mine;
+        dsl_u[k] = ((fl_u & IRS_F_REQ) && (fl_u & fbit[k])) ? mean : -2.0;
+    }
+    const double se_slice_u = group_sum_ordered(f.sebar, gmask) / (double)n_mine; // ib_sched.py:146-157
+    const int rbs_alloc_u = group_sum_int(f.rb_count, gmask);                      // :176-181
+    const int snt_u = group_sum_int(f.sent, gmask);
+
+    // ---- slice lanes: fetch the slice-level values from the slice's first UE lane -------
+    const int sl_id = lane < S ? lane : 0;
+    const uint32_t my_smask = lane < S ? smask[0] * (lane == 0) + smask[1] * (lane == 1) + smask[2] * (lane == 2) +
+                                             smask[3] * (lane == 3) + smask[4] * (lane == 4)
+                                       : 0u;
+    const int src = my_smask ? (__ffs(my_smask) - 1) : lane;
+    SliceView v;
+    v.n = __popc(my_smask);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const double d = __shfl_sync(FULL, dsl_u[k], src);
+        v.dsl[k] = v.n > 0 ? d : -2.0;
+    }
+    double se_slice = __shfl_sync(FULL, se_slice_u, src);
+    int rbs_alloc = __shfl_sync(FULL, rbs_alloc_u, src);
+    int snt = __shfl_sync(FULL, snt_u, src);
+    if (v.n == 0) { se_slice = 0; rbs_alloc = 0; snt = 0; }
+    const irs_slice* sl = &sc->sl[sl_id];
+    const int fl = __ldg(&sl->flags);
+    v.active = (fl & IRS_F_ACTIVE) != 0;
+    v.msg = __ldg(&sl->message_size);
+    v.snt = snt;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { // ib_sched.py:142-145  (np.isclose(x, -2): atol 1e-8 + rtol 1e-5 * 2)
+        const bool close = fabs(v.dsl[k] - (-2.0)) <= 1e-8 + 1e-5 * 2.0;
+        v.act[k] = close ? 0 : 1;
+        if (close) v.dsl[k] = 0;
+    }
+    const double traffic = v.active ? __ldg(&sl->traffic) : 0; // :125-134
+    v.prio = v.n != 0 ? __ldg(&sl->priority) : 0;              // :135-141
+
+    // ---- sort_slices (ib_sched.py:351-370): stable ascending argsort of n_ues * traffic --
+    int pos = 0;
+    if (A.cfg.sort_slices) {
+        const double key = (double)__ldg(&sl->n_ues) * ((fl & IRS_F_REQ) ? __ldg(&sl->traffic) : 0.0);
+#pragma unroll
+        for (int j = 0; j < S; ++j) {
+            const double kj = __shfl_sync(FULL, key, j);
+            if (kj < key || (kj == key && j < lane)) ++pos;
+        }
+        if (lane < S) st.sorted[(size_t)e * S + pos] = (int8_t)lane;
+    } else {
+#pragma unroll
+        for (int j = 0; j < S; ++j)
+            if (st.sorted[(size_t)e * S + j] == lane) pos = j;
+    }
+    v.pos = pos;
+
+    if (lane < S) {
+        double* p0 = st.out_obs0 + (size_t)e * IRS_OBS0 + pos * 10; // :160-173
+        p0[0] = v.dsl[0]; p0[1] = v.dsl[1]; p0[2] = v.dsl[2];
+        p0[3] = v.act[0]; p0[4] = v.act[1]; p0[5] = v.act[2];
+        p0[6] = v.prio; p0[7] = traffic / 120.0; p0[8] = (double)v.n / 5.0; p0[9] = se_slice / 40.0;
+        double* pi = st.out_obsi + ((size_t)e * S + lane) * IRS_OBSI; // :186-200
+        pi[0] = v.dsl[0]; pi[1] = v.dsl[1]; pi[2] = v.dsl[2];
+        pi[3] = v.act[0]; pi[4] = v.act[1]; pi[5] = v.act[2];
+        pi[6] = (double)rbs_alloc / (double)R; pi[7] = traffic / 120.0; pi[8] = (double)v.n / 5.0;
+        for (int j = v.n; j < NS; ++j) { pi[9 + j] = 0; pi[14 + j] = 0; }
+        st.out_mask0[(size_t)e * S + lane] = v.active ? 1 : 0; // :76-81 (unsorted order)
+        for (int j = 0; j < NS; ++j) st.out_maski[((size_t)e * S + lane) * NS + j] = j < v.n ? 1 : 0;
+        if (A.raw.sorted_slices) A.raw.sorted_slices[(size_t)e * S + pos] = (int8_t)lane;
+    }
+    if (member) { // per-UE tail of player_{s+1}'s observation
+        const int j = __popc(gmask & ((1u << lane) - 1u));
+        double* pi = st.out_obsi + ((size_t)e * S + s_mine) * IRS_OBSI;
+        pi[9 + j] = f.occ;
+        pi[14 + j] = f.sebar / 40.0;
+    }
+    return v;
+}

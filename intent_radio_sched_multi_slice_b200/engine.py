@@ -1,0 +1,189 @@
+"""BatchEngine: E env instances as structure-of-arrays state in HBM, stepped through the C ABI.
+
+PyTorch owns the memory (one uint8 state blob, viewed as typed tensors) and the stream; the
+kernels live in libirs_b200.so.  This is the layer `BatchedMARLCommEnv` (env.py) and bench.py
+sit on.  There is no CPU path: constructing an engine without CUDA raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import capi
+from .scenario import ScenarioBank
+
+U, S, R = capi.MAX_UES, capi.MAX_SLICES, capi.NUM_RBS
+
+_VIEWS = {  # name -> (torch dtype, trailing shape)
+    "occ": (torch.float64, (U,)), "lat": (torch.float64, (U,)), "sebar": (torch.float64, (U,)),
+    "thr": (torch.float64, (U,)),
+    "tot": (torch.int32, (U,)), "sum_sent": (torch.int32, (U,)), "sum_drop": (torch.int32, (U,)),
+    "last_sent": (torch.int32, (U,)), "last_drop": (torch.int32, (U,)), "last_inc": (torch.int32, (U,)),
+    "ring_sent": (torch.int32, (capi.WINDOW, U)), "ring_drop": (torch.int32, (capi.WINDOW, U)),
+    "occ1z": (torch.uint8, (U,)), "rb_start": (torch.int16, (U,)), "rb_count": (torch.int16, (U,)),
+    "step": (torch.int32, ()), "episode": (torch.int32, ()), "scen": (torch.int32, ()),
+    "win_len": (torch.int32, ()), "win_head": (torch.int32, ()), "err": (torch.int32, ()),
+    "sorted": (torch.int8, (S,)), "acc": (torch.float64, (capi.NUM_METRICS,)),
+    "in_a0": (torch.float64, (S,)), "in_intra": (torch.int32, (S,)),
+    "out_obs0": (torch.float64, (capi.OBS0,)), "out_obsi": (torch.float64, (S, capi.OBSI)),
+    "out_mask0": (torch.int8, (S,)), "out_maski": (torch.int8, (S, 5)),
+    "out_reward": (torch.float64, (6,)), "out_done": (torch.uint8, ()),
+}
+
+_RAW_SPECS = {
+    "pkt_incoming": (torch.float64, (U,)), "pkt_throughputs": (torch.float64, (U,)),
+    "sent": (torch.int32, (U,)), "dropped": (torch.int32, (U,)), "occ": (torch.float64, (U,)),
+    "lat": (torch.float64, (U,)), "rb_start": (torch.int16, (U,)), "rb_count": (torch.int16, (U,)),
+    "sorted_slices": (torch.int8, (S,)), "a0_used": (torch.float64, (S,)), "intra_used": (torch.int32, (S,)),
+    "se_used": (torch.float64, (U, R)), "traffic_used": (torch.float64, (U,)),
+}
+
+
+def _nbytes(dtype):
+    return torch.empty((), dtype=dtype).element_size()
+
+
+class BatchEngine:
+    def __init__(self, bank: ScenarioBank, num_envs: int, *, device="cuda:0", depth_cap=None,
+                 channel_mode=2, traffic_mode=1, sort_slices=1, fixed_intra=-1, policy=0, assoc_mode=0,
+                 scen_mod=200, scen_div=100, max_steps=1000, max_episodes=10000, initial_episode=0,
+                 auto_reset=0, env_id_base=0, seed=10, bandwidth=1e8):
+        if not torch.cuda.is_available():
+            raise RuntimeError("intent_radio_sched_multi_slice_b200 needs a CUDA device (there is no CPU path)")
+        self.lib = capi.load()
+        self.device = torch.device(device)
+        self.E = int(num_envs)
+        self.bank_array = np.ascontiguousarray(bank.array())
+        self.cdf = np.ascontiguousarray(bank.poisson_cdf(), np.float64)
+        if depth_cap is None:
+            depth_cap = max(bank.max_depth(), 101)  # 101: default depth of unassociated UEs (comm_env.py:184-198)
+        self.cfg = capi.Config(self.E, int(depth_cap), channel_mode, traffic_mode, sort_slices, fixed_intra, policy,
+                               assoc_mode, scen_mod, scen_div, len(self.bank_array), max_steps, max_episodes,
+                               initial_episode, auto_reset, env_id_base, seed, bandwidth)
+        self.h = C.c_void_p()
+        rc = self.lib.irs_create(C.byref(self.cfg), self.cdf.shape[0], C.byref(self.h))
+        if rc:
+            raise capi.IrsError(rc, "irs_create rejected the configuration")
+        self.layout = capi.Layout()
+        capi.check(self.h, self.lib.irs_state_layout(self.h, C.byref(self.layout)))
+        self.row_stride = self.layout.row_stride
+        with torch.cuda.device(self.device):
+            self.blob = torch.empty(self.layout.total_bytes + 256, dtype=torch.uint8, device=self.device)
+            off = (-self.blob.data_ptr()) % 256
+            self.blob = self.blob[off:off + self.layout.total_bytes]
+            capi.check(self.h, self.lib.irs_bind(self.h, self.blob.data_ptr(), self.layout.total_bytes, self._stream()))
+            capi.check(self.h, self.lib.irs_load_scenarios(
+                self.h, self.bank_array.ctypes.data, len(self.bank_array), self.cdf.ctypes.data, self.cdf.shape[0],
+                self._stream()))
+        self.v = {name: self._view(name, dt, shp) for name, (dt, shp) in _VIEWS.items()}
+        self.buf = self._view("buf", torch.int32, (U, self.row_stride))
+        self.metrics_total = self._view1("metrics_total", torch.float64, capi.NUM_METRICS)
+        self._raw = None
+        self._raw_struct = None
+        self._keep = None
+
+    # -- plumbing ---------------------------------------------------------------------------
+    def _stream(self):
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def _view1(self, name, dtype, n):
+        off = getattr(self.layout, name)
+        return self.blob[off:off + n * _nbytes(dtype)].view(dtype)
+
+    def _view(self, name, dtype, shape):
+        n = self.E * int(np.prod(shape, dtype=np.int64)) if shape else self.E
+        return self._view1(name, dtype, n).view((self.E,) + tuple(shape))
+
+    def enable_raw_outputs(self, names=None):
+        """Allocate the optional per-UE outputs (ues.py:236-243 raw metrics + inputs used)."""
+        names = list(_RAW_SPECS) if names is None else list(names)
+        self._raw = {n: torch.zeros((self.E,) + _RAW_SPECS[n][1], dtype=_RAW_SPECS[n][0], device=self.device)
+                     for n in names}
+        self._raw_struct = capi.RawOutputs(*[self._raw[n].data_ptr() if n in self._raw else None
+                                             for n in capi.RAW_FIELDS])
+        return self._raw
+
+    def _raw_ref(self):
+        return C.byref(self._raw_struct) if self._raw_struct is not None else None
+
+    def _dev(self, x, dtype):
+        if x is None:
+            return None
+        if isinstance(x, torch.Tensor):
+            t = x.to(device=self.device, dtype=dtype).contiguous()
+        else:
+            t = torch.from_numpy(np.ascontiguousarray(x)).to(device=self.device, dtype=dtype)
+        return t
+
+    # -- the path ---------------------------------------------------------------------------
+    def reset(self, mask=None, initial_episode=-1, initial_episodes=None, se=None):
+        """CommunicationEnv.reset for the masked envs (comm_env.py:375-482)."""
+        m = self._dev(mask, torch.uint8)
+        ie = self._dev(initial_episodes, torch.int32)
+        se_t = self._dev(se, torch.float64)
+        inj = capi.Inject(se_t.data_ptr() if se_t is not None else None, None)
+        self._keep = (m, ie, se_t)
+        with torch.cuda.device(self.device):
+            capi.check(self.h, self.lib.irs_reset(
+                self.h, m.data_ptr() if m is not None else None, int(initial_episode),
+                ie.data_ptr() if ie is not None else None, C.byref(inj), self._raw_ref(), self._stream()))
+
+    def step(self, a0=None, intra=None, se=None, traffic=None):
+        """CommunicationEnv.step for every env (comm_env.py:271-373).  Asynchronous."""
+        a0_t, in_t = self._dev(a0, torch.float64), self._dev(intra, torch.int32)
+        se_t, tr_t = self._dev(se, torch.float64), self._dev(traffic, torch.float64)
+        act = capi.Actions(a0_t.data_ptr() if a0_t is not None else None, in_t.data_ptr() if in_t is not None else None)
+        inj = capi.Inject(se_t.data_ptr() if se_t is not None else None, tr_t.data_ptr() if tr_t is not None else None)
+        self._keep = (a0_t, in_t, se_t, tr_t)
+        with torch.cuda.device(self.device):
+            capi.check(self.h, self.lib.irs_step(self.h, C.byref(act), C.byref(inj), self._raw_ref(), self._stream()))
+
+    def run(self, n_steps: int):
+        with torch.cuda.device(self.device):
+            capi.check(self.h, self.lib.irs_run(self.h, int(n_steps), self._stream()))
+
+    def step_host(self, a0_host, intra_host, surface):
+        """irs_step_host: host actions in, host surface out (synchronous)."""
+        act = capi.Actions(a0_host.data_ptr() if a0_host is not None else None,
+                           intra_host.data_ptr() if intra_host is not None else None)
+        with torch.cuda.device(self.device):
+            capi.check(self.h, self.lib.irs_step_host(self.h, C.byref(act), C.byref(surface), self._stream()))
+
+    def reset_host(self, initial_episode, surface):
+        with torch.cuda.device(self.device):
+            capi.check(self.h, self.lib.irs_reset_host(self.h, int(initial_episode), C.byref(surface), self._stream()))
+
+    def episode_metrics(self):
+        out = np.zeros(capi.NUM_METRICS)
+        with torch.cuda.device(self.device):
+            capi.check(self.h, self.lib.irs_episode_metrics(self.h, out.ctypes.data, self._stream()))
+        return out
+
+    def check_errors(self):
+        first, code = C.c_int32(-1), C.c_int32(0)
+        with torch.cuda.device(self.device):
+            rc = self.lib.irs_check_errors(self.h, C.byref(first), C.byref(code), self._stream())
+        if rc == capi.IRS_ERR_ENV:
+            return first.value, code.value
+        capi.check(self.h, rc)
+        return None
+
+    def surface(self):
+        """The env surface tensors (device views into the state blob)."""
+        v = self.v
+        return {"obs0": v["out_obs0"], "obs_i": v["out_obsi"], "mask0": v["out_mask0"], "mask_i": v["out_maski"],
+                "reward": v["out_reward"], "done": v["out_done"], "sorted_slices": v["sorted"]}
+
+    def close(self):
+        if getattr(self, "h", None) is not None and self.h:
+            torch.cuda.synchronize(self.device)
+            self.lib.irs_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
