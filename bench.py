@@ -1,0 +1,348 @@
+#!/usr/bin/env python
+"""bench.py - UE-steps/s of the batched CommunicationEnv.step path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+                    [--envs E_per_gpu] [--depth D] [--workload mix|cfg2]
+
+One "step" = one env step (action->RB, arrivals, SE, throughput, buffers, obs, masks, reward,
+rollover) of every env of the batch.  Prints ONE JSON line (rank 0).  See DESIGN.md
+"Measurement" for the definitions of value / e2e / roofline / cpu_baseline.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+U = 25
+FIXED_ROW_BYTES = 96  # per streamed UE row besides the buffer: run, params, window ring, frame
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=200)
+    p.add_argument("--warmup", type=int, default=20)
+    p.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    p.add_argument("--envs", type=int, default=65536, help="env instances per GPU (weak scaling)")
+    p.add_argument("--depth", type=int, default=0, help="force every UE to a deep buffer profile (config 5 sweep)")
+    p.add_argument("--workload", default="mix", choices=["mix", "cfg2"])
+    p.add_argument("--cpu-envs", type=int, default=2048, help="env instances of the CPU baseline sample")
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-e2e", action="store_true")
+    return p.parse_args()
+
+
+def make_bank(depth: int):
+    from intent_radio_sched_multi_slice_b200 import scenario as scn
+
+    bank = scn.ScenarioBank()
+    st, us = scn.generate_scenarios(200, seed=10)
+    if depth <= 0:
+        for i in range(len(st)):
+            bank.add_typed(st[i], us[i])
+        return bank, "mult_slice scenario mix (200 scenarios, 10 slice types, D 21..401)"
+    # BASELINE config 5: every UE gets a deep profile derived from uav_app_case_1
+    for i in range(len(st)):
+        req = {}
+        sua = np.zeros((5, 25))
+        for s in range(5):
+            req[f"slice_{s}"] = scn.slice_req_from_type(5)
+            req[f"slice_{s}"]["ues"]["buffer_latency"] = depth - 1
+            req[f"slice_{s}"]["parameters"]["par1"]["value"] = depth // 2
+            sua[s, 5 * s:5 * s + 5] = 1
+        bank.add(req, sua)
+    return bank, f"scale sweep: 25 UEs x buffer depth {depth} (uav_app_case_1 profile)"
+
+
+def engine_kwargs(args, rank):
+    return dict(channel_mode=2, traffic_mode=1, sort_slices=1, fixed_intra=-1, policy=0, assoc_mode=0,
+                scen_mod=200, max_steps=1000, max_episodes=10000, auto_reset=1, seed=10,
+                env_id_base=rank * args.envs)
+
+
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if not self.proc:
+            return None
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], 0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for t, line in self.rows:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                mx = max(mx, int(f[1]))
+                if t0 - 0.05 <= t <= t1 + 0.15:
+                    sm.append(int(f[0]))
+                    reasons |= {n for n, v in zip(names, f[2:6]) if v.lower().startswith("active")}
+            except ValueError:
+                continue
+        if not sm:
+            sm = [int(x.split(",")[0]) for _, x in self.rows[-3:] if x.split(",")[0].strip().isdigit()]
+        return {"sm_mhz": int(np.median(sm)) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def cpu_oracle_run(args, bank, n_envs, warmup, steps=None, budget_s=12.0):
+    """The oracle port (oracle/irs_oracle.c, OpenMP over envs) on the host cores: same scenario
+    bank, generators, agent surface and action distribution as the GPU arm."""
+    from oracle import oracle
+
+    kw = engine_kwargs(args, 0)
+    kw["env_id_base"] = 0
+    cores = os.cpu_count() or 1
+    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    env = oracle.OracleEnv(bank.array(), bank.poisson_cdf(), n_envs,
+                           depth_cap=max(bank.max_depth(), 101), **kw)
+    rng = np.random.default_rng(1234)
+    pool = [(rng.uniform(-1, 1, (n_envs, 5)), rng.integers(0, 3, (n_envs, 5)).astype(np.int32)) for _ in range(4)]
+    m = np.ones(n_envs, np.uint8)
+    for e0 in range(200):  # stagger the scenarios like the GPU arm: env e starts at episode e % 200
+        m[:] = (np.arange(n_envs) % 200) == e0
+        if m.any():
+            env.reset(mask=m, initial_episode=e0)
+    for k in range(warmup):
+        env.step(*pool[k % 4])
+    if steps is None:
+        t = time.perf_counter()
+        for k in range(3):
+            env.step(*pool[k % 4])
+        per = (time.perf_counter() - t) / 3
+        steps = int(max(5, min(2000, budget_s / max(per, 1e-6))))
+    t = time.perf_counter()
+    for k in range(steps):
+        env.step(*pool[k % 4])
+    dt = time.perf_counter() - t
+    env.close()
+    return {"value": n_envs * U * steps / dt, "unit": "UE-steps/s", "cores": cores, "kind": "port",
+            "sample": f"{n_envs} envs x {steps} steps of the same workload, oracle/irs_oracle.c with OpenMP on {cores} threads",
+            "seconds": dt, "ms_per_step": dt / steps * 1e3, "steps": steps}
+
+
+def run_reference(args):
+    """--impl reference: the reference is pure Python and is not present on the GPU box
+    (/root/reference does not travel), so its CPU implementation of the path is timed as the C
+    restatement that tests/ pin against it (kind "port"), on all host threads."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    bank, wl = make_bank(args.depth)
+    n_envs = args.cpu_envs
+    r = cpu_oracle_run(args, bank, n_envs, args.warmup, steps=args.steps)
+    line = {
+        "impl": "reference", "metric": "UE-steps/sec (env-steps/sec x UEs)", "value": r["value"], "unit": "UE-steps/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64+i32", "data": "synthetic",
+        "config": {"workload": wl, "envs_per_step": n_envs, "ues": U, "surface": "IBSched dict obs + masks + 6 rewards",
+                   "note": "bounded CPU sample of the GPU arm's workload; per-env cost is independent of batch size"},
+        "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "e2e": {"value": r["value"], "unit": "UE-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    from intent_radio_sched_multi_slice_b200 import capi
+    from intent_radio_sched_multi_slice_b200.engine import BatchEngine
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    if args.workload == "cfg2":
+        args.envs = 1024
+    E, K, Wm = args.envs, args.steps, max(args.warmup, 3)
+    bank, wl = make_bank(args.depth)
+    eng = BatchEngine(bank, E, device=dev, depth_cap=max(bank.max_depth(), 101), **engine_kwargs(args, rank))
+    gid = torch.arange(E, device=dev, dtype=torch.int32) + rank * E
+    eng.reset(initial_episodes=(gid % 200).to(torch.int32), initial_episode=0)
+    g = torch.Generator(device=dev)
+    g.manual_seed(1234 + rank)
+    pool = [(torch.rand(E, 5, generator=g, device=dev, dtype=torch.float64) * 2 - 1,
+             torch.randint(0, 3, (E, 5), generator=g, device=dev, dtype=torch.int32)) for _ in range(4)]
+    state_bytes = eng.layout.total_bytes
+    flush = None
+    if state_bytes < 2 * 126e6:  # state fits L2: flush it between timed steps (config 2)
+        flush = torch.empty(int(256e6), dtype=torch.uint8, device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    for k in range(Wm):
+        eng.step(*pool[k % 4])
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    time.sleep(0.25)
+
+    # ---- value: K steps, inputs resident in HBM, CUDA events on the launching stream ----------
+    t0 = time.time()
+    if flush is None:
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        for k in range(K):
+            eng.step(*pool[k % 4])
+        ev1.record()
+        barrier()
+        ms_total = ev0.elapsed_time(ev1)
+    else:
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+        for k in range(K):
+            flush.fill_(k & 255)
+            evs[k][0].record()
+            eng.step(*pool[k % 4])
+            evs[k][1].record()
+        barrier()
+        ms_total = sum(a.elapsed_time(b) for a, b in evs)
+    t1 = time.time()
+    clocks = sampler.stop(t0, t1)
+
+    # ---- roofline of the dominant kernel (k_ue_step): per-kernel CUDA events, live ----------
+    depth_tab = np.zeros(len(bank.rows))
+    arr = bank.array()
+    for i in range(len(arr)):
+        for s in range(5):
+            n = int(arr["sl"]["n_ues"][i, s])
+            if n:
+                depth_tab[i] += n * (8 * (int(arr["sl"]["buffer_latency"][i, s]) + 1) + FIXED_ROW_BYTES)
+    depth_tab_t = torch.from_numpy(depth_tab).to(dev)
+    P = max(3, min(K, 20))
+    kms = np.zeros(3)
+    ue_bytes = 0.0
+    for k in range(P):
+        if flush is not None:
+            flush.fill_(k & 255)
+        ue_bytes += float(depth_tab_t[eng.v["scen"].long()].sum().item())
+        kms += np.array(eng.step_profiled(*pool[k % 4]))
+    kms /= P
+    ue_bytes /= P
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    achieved = ue_bytes / (kms[1] * 1e-3) / 1e9
+    traffic = None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "ue_step_traffic.json")))
+        if tj.get("envs") == E and tj.get("depth", 0) == args.depth:
+            traffic = tj["dram_bytes_per_launch"]
+    except Exception:
+        pass
+    roofline = {"bound": "hbm", "kernel": "k_ue_step", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": traffic,
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650 GB/s",
+                "algorithmic_bytes_per_launch": ue_bytes, "kernel_ms": kms[1],
+                "kernel_ms_all": {"k_action": kms[0], "k_ue_step": kms[1], "k_env_tail": kms[2]},
+                "bytes_per_ue_row": "8*D_u + %d for associated UEs, 0 for unassociated" % FIXED_ROW_BYTES}
+
+    # ---- e2e: host actions in, host surface out, through irs_step_host ------------------------
+    e2e = None
+    if not args.no_e2e:
+        Ke = max(3, min(K, 30))
+        pin = lambda *s, dt: torch.empty(*s, dtype=dt).pin_memory()
+        h_pool = [(a.cpu().pin_memory(), b.cpu().pin_memory()) for a, b in pool]
+        hs = {"obs0": pin(E, 50, dt=torch.float64), "obsi": pin(E, 5, 19, dt=torch.float64),
+              "mask0": pin(E, 5, dt=torch.int8), "maski": pin(E, 5, 5, dt=torch.int8),
+              "reward": pin(E, 6, dt=torch.float64), "done": pin(E, dt=torch.uint8)}
+        surf = capi.HostSurface(*[hs[n].data_ptr() for n in capi.SURFACE_FIELDS])
+        h2d = sum(a.numel() * a.element_size() + b.numel() * b.element_size() for a, b in h_pool[:1])
+        d2h = sum(t.numel() * t.element_size() for t in hs.values())
+        for k in range(3):
+            eng.step_host(h_pool[k % 4][0], h_pool[k % 4][1], surf)
+        barrier()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        tw = time.perf_counter()
+        for k in range(Ke):
+            eng.step_host(h_pool[k % 4][0], h_pool[k % 4][1], surf)
+        ev1.record()
+        barrier()
+        ms_e2e = max(ev0.elapsed_time(ev1), (time.perf_counter() - tw) * 1e3)
+        if world > 1:
+            t = torch.tensor([ms_e2e], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms_e2e = float(t.item())
+        e2e = {"value": world * E * U * Ke / (ms_e2e * 1e-3), "unit": "UE-steps/s", "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": d2h, "steps": Ke, "ms_per_step": ms_e2e / Ke,
+               "api": "irs_step_host (pinned host actions in, obs/masks/rewards/done out, stream drained)"}
+
+    if world > 1:
+        t = torch.tensor([ms_total], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    err = eng.check_errors()
+    active = float((torch.from_numpy((arr["ue_slice"][:, :25] >= 0).sum(1)).to(dev)[eng.v["scen"].long()]).double().mean().item())
+    metrics = eng.episode_metrics()
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_oracle_run(args, bank, args.cpu_envs, warmup=5)
+        cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    if rank == 0:
+        value = world * E * U * K / (ms_total * 1e-3)
+        line = {
+            "metric": "UE-steps/sec (env-steps/sec x UEs)", "value": value, "unit": "UE-steps/s", "n_gpus": world,
+            "steps": K, "warmup": Wm, "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "i32 buffers + f64", "data": "synthetic",
+            "config": {"workload": wl, "envs_per_gpu": E, "ues_per_env": U, "active_ues_per_env": active,
+                       "surface": "IBSched dict obs + action masks + 6 rewards, random actions supplied on device",
+                       "channel": "native mimic_quadriga", "traffic": "native Poisson",
+                       "state_bytes_per_gpu": state_bytes,
+                       "l2": "state larger than L2" if flush is None else "L2 flushed (256 MB fill) between timed steps"},
+            "e2e": e2e, "roofline": roofline, "cpu_baseline": cpu, "gpu_launches": 3 * K, "clocks": clocks,
+            "env_errors": err, "episode_metrics": dict(zip(capi.METRIC_NAMES, metrics.tolist())),
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

@@ -180,6 +180,11 @@ int irs_reset(irs_env* env, const uint8_t* mask_dev, int32_t initial_episode,
 /* CommunicationEnv.step (comm_env.py:271-373) for every env of the batch. */
 int irs_step(irs_env* env, const irs_actions* actions_dev, const irs_inject* inject_dev,
              const irs_raw_outputs* raw_dev, void* stream);
+/* irs_step with CUDA events recorded around each of its kernels; waits for the step and returns
+ * their durations in ms: [0] action->RB, [1] per-UE row kernel, [2] obs/reward/rollover.
+ * Measurement aid for bench.py (roofline of the dominant kernel); not graph capturable. */
+int irs_step_profiled(irs_env* env, const irs_actions* actions_dev, const irs_inject* inject_dev,
+                      const irs_raw_outputs* raw_dev, void* stream, float* kernel_ms_host);
 /* n steps back to back with the on-device policy (cfg.policy != 0) and native generators. */
 int irs_run(irs_env* env, int32_t n_steps, void* stream);
 /* Same as irs_step but actions come from host memory and the env surface is copied back to

@@ -18,6 +18,8 @@ struct irs_env {
     bool bound, loaded;
     DevState st;
     char* blob;
+    cudaEvent_t ev[4];
+    bool have_ev;
     char err[256];
 };
 
@@ -105,6 +107,8 @@ int irs_create(const irs_config* cfg, int32_t n_lambda, irs_env** out)
 
 int irs_destroy(irs_env* env)
 {
+    if (env && env->have_ev)
+        for (int i = 0; i < 4; ++i) cudaEventDestroy(env->ev[i]);
     delete env;
     return IRS_OK;
 }
@@ -211,29 +215,59 @@ int irs_reset(irs_env* env, const uint8_t* mask_dev, int32_t initial_episode, co
     return IRS_OK;
 }
 
-static int launch_step(irs_env* env, const StepArgs& A, cudaStream_t st)
+static int launch_step(irs_env* env, const StepArgs& A, cudaStream_t st, bool profile = false)
 {
     const int E = env->cfg.num_envs;
+    if (profile) CK(cudaEventRecord(env->ev[0], st));
     k_action<<<(E + 7) / 8, 256, 0, st>>>(A);
+    if (profile) CK(cudaEventRecord(env->ev[1], st));
     const long long rows = (long long)E * U;
     k_ue_step<<<(unsigned)((rows + UE_WARPS - 1) / UE_WARPS), UE_WARPS * 32, 0, st>>>(A);
+    if (profile) CK(cudaEventRecord(env->ev[2], st));
     k_env_tail<<<(E + ENV_WARPS - 1) / ENV_WARPS, ENV_WARPS * 32, 0, st>>>(A);
+    if (profile) CK(cudaEventRecord(env->ev[3], st));
     CK(cudaGetLastError());
     return IRS_OK;
 }
 
-int irs_step(irs_env* env, const irs_actions* actions, const irs_inject* inject, const irs_raw_outputs* raw, void* stream)
+static int step_args(irs_env* env, const irs_actions* actions, const irs_inject* inject, const irs_raw_outputs* raw, StepArgs* A)
 {
     int rc = check_ready(env, inject);
     if (rc) return rc;
     if (env->cfg.policy == 0 && !(actions && actions->a0)) return fail(env, IRS_ERR_ARG, "policy 0 needs actions.a0");
     if (env->cfg.policy == 0 && env->cfg.fixed_intra < 0 && !actions->intra) return fail(env, IRS_ERR_ARG, "fixed_intra -1 needs actions.intra");
     if (env->cfg.traffic_mode == 0 && !(inject && inject->traffic)) return fail(env, IRS_ERR_ARG, "traffic_mode 0 needs inject.traffic");
-    StepArgs A = make_args(env);
-    if (actions) { A.a0 = actions->a0; A.intra = actions->intra; }
-    if (inject) { A.se = inject->se; A.traffic = inject->traffic; }
-    if (raw) A.raw = *raw;
+    *A = make_args(env);
+    if (actions) { A->a0 = actions->a0; A->intra = actions->intra; }
+    if (inject) { A->se = inject->se; A->traffic = inject->traffic; }
+    if (raw) A->raw = *raw;
+    return IRS_OK;
+}
+
+int irs_step(irs_env* env, const irs_actions* actions, const irs_inject* inject, const irs_raw_outputs* raw, void* stream)
+{
+    StepArgs A;
+    int rc = step_args(env, actions, inject, raw, &A);
+    if (rc) return rc;
     return launch_step(env, A, (cudaStream_t)stream);
+}
+
+int irs_step_profiled(irs_env* env, const irs_actions* actions, const irs_inject* inject, const irs_raw_outputs* raw,
+                      void* stream, float* kernel_ms_host)
+{
+    StepArgs A;
+    int rc = step_args(env, actions, inject, raw, &A);
+    if (rc) return rc;
+    if (!kernel_ms_host) return IRS_ERR_ARG;
+    if (!env->have_ev) {
+        for (int i = 0; i < 4; ++i) CK(cudaEventCreate(&env->ev[i]));
+        env->have_ev = true;
+    }
+    rc = launch_step(env, A, (cudaStream_t)stream, true);
+    if (rc) return rc;
+    CK(cudaEventSynchronize(env->ev[3]));
+    for (int i = 0; i < 3; ++i) CK(cudaEventElapsedTime(&kernel_ms_host[i], env->ev[i], env->ev[i + 1]));
+    return IRS_OK;
 }
 
 int irs_run(irs_env* env, int32_t n_steps, void* stream)

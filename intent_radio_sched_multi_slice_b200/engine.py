@@ -140,6 +140,19 @@ class BatchEngine:
         with torch.cuda.device(self.device):
             capi.check(self.h, self.lib.irs_step(self.h, C.byref(act), C.byref(inj), self._raw_ref(), self._stream()))
 
+    def step_profiled(self, a0=None, intra=None, se=None, traffic=None):
+        """One step with CUDA events around each kernel; returns their durations in ms
+        (action->RB, per-UE rows, obs/reward/rollover).  Synchronous; for measurement."""
+        a0_t, in_t = self._dev(a0, torch.float64), self._dev(intra, torch.int32)
+        se_t, tr_t = self._dev(se, torch.float64), self._dev(traffic, torch.float64)
+        act = capi.Actions(a0_t.data_ptr() if a0_t is not None else None, in_t.data_ptr() if in_t is not None else None)
+        inj = capi.Inject(se_t.data_ptr() if se_t is not None else None, tr_t.data_ptr() if tr_t is not None else None)
+        ms = (C.c_float * 3)()
+        with torch.cuda.device(self.device):
+            capi.check(self.h, self.lib.irs_step_profiled(self.h, C.byref(act), C.byref(inj), self._raw_ref(),
+                                                          self._stream(), ms))
+        return [float(x) for x in ms]
+
     def run(self, n_steps: int):
         with torch.cuda.device(self.device):
             capi.check(self.h, self.lib.irs_run(self.h, int(n_steps), self._stream()))
