@@ -24,7 +24,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 U = 25
-FIXED_ROW_BYTES = 96  # per streamed UE row besides the buffer: run, params, window ring, frame
+FIXED_ROW_BYTES = 124  # per UE row besides the buffer: int/f64 records R+W, ring slot R+W, RB run
 
 
 def parse():
@@ -239,24 +239,32 @@ def run_b200(args):
     clocks = sampler.stop(t0, t1)
 
     # ---- roofline of the dominant kernel (k_ue_step): per-kernel CUDA events, live ----------
-    depth_tab = np.zeros(len(bank.rows))
     arr = bank.array()
+    depth_tab = np.full((len(arr), U), 101, np.int64)  # buffer depth of every (scenario, UE) row
     for i in range(len(arr)):
-        for s in range(5):
-            n = int(arr["sl"]["n_ues"][i, s])
-            if n:
-                depth_tab[i] += n * (8 * (int(arr["sl"]["buffer_latency"][i, s]) + 1) + FIXED_ROW_BYTES)
+        for u in range(U):
+            s_ = int(arr["ue_slice"][i, u])
+            if s_ >= 0:
+                depth_tab[i, u] = int(arr["sl"]["buffer_latency"][i, s_]) + 1
     depth_tab_t = torch.from_numpy(depth_tab).to(dev)
     P = max(3, min(K, 20))
     kms = np.zeros(3)
     ue_bytes = 0.0
+    path_frac = np.zeros(3)
     for k in range(P):
         if flush is not None:
             flush.fill_(k & 255)
-        ue_bytes += float(depth_tab_t[eng.v["scen"].long()].sum().item())
         kms += np.array(eng.step_profiled(*pool[k % 4]))
+        # bytes the row kernel had to move in THIS launch: per-UE records for every row, plus the
+        # buffer row by the path the kernel took (DESIGN.md "Algorithmic bytes")
+        path = eng.v["path"].long()
+        dep = depth_tab_t[eng.v["scen"].long()]
+        row_b = torch.where(path == 2, 8 * dep, torch.where(path == 1, 4 * dep, torch.full_like(dep, 4)))
+        ue_bytes += float((row_b + FIXED_ROW_BYTES).sum().item())
+        path_frac += np.array([(path == i).float().mean().item() for i in range(3)])
     kms /= P
     ue_bytes /= P
+    path_frac /= P
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -276,7 +284,8 @@ def run_b200(args):
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650 GB/s",
                 "algorithmic_bytes_per_launch": ue_bytes, "kernel_ms": kms[1],
                 "kernel_ms_all": {"k_action": kms[0], "k_ue_step": kms[1], "k_env_tail": kms[2]},
-                "bytes_per_ue_row": "8*D_u + %d for associated UEs, 0 for unassociated" % FIXED_ROW_BYTES}
+                "bytes_per_ue_row": "%d (per-UE records) + buffer row: 8*D_u streamed, 4*D_u zero-filled, 4 empty" % FIXED_ROW_BYTES,
+                "row_paths": {"empty": path_frac[0], "zero_fill": path_frac[1], "stream": path_frac[2]}}
 
     # ---- e2e: host actions in, host surface out, through irs_step_host ------------------------
     e2e = None

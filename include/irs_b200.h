@@ -95,16 +95,15 @@ typedef struct {
     int32_t row_stride;      /* ints per buffer row: depth_cap rounded up to 4 */
     int32_t reserved;
     size_t buf;              /* i32 [E][25][row_stride]  age histograms (buffer.py:47) */
-    size_t occ, lat, sebar;  /* f64 [E][25]  newest window frame (win[0]) */
-    size_t tot;              /* i32 [E][25]  packets in buffer */
-    size_t sum_sent, sum_drop;   /* i32 [E][25] window sums (<=10 frames) */
-    size_t last_sent, last_drop, last_inc; /* i32 [E][25] newest frame */
-    size_t ring_sent, ring_drop; /* i32 [E][10][25] */
-    size_t thr;              /* f64 [E][25] pkt_throughputs of the newest frame */
-    size_t occ1z;            /* u8  [E][32] isclose(win[1].occ, 0) */
-    size_t rb_start, rb_count;   /* i16 [E][32] contiguous RB run of each UE */
+    size_t ue_i;             /* i32 [E][25][8]  per-UE record: packets in buffer, window sums of
+                                sent / dropped, newest frame's sent / dropped / incoming,
+                                isclose(win[1].occ, 0), row path taken (0 empty, 1 zero-fill, 2 stream) */
+    size_t ue_d;             /* f64 [E][25][4]  newest window frame: occupancy, mean delay, mean SE,
+                                pkt_throughputs */
+    size_t ring;             /* i32 [E][25][10][2] (sent, dropped) of the last 10 frames */
+    size_t rb;               /* i16 [E][25][2] (rb_start, rb_count): contiguous RB run of each UE */
     size_t step, episode, scen, win_len, win_head, err; /* i32 [E] */
-    size_t sorted;           /* i8  [E][8] IBSched.sorted_slices */
+    size_t sorted;           /* i8  [E][5] IBSched.sorted_slices */
     size_t acc;              /* f64 [E][16] episode-metric accumulators */
     size_t bank;             /* irs_scenario [n_scen] */
     size_t cdf;              /* f64 [n_lambda][256] Poisson CDF tables */

@@ -30,11 +30,12 @@ class Config(C.Structure):
 
 
 _LAYOUT_ARRAYS = [
-    "buf", "occ", "lat", "sebar", "tot", "sum_sent", "sum_drop", "last_sent", "last_drop", "last_inc",
-    "ring_sent", "ring_drop", "thr", "occ1z", "rb_start", "rb_count", "step", "episode", "scen", "win_len",
+    "buf", "ue_i", "ue_d", "ring", "rb", "step", "episode", "scen", "win_len",
     "win_head", "err", "sorted", "acc", "bank", "cdf", "in_a0", "in_intra", "out_obs0", "out_obsi",
     "out_mask0", "out_maski", "out_reward", "out_done", "metrics_total",
 ]
+UI_FIELDS = ["tot", "sum_sent", "sum_drop", "last_sent", "last_drop", "last_inc", "occ1z", "path"]
+UD_FIELDS = ["occ", "lat", "sebar", "thr"]
 
 
 class Layout(C.Structure):

@@ -106,9 +106,9 @@ __device__ __forceinline__ void action_to_rb_warp(const StepArgs& A, int e)
     for (int s = 0; s < S; ++s) { active[s] = (__ldg(&sc->sl[s].flags) & IRS_F_ACTIVE) != 0; nact += active[s]; }
 
     const size_t eu = (size_t)e * U + (lane < U ? lane : 0);
-    const double occ = st.occ[eu];
-    const double sebar = st.sebar[eu];
-    const int sum_sent = st.sum_sent[eu];
+    const double occ = st.ue_d[eu * UD_N + UD_OCC];
+    const double sebar = st.ue_d[eu * UD_N + UD_SEBAR];
+    const int sum_sent = st.ue_i[eu * UI_N + UI_SUM_SENT];
     const int win_len = st.win_len[e];
     const UeParams up = ue_params(sc, s_mine);
 
@@ -233,8 +233,7 @@ __device__ __forceinline__ void action_to_rb_warp(const StepArgs& A, int e)
         if (lane == 0 && total != expect) atomicOr(&st.err[e], ERR_RB_SUM);
     }
     if (lane < U) {
-        st.rb_start[eu] = (int16_t)start;
-        st.rb_count[eu] = (int16_t)count;
+        st.rb[eu] = make_short2((short)start, (short)count);
         if (A.raw.rb_start) A.raw.rb_start[eu] = (int16_t)start;
         if (A.raw.rb_count) A.raw.rb_count[eu] = (int16_t)count;
     }

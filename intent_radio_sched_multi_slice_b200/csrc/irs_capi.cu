@@ -33,14 +33,10 @@ static void compute_layout(const irs_config& c, int32_t n_lambda, irs_layout* L)
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
     L->buf = take(E * U * L->row_stride * 4);
-    L->occ = take(E * U * 8); L->lat = take(E * U * 8); L->sebar = take(E * U * 8);
-    L->tot = take(E * U * 4);
-    L->sum_sent = take(E * U * 4); L->sum_drop = take(E * U * 4);
-    L->last_sent = take(E * U * 4); L->last_drop = take(E * U * 4); L->last_inc = take(E * U * 4);
-    L->ring_sent = take(E * W * U * 4); L->ring_drop = take(E * W * U * 4);
-    L->thr = take(E * U * 8);
-    L->occ1z = take(E * U);
-    L->rb_start = take(E * U * 2); L->rb_count = take(E * U * 2);
+    L->ue_i = take(E * U * UI_N * 4);
+    L->ue_d = take(E * U * UD_N * 8);
+    L->ring = take(E * U * W * 8);
+    L->rb = take(E * U * 4);
     L->step = take(E * 4); L->episode = take(E * 4); L->scen = take(E * 4);
     L->win_len = take(E * 4); L->win_head = take(E * 4); L->err = take(E * 4);
     L->sorted = take(E * S);
@@ -76,6 +72,7 @@ static StepArgs make_args(const irs_env* env)
     memset(&A, 0, sizeof(A));
     A.st = env->st;
     A.cfg = env->cfg;
+    A.bw_rb = env->cfg.bandwidth / (double)R; // ues.py:110
     A.initial_episode = -1;
     return A;
 }
@@ -93,7 +90,7 @@ int irs_create(const irs_config* cfg, int32_t n_lambda, irs_env** out)
         cfg->policy < 0 || cfg->policy > 3 || cfg->fixed_intra < -1 || cfg->fixed_intra > 2 ||
         (cfg->assoc_mode == 0 && cfg->scen_mod <= 0) || (cfg->assoc_mode == 1 && cfg->scen_div <= 0) ||
         cfg->assoc_mode < 0 || cfg->assoc_mode > 1 || !(cfg->bandwidth > 0) ||
-        (cfg->traffic_mode == 1 && n_lambda <= 0))
+        (cfg->traffic_mode == 1 && n_lambda <= 0) || (long long)cfg->num_envs * U >= (1ll << 31))
         return IRS_ERR_ARG;
     irs_env* env = new (std::nothrow) irs_env;
     if (!env) return IRS_ERR_ARG;
@@ -132,15 +129,10 @@ int irs_bind(irs_env* env, void* state_dev, size_t bytes, void* stream)
     DevState& s = env->st;
     env->blob = b;
     s.buf = (int32_t*)(b + L.buf);
-    s.occ = (double*)(b + L.occ); s.lat = (double*)(b + L.lat); s.sebar = (double*)(b + L.sebar);
-    s.thr = (double*)(b + L.thr);
-    s.tot = (int32_t*)(b + L.tot);
-    s.sum_sent = (int32_t*)(b + L.sum_sent); s.sum_drop = (int32_t*)(b + L.sum_drop);
-    s.last_sent = (int32_t*)(b + L.last_sent); s.last_drop = (int32_t*)(b + L.last_drop);
-    s.last_inc = (int32_t*)(b + L.last_inc);
-    s.ring_sent = (int32_t*)(b + L.ring_sent); s.ring_drop = (int32_t*)(b + L.ring_drop);
-    s.occ1z = (uint8_t*)(b + L.occ1z);
-    s.rb_start = (int16_t*)(b + L.rb_start); s.rb_count = (int16_t*)(b + L.rb_count);
+    s.ue_i = (int32_t*)(b + L.ue_i);
+    s.ue_d = (double*)(b + L.ue_d);
+    s.ring = (int2*)(b + L.ring);
+    s.rb = (short2*)(b + L.rb);
     s.step = (int32_t*)(b + L.step); s.episode = (int32_t*)(b + L.episode); s.scen = (int32_t*)(b + L.scen);
     s.win_len = (int32_t*)(b + L.win_len); s.win_head = (int32_t*)(b + L.win_head); s.err = (int32_t*)(b + L.err);
     s.sorted = (int8_t*)(b + L.sorted);

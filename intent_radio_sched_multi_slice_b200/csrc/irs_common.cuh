@@ -19,13 +19,21 @@
 
 enum { ERR_INTRA_ACTION = 1, ERR_EPISODE_RANGE = 2, ERR_RB_SUM = 4 };
 
+// Per-UE state is kept as small records so that one warp-wide access moves a whole record:
+//   ue_i[E][25][8]  int32: the fields below (UI_*)
+//   ue_d[E][25][4]  f64  : newest window frame (UD_*)
+//   ring[E][25][10] int2 : (sent, dropped) of the last 10 frames (agents/ib_sched.py:49-51)
+//   rb[E][25]       short2: (rb_start, rb_count) contiguous RB run of the UE
+enum { UI_TOT = 0, UI_SUM_SENT, UI_SUM_DROP, UI_SENT, UI_DROP, UI_INC, UI_OCC1Z, UI_PATH, UI_N };
+enum { UD_OCC = 0, UD_LAT, UD_SEBAR, UD_THR, UD_N };
+
 // Pointers into the caller-owned state blob (see irs_layout).
 struct DevState {
     int32_t* buf;
-    double *occ, *lat, *sebar, *thr;
-    int32_t *tot, *sum_sent, *sum_drop, *last_sent, *last_drop, *last_inc, *ring_sent, *ring_drop;
-    uint8_t* occ1z;
-    int16_t *rb_start, *rb_count;
+    int32_t* ue_i;
+    double* ue_d;
+    int2* ring;
+    short2* rb;
     int32_t *step, *episode, *scen, *win_len, *win_head, *err;
     int8_t* sorted;
     double* acc;
@@ -43,6 +51,7 @@ struct DevState {
 struct StepArgs {
     DevState st;
     irs_config cfg;
+    double bw_rb;          // cfg.bandwidth / 135 (ues.py:110), rounded once on the host
     const double* a0;      // actions (device) or NULL
     const int32_t* intra;  // or NULL
     const double* se;      // injected SE or NULL
@@ -195,6 +204,34 @@ __device__ __forceinline__ double np_sum135_pair(const double* rowA, const doubl
     }
     const double other = __shfl_down_sync(FULL, r, 8);
     return 0. + (r + other); // valid in lanes 0 and 16
+}
+
+// Same reduction order, both sums of one SE row at once: lanes 0..15 sum the throughput
+// terms ((BW/R) * sched[r]) * SE[r] (ues.py:108-116; sched is 1 inside the UE's RB run, else
+// 0), lanes 16..31 sum SE[r] itself.  Results valid in lanes 0 and 16.
+__device__ __forceinline__ double np_sum135_thr_se(const double* se, int rb_s, int rb_e, double bw_rb)
+{
+    const int lane = lane_id();
+    const int j = lane & 7;
+    const int base = ((lane >> 3) & 1) * 64 + j;
+    const bool terms = lane < 16;
+    auto elem = [&](int r) -> double {
+        const double x = se[r];
+        const double sched = (r >= rb_s && r < rb_e) ? 1.0 : 0.0;
+        return terms ? (bw_rb * sched) * x : x;
+    };
+    double r = elem(base);
+#pragma unroll
+    for (int k = 1; k < 8; ++k) r += elem(base + 8 * k);
+    r = r + __shfl_down_sync(FULL, r, 1);
+    r = r + __shfl_down_sync(FULL, r, 2);
+    r = r + __shfl_down_sync(FULL, r, 4);
+    if ((lane & 15) == 8) {
+#pragma unroll
+        for (int k = 0; k < 7; ++k) r += elem(128 + k);
+    }
+    const double other = __shfl_down_sync(FULL, r, 8);
+    return 0. + (r + other);
 }
 
 __device__ __forceinline__ int scen_of_episode(const irs_config& c, int episode)

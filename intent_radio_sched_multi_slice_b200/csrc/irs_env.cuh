@@ -54,19 +54,17 @@ __device__ __forceinline__ void reset_env_warp(const StepArgs& A, int e, int ini
     f.sum_sent = 0; f.sum_drop = 0; f.occ1z = false;
     if (lane < U) {
         const size_t eu = (size_t)e * U + lane;
-        const size_t ri = ((size_t)e * W + p) * U + lane;
-        int ss = st.sum_sent[eu], sd = st.sum_drop[eu];
-        if (win_len == W) { ss -= st.ring_sent[ri]; sd -= st.ring_drop[ri]; }
-        st.ring_sent[ri] = 0;
-        st.ring_drop[ri] = 0;
-        st.sum_sent[eu] = ss;
-        st.sum_drop[eu] = sd;
+        int* ui = st.ue_i + eu * UI_N;
+        double* ud = st.ue_d + eu * UD_N;
+        int ss = ui[UI_SUM_SENT], sd = ui[UI_SUM_DROP];
+        if (win_len == W) { const int2 ev = st.ring[eu * W + p]; ss -= ev.x; sd -= ev.y; }
+        st.ring[eu * W + p] = make_int2(0, 0);
         f.sum_sent = ss; f.sum_drop = sd;
-        f.occ1z = isclose0(st.occ[eu]);
-        st.occ1z[eu] = f.occ1z ? 1 : 0;
-        st.occ[eu] = 0; st.lat[eu] = 0; st.sebar[eu] = sebar; st.thr[eu] = 0;
-        st.tot[eu] = 0; st.last_sent[eu] = 0; st.last_drop[eu] = 0; st.last_inc[eu] = 0;
-        st.rb_start[eu] = 0; st.rb_count[eu] = 0;
+        f.occ1z = isclose0(ud[UD_OCC]);
+        ui[UI_TOT] = 0; ui[UI_SUM_SENT] = ss; ui[UI_SUM_DROP] = sd; ui[UI_SENT] = 0; ui[UI_DROP] = 0;
+        ui[UI_INC] = 0; ui[UI_OCC1Z] = f.occ1z ? 1 : 0; ui[UI_PATH] = 0;
+        ud[UD_OCC] = 0; ud[UD_LAT] = 0; ud[UD_SEBAR] = sebar; ud[UD_THR] = 0;
+        st.rb[eu] = make_short2(0, 0);
     }
     const int win_len_new = win_len < W ? win_len + 1 : W;
     __syncwarp();
@@ -81,11 +79,13 @@ __device__ __forceinline__ void env_tail_warp(const StepArgs& A, int e, double* 
     const irs_config& c = A.cfg;
     const int lane = lane_id();
     const size_t eu = (size_t)e * U + (lane < U ? lane : 0);
+    const int* ui = st.ue_i + eu * UI_N;
+    const double* ud = st.ue_d + eu * UD_N;
     UeFrame f;
-    f.occ = st.occ[eu]; f.lat = st.lat[eu]; f.sebar = st.sebar[eu];
-    f.sent = st.last_sent[eu]; f.sum_sent = st.sum_sent[eu]; f.sum_drop = st.sum_drop[eu];
-    f.rb_count = st.rb_count[eu]; f.occ1z = st.occ1z[eu] != 0;
-    int dropped = st.last_drop[eu], inc = st.last_inc[eu];
+    f.occ = ud[UD_OCC]; f.lat = ud[UD_LAT]; f.sebar = ud[UD_SEBAR];
+    f.sent = ui[UI_SENT]; f.sum_sent = ui[UI_SUM_SENT]; f.sum_drop = ui[UI_SUM_DROP];
+    f.rb_count = st.rb[eu].y; f.occ1z = ui[UI_OCC1Z] != 0;
+    int dropped = ui[UI_DROP], inc = ui[UI_INC];
     if (lane >= U) { f.sent = 0; f.rb_count = 0; dropped = 0; inc = 0; }
     // the per-UE part of the window push was done by k_ue_step; finish the per-env part
     const int win_len_old = st.win_len[e];

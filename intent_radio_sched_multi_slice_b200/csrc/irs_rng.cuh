@@ -19,9 +19,8 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1
 {
 #pragma unroll
     for (int r = 0; r < 10; ++r) {
-        const uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
-        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
-        c = make_uint4(hi1 ^ c.y ^ k0, lo1, hi0 ^ c.w ^ k1, lo0);
+        const uint64_t p0 = (uint64_t)0xD2511F53u * c.x, p1 = (uint64_t)0xCD9E8D57u * c.z;
+        c = make_uint4((uint32_t)(p1 >> 32) ^ c.y ^ k0, (uint32_t)p1, (uint32_t)(p0 >> 32) ^ c.w ^ k1, (uint32_t)p0);
         k0 += 0x9E3779B9u;
         k1 += 0xBB67AE85u;
     }
@@ -114,4 +113,45 @@ __device__ __forceinline__ double native_traffic(uint64_t seed, const double* cd
         if (__ldg(&cdf[mid]) <= u) lo = mid + 1; else hi = mid;
     }
     return (double)lo * 1e6;
+}
+
+// One UE row of a step in native mode, by the whole warp, in two generator passes:
+//   pass A  lane 0,1: SE quads 32,33 (RBs 128..134); lane 2: the UE's per-episode mean;
+//           lane 3: the Poisson arrival          (same counters and values as the functions above)
+//   pass B  lane l: SE quad l (RBs 4l..4l+3)
+// Returns the offered traffic in bits (0 when the UE's slice has no requirements).
+__device__ __forceinline__ double native_row(uint64_t seed, const double* cdf_all, int ue, int lam_idx,
+                                             bool has_traffic, int frame, int episode, int gid, double* se)
+{
+    const int lane = lane_id();
+    const int kindA = lane == 2 ? K_MU : (lane == 3 ? K_TRAFFIC : K_SE);
+    const int qA = lane == 0 ? 32 : (lane == 1 ? 33 : 0);
+    const uint4 wa = rng_quad(seed, kindA, ue, qA, lane == 2 ? 0 : frame, episode, gid);
+    float z[4];
+    normal_pair(wa.x, wa.y, z[0], z[1]);
+    normal_pair(wa.z, wa.w, z[2], z[3]);
+    const double mu = __shfl_sync(FULL, fabs(__fma_rn(7.5, (double)z[0], 10.0)), 2);
+    if (lane < 2) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (4 * qA + j < R) se[4 * qA + j] = fabs(__fma_rn(1.5, (double)z[j], mu));
+    }
+    // Poisson by table inversion (lane 3's words; the other lanes run along)
+    const double u = ((double)(wa.x >> 5) * 67108864.0 + (double)(wa.y >> 6)) * (1.0 / 9007199254740992.0);
+    const double* cdf = cdf_all + (size_t)lam_idx * IRS_POISSON_K;
+    int lo = 0;
+    if (has_traffic) {
+#pragma unroll
+        for (int step = IRS_POISSON_K / 2; step > 0; step >>= 1) // branch-free upper bound
+            if (__ldg(&cdf[lo + step - 1]) <= u) lo += step;
+        if (__ldg(&cdf[lo]) <= u) lo += 1; // lo in [0, 256]
+    }
+    const double traffic = __shfl_sync(FULL, (double)lo * 1e6, 3);
+    const uint4 wb = rng_quad(seed, K_SE, ue, lane, frame, episode, gid);
+    normal_pair(wb.x, wb.y, z[0], z[1]);
+    normal_pair(wb.z, wb.w, z[2], z[3]);
+    double2* out = reinterpret_cast<double2*>(se + 4 * lane);
+    out[0] = make_double2(fabs(__fma_rn(1.5, (double)z[0], mu)), fabs(__fma_rn(1.5, (double)z[1], mu)));
+    out[1] = make_double2(fabs(__fma_rn(1.5, (double)z[2], mu)), fabs(__fma_rn(1.5, (double)z[3], mu)));
+    return traffic;
 }

@@ -10,35 +10,34 @@
 //   get_buffer_occupancy / get_avg_delay   buffer.py:106-130
 // and the per-UE part of the 10-frame observation window (agents/ib_sched.py:49-51,64).
 //
-// Buffer row = age histogram int32[depth]; index = age in steps.  The row is streamed once:
-// 128-bit loads, the one-slot age shift is done in registers (shuffle from the neighbouring
-// lane), the drain is a suffix scan from the oldest end, 128-bit stores to the same place.
-// Rows are walked from the old end in groups of 4 x 128 slots so that the in-place shift
-// never reads a slot it has already overwritten.
+// Buffer row = age histogram int32[depth]; index = age in steps.  Because the row's packet
+// count is kept as state, everything but the mean delay is known before the row is touched:
+//   * empty row            -> only slot 0 is written (4 bytes),
+//   * everything older than the new arrivals is sent -> the row is zero-filled (write only),
+//   * otherwise the row is streamed once: 128-bit loads, the one-slot age shift done in
+//     registers (shuffle from the neighbouring lane), the oldest-first drain as a suffix scan
+//     from the old end (skipped as soon as the scan has passed `thr` packets), 128-bit stores
+//     to the same place.  Rows are walked from the old end in groups of 4 x 128 slots so that
+//     the in-place shift never reads a slot it has already overwritten.
 #pragma once
 #include "irs_common.cuh"
 #include "irs_rng.cuh"
 
+
 #define UE_WARPS 8 /* warps (rows) per block */
 #define GC 4       /* 128-slot chunks per group */
 
-struct RowResult {
-    int sent, dropped, rem;
-    long long wsum;
-};
+enum { ROW_EMPTY = 0, ROW_ZERO_FILL = 1, ROW_STREAM = 2 };
 
-// The whole warp works on one row.  thr_i: packets that can be sent; inc: packets arriving.
-__device__ __forceinline__ RowResult buffer_row_step(int* __restrict__ row, int depth, int max_pkts, int thr_i,
-                                                     double inc)
+// General case: stream the row once.  `total` = packets in slots >= 1 after the shift,
+// `thr_i` = packets that may leave (thr_i < total here), `a_left` = what stays in slot 0.
+// Returns sum(age * packets left), reduced over the warp.
+__device__ __forceinline__ long long buffer_row_stream(int* __restrict__ row, int depth, int thr_i, int a_left)
 {
     const int lane = lane_id();
-    const int expired = row[depth - 1]; // buffer.py:60 dropped = buffer[-1]
     const int nch = (depth + 127) >> 7;
-    int sfx = 0;        // packets in slots older than the ones being processed (after the shift)
-    int rem = 0;        // packets left in this lane's slots
-    long long wsum = 0; // sum age * packets left
-    int arrived_kept = 0;
-    int4 first = make_int4(0, 0, 0, 0);
+    int sfx = 0;        // packets in slots older than the chunk being processed (warp-uniform)
+    long long wsum = 0; // sum age * packets left (this lane's slots)
     for (int g = (nch + GC - 1) / GC - 1; g >= 0; --g) {
         const int cb = g * GC;
         int4 v[GC];
@@ -53,62 +52,52 @@ __device__ __forceinline__ RowResult buffer_row_step(int* __restrict__ row, int 
             const int c0 = (cb + k) << 7;
             if (c0 >= depth) continue; // warp-uniform
             const int i0 = c0 + 4 * lane;
-            int pw = __shfl_up_sync(FULL, v[k].w, 1);
+            int n0 = __shfl_up_sync(FULL, v[k].w, 1);
             const int prev_last = (k > 0) ? __shfl_sync(FULL, v[k > 0 ? k - 1 : 0].w, 31) : carry_in;
-            if (lane == 0) pw = prev_last;
-            // shifted row: new[i] = old[i-1]; new[0] is filled in after the totals are known
-            int n0 = (i0 < depth && i0 != 0) ? pw : 0;
-            int n1 = (i0 + 1 < depth) ? v[k].x : 0;
-            int n2 = (i0 + 2 < depth) ? v[k].y : 0;
-            int n3 = (i0 + 3 < depth) ? v[k].z : 0;
-            const int t = n0 + n1 + n2 + n3;
-            int incl = t; // inclusive suffix sum over lanes (lane 31 holds the oldest slots)
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const int y = __shfl_down_sync(FULL, incl, d);
-                if (lane + d < 32) incl += y;
+            if (lane == 0) n0 = prev_last; // new[i] = old[i-1]
+            int n1 = v[k].x, n2 = v[k].y, n3 = v[k].z;
+            if (c0 + 128 > depth) { // tail chunk: nothing lives at index >= depth
+                n0 = (i0 < depth) ? n0 : 0;
+                n1 = (i0 + 1 < depth) ? n1 : 0;
+                n2 = (i0 + 2 < depth) ? n2 : 0;
+                n3 = (i0 + 3 < depth) ? n3 : 0;
             }
-            const int s3 = sfx + incl - t; // packets strictly older than slot i0+3
-            const int s2 = s3 + n3, s1 = s2 + n2, s0 = s1 + n1;
-            sfx += __shfl_sync(FULL, incl, 0);
-            // buffer.py:97-103: the oldest `thr` packets leave
-            n3 -= min(n3, max(0, thr_i - s3));
-            n2 -= min(n2, max(0, thr_i - s2));
-            n1 -= min(n1, max(0, thr_i - s1));
-            n0 -= min(n0, max(0, thr_i - s0));
-            rem += n0 + n1 + n2 + n3;
-            wsum += (long long)n0 * i0 + (long long)n1 * (i0 + 1) + (long long)n2 * (i0 + 2) + (long long)n3 * (i0 + 3);
-            const int4 out = make_int4(n0, n1, n2, n3);
-            if (c0 == 0) first = out; // slot 0 still open
-            else if (i0 < depth) *reinterpret_cast<int4*>(row + i0) = out;
+            if (sfx < thr_i) { // buffer.py:97-103: the oldest `thr` packets leave
+                const int t = n0 + n1 + n2 + n3;
+                int incl = t; // inclusive suffix sum over lanes (lane 31 holds the oldest slots)
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const int y = __shfl_down_sync(FULL, incl, d);
+                    if (lane + d < 32) incl += y;
+                }
+                const int s3 = sfx + incl - t; // packets strictly older than slot i0+3
+                const int s2 = s3 + n3, s1 = s2 + n2, s0 = s1 + n1;
+                sfx += __shfl_sync(FULL, incl, 0);
+                n3 -= min(n3, max(0, thr_i - s3));
+                n2 -= min(n2, max(0, thr_i - s2));
+                n1 -= min(n1, max(0, thr_i - s1));
+                n0 -= min(n0, max(0, thr_i - s0));
+            }
+            if (i0 == 0) n0 = a_left; // slot 0: the new arrivals (already net of what was sent)
+            wsum += (long long)i0 * (n0 + n1 + n2 + n3) + (n1 + 2 * n2 + 3 * n3);
+            if (i0 < depth) *reinterpret_cast<int4*>(row + i0) = make_int4(n0, n1, n2, n3);
         }
     }
-    // buffer.py:62-80: sfx is now the occupancy after the shift
-    const int total = sfx;
-    int dropped = expired;
-    if ((double)total + inc <= (double)max_pkts) {
-        arrived_kept = (int)inc;
-    } else {
-        dropped += (int)(long long)(inc - (double)(max_pkts - total));
-        arrived_kept = max_pkts - total;
-    }
-    const int a_left = arrived_kept - min(arrived_kept, max(0, thr_i - total));
-    if (lane == 0) { first.x = a_left; rem += a_left; }
-    if (4 * lane < depth) *reinterpret_cast<int4*>(row + 4 * lane) = first;
 #pragma unroll
-    for (int d = 16; d > 0; d >>= 1) {
-        rem += __shfl_xor_sync(FULL, rem, d);
-        wsum += __shfl_xor_sync(FULL, wsum, d);
-    }
-    RowResult r;
-    r.rem = rem;
-    r.wsum = wsum;
-    r.sent = total + arrived_kept - rem; // buffer.py:85,104 sum before - sum after
-    r.dropped = dropped;
-    return r;
+    for (int d = 16; d > 0; d >>= 1) wsum += __shfl_xor_sync(FULL, wsum, d);
+    return wsum;
 }
 
-// SE row of (e, u) for `frame` into shared memory, by the calling warp.
+// Everything older than the new arrivals was sent: the row becomes [a_left, 0, 0, ...].
+__device__ __forceinline__ void buffer_row_zero_fill(int* __restrict__ row, int depth, int a_left)
+{
+    const int lane = lane_id();
+    for (int i0 = 4 * lane; i0 < depth; i0 += 128)
+        *reinterpret_cast<int4*>(row + i0) = make_int4(i0 == 0 ? a_left : 0, 0, 0, 0);
+}
+
+// SE row of (e, u) for `frame` into shared memory, by the calling warp (reset path and the
+// injected / fixed channel modes of the step).
 __device__ __forceinline__ void channel_row(const StepArgs& A, int e, int u, bool associated, int frame,
                                             int episode, double* se)
 {
@@ -125,80 +114,124 @@ __device__ __forceinline__ void channel_row(const StepArgs& A, int e, int u, boo
     }
 }
 
-__global__ void __launch_bounds__(UE_WARPS * 32) k_ue_step(const __grid_constant__ StepArgs A)
+__global__ void __launch_bounds__(UE_WARPS * 32, 4) k_ue_step(const __grid_constant__ StepArgs A)
 {
-    __shared__ double sm[UE_WARPS][2][136];
+    __shared__ __align__(16) double sm[UE_WARPS][136];
     const DevState& st = A.st;
     const irs_config& cfg = A.cfg;
     const int lane = lane_id();
     const int wib = threadIdx.x >> 5;
-    const long long gw = (long long)blockIdx.x * UE_WARPS + wib;
-    if (gw >= (long long)cfg.num_envs * U) return;
-    const int e = (int)(gw / U), u = (int)(gw % U);
-    const size_t eu = (size_t)gw;
+    const unsigned gw = blockIdx.x * UE_WARPS + wib; // row index e * 25 + u (host checks E * 25 < 2^31)
+    if (gw >= (unsigned)cfg.num_envs * U) return;
+    const int e = gw / U, u = gw - e * U;
+    const size_t eu = gw;
+
+    // ---- prologue: every scalar the row needs, one lane each, issued before the generators --
+    const int win_len = st.win_len[e];
+    const int p = (st.win_head[e] + 1) % W; // window slot this frame goes to (deque.appendleft)
+    const int pre_i = lane < UI_N ? st.ue_i[eu * UI_N + lane] : 0;
+    const double occ_old_l = lane == 0 ? st.ue_d[eu * UD_N + UD_OCC] : 0.0;
+    int2 evict = make_int2(0, 0);
+    if (lane == 0 && win_len == W) evict = st.ring[(eu * W) + p];
+    const short2 run = st.rb[eu];
     const irs_scenario* sc = st.bank + st.scen[e];
     const int s = sc->ue_slice[u];
     UeParams up = ue_params(sc, s);
     if (up.depth > st.row_stride) up.depth = st.row_stride;
-    const int rb_s = st.rb_start[eu], rb_c = st.rb_count[eu];
     const int frame = st.step[e] + 1, episode = st.episode[e];
+    const int tot_prev = __shfl_sync(FULL, pre_i, UI_TOT);
 
-    double* se = sm[wib][0];
-    double* tm = sm[wib][1];
-    channel_row(A, e, u, s >= 0, frame, episode, se);
-    __syncwarp();
-    const double bw_rb = cfg.bandwidth / (double)R; // ues.py:110
-    for (int r = lane; r < R; r += 32) {
-        const double sched = (r >= rb_s && r < rb_s + rb_c) ? 1.0 : 0.0;
-        tm[r] = (bw_rb * sched) * se[r];
-        if (A.raw.se_used) A.raw.se_used[eu * R + r] = se[r];
+    // ---- channel + traffic of this frame --------------------------------------------------
+    double* se = sm[wib];
+    double traffic = 0.0, sum_t = 0.0, sum_se = 0.0;
+    const bool native = cfg.channel_mode == 2 && cfg.traffic_mode == 1;
+    const bool has_traffic = s >= 0 && (__ldg(&sc->sl[s >= 0 ? s : 0].flags) & IRS_F_REQ);
+    if (!(native && s < 0)) { // an unassociated UE has SE 0 and no traffic in native mode
+        if (native) {
+            traffic = native_row(cfg.seed, st.cdf, u, has_traffic ? __ldg(&sc->sl[s].lam_idx) : 0, has_traffic,
+                                 frame, episode, cfg.env_id_base + e, se);
+        } else {
+            channel_row(A, e, u, s >= 0, frame, episode, se);
+            if (cfg.traffic_mode == 0) traffic = A.traffic[eu];
+            else if (has_traffic)
+                traffic = native_traffic(cfg.seed, st.cdf, u, sc->sl[s].lam_idx, frame, episode, cfg.env_id_base + e);
+        }
+        __syncwarp();
+        const double sums = np_sum135_thr_se(se, run.x, run.x + run.y, A.bw_rb);
+        sum_t = __shfl_sync(FULL, sums, 0);
+        sum_se = __shfl_sync(FULL, sums, 16);
+        if (A.raw.se_used)
+            for (int r = lane; r < R; r += 32) A.raw.se_used[eu * R + r] = se[r];
+    } else if (A.raw.se_used) {
+        for (int r = lane; r < R; r += 32) A.raw.se_used[eu * R + r] = 0.0;
     }
-    __syncwarp();
-    const double sums = np_sum135_pair(tm, se);
-    const double sum_t = __shfl_sync(FULL, sums, 0), sum_se = __shfl_sync(FULL, sums, 16);
-    const double thr = floor(sum_t / up.pkt_bits); // ues.py:108-116
-    const double sebar = sum_se / (double)R;       // np.mean(SE[0,u,:])
-    double traffic;
-    if (cfg.traffic_mode == 0) traffic = A.traffic[eu];
-    else traffic = (s >= 0 && (sc->sl[s].flags & IRS_F_REQ))
-                       ? native_traffic(cfg.seed, st.cdf, u, sc->sl[s].lam_idx, frame, episode, cfg.env_id_base + e)
-                       : 0.0;
-    const double inc = floor(traffic / up.pkt_bits); // ues.py:199
+    // three float64 divisions in one instruction stream (lanes 0, 1, 2)
+    const double num = lane == 0 ? sum_t : (lane == 1 ? traffic : sum_se);
+    const double den = lane == 2 ? (double)R : up.pkt_bits;
+    const double quo = num / den;
+    const double thr = floor(__shfl_sync(FULL, quo, 0)); // ues.py:108-116
+    const double inc = floor(__shfl_sync(FULL, quo, 1)); // ues.py:199
+    const double sebar = __shfl_sync(FULL, quo, 2);      // np.mean(SE[0,u,:])
     const int thr_i = (int)fmin(fmax(thr, 0.0), 2147483647.0);
 
-    RowResult rr;
-    const int tot_prev = st.tot[eu];
-    if (tot_prev == 0 && inc == 0.0) { // empty row stays empty: nothing to stream
-        rr.sent = 0; rr.dropped = 0; rr.rem = 0; rr.wsum = 0;
+    // ---- Buffer.receive_packets + send_packets (buffer.py:53-104) ---------------------------
+    int* row = st.buf + eu * (size_t)st.row_stride;
+    int expired = 0, path = ROW_EMPTY;
+    if (tot_prev != 0) expired = row[up.depth - 1];   // buffer.py:60 dropped = buffer[-1]
+    const int total = tot_prev - expired;             // occupancy after the age shift
+    int dropped = expired, kept;
+    if ((double)total + inc <= (double)up.max_pkts) { // buffer.py:62-80
+        kept = (int)inc;
     } else {
-        rr = buffer_row_step(st.buf + eu * (size_t)st.row_stride, up.depth, up.max_pkts, thr_i, inc);
+        dropped += (int)(long long)(inc - (double)(up.max_pkts - total));
+        kept = up.max_pkts - total;
     }
+    const int sent_old = min(thr_i, total);           // oldest first (buffer.py:97-103)
+    const int a_left = kept - min(kept, thr_i - sent_old);
+    const int sent = sent_old + (kept - a_left);
+    const int rem = total + kept - sent;
+    long long wsum = 0;
+    if (tot_prev == 0) {                              // row is all zero: only slot 0 changes
+        if (lane == 0 && a_left != 0) row[0] = a_left;
+    } else if (sent_old == total) {                   // all older packets left: zero-fill
+        buffer_row_zero_fill(row, up.depth, a_left);
+        path = ROW_ZERO_FILL;
+    } else {
+        wsum = buffer_row_stream(row, up.depth, thr_i, a_left);
+        path = ROW_STREAM;
+    }
+    // occupancy and mean delay: two divisions in one stream (buffer.py:106-130)
+    const double num2 = lane == 0 ? (double)rem : (double)wsum;
+    const double den2 = lane == 0 ? (double)up.max_pkts : (double)rem;
+    const double quo2 = num2 / den2;
+    const double occ = __shfl_sync(FULL, quo2, 0);
+    const double lat = rem != 0 ? __shfl_sync(FULL, quo2, 1) : 0.0;
+
+    // ---- epilogue: window push + newest frame, one lane per field ---------------------------
+    const double occ_old = __shfl_sync(FULL, occ_old_l, 0);
+    const int ev_s = __shfl_sync(FULL, evict.x, 0), ev_d = __shfl_sync(FULL, evict.y, 0);
+    const int sum_sent = __shfl_sync(FULL, pre_i, UI_SUM_SENT) + sent - ev_s;
+    const int sum_drop = __shfl_sync(FULL, pre_i, UI_SUM_DROP) + dropped - ev_d;
+    int out_i = rem;                                  // UI_TOT
+    out_i = lane == UI_SUM_SENT ? sum_sent : out_i;
+    out_i = lane == UI_SUM_DROP ? sum_drop : out_i;
+    out_i = lane == UI_SENT ? sent : out_i;
+    out_i = lane == UI_DROP ? dropped : out_i;
+    out_i = lane == UI_INC ? (int)inc : out_i;
+    out_i = lane == UI_OCC1Z ? (isclose0(occ_old) ? 1 : 0) : out_i; // win[1].occ of the new window
+    out_i = lane == UI_PATH ? path : out_i;
+    if (lane < UI_N) st.ue_i[eu * UI_N + lane] = out_i;
+    double out_d = occ;                               // UD_OCC
+    out_d = lane == UD_LAT ? lat : out_d;
+    out_d = lane == UD_SEBAR ? sebar : out_d;
+    out_d = lane == UD_THR ? thr : out_d;
+    if (lane < UD_N) st.ue_d[eu * UD_N + lane] = out_d;
     if (lane == 0) {
-        const double occ = (double)rr.rem / (double)up.max_pkts;               // buffer.py:106-114
-        const double lat = rr.rem != 0 ? (double)rr.wsum / (double)rr.rem : 0.0; // buffer.py:116-130
-        // window push (deque.appendleft, maxlen 10): slot after the env's current head
-        const int win_len = st.win_len[e];
-        const int p = (st.win_head[e] + 1) % W;
-        const size_t ri = ((size_t)e * W + p) * U + u;
-        int ss = st.sum_sent[eu] + rr.sent, sd = st.sum_drop[eu] + rr.dropped;
-        if (win_len == W) { ss -= st.ring_sent[ri]; sd -= st.ring_drop[ri]; }
-        st.ring_sent[ri] = rr.sent;
-        st.ring_drop[ri] = rr.dropped;
-        st.sum_sent[eu] = ss;
-        st.sum_drop[eu] = sd;
-        st.occ1z[eu] = isclose0(st.occ[eu]) ? 1 : 0; // win[1].occ of the new window
-        st.occ[eu] = occ;
-        st.lat[eu] = lat;
-        st.sebar[eu] = sebar;
-        st.thr[eu] = thr;
-        st.tot[eu] = rr.rem;
-        st.last_sent[eu] = rr.sent;
-        st.last_drop[eu] = rr.dropped;
-        st.last_inc[eu] = (int)inc;
+        st.ring[eu * W + p] = make_int2(sent, dropped);
         if (A.raw.pkt_incoming) A.raw.pkt_incoming[eu] = inc;
         if (A.raw.pkt_throughputs) A.raw.pkt_throughputs[eu] = thr;
-        if (A.raw.sent) A.raw.sent[eu] = rr.sent;
-        if (A.raw.dropped) A.raw.dropped[eu] = rr.dropped;
+        if (A.raw.sent) A.raw.sent[eu] = sent;
+        if (A.raw.dropped) A.raw.dropped[eu] = dropped;
         if (A.raw.occ) A.raw.occ[eu] = occ;
         if (A.raw.lat) A.raw.lat[eu] = lat;
         if (A.raw.traffic_used) A.raw.traffic_used[eu] = traffic;

@@ -17,12 +17,8 @@ from .scenario import ScenarioBank
 U, S, R = capi.MAX_UES, capi.MAX_SLICES, capi.NUM_RBS
 
 _VIEWS = {  # name -> (torch dtype, trailing shape)
-    "occ": (torch.float64, (U,)), "lat": (torch.float64, (U,)), "sebar": (torch.float64, (U,)),
-    "thr": (torch.float64, (U,)),
-    "tot": (torch.int32, (U,)), "sum_sent": (torch.int32, (U,)), "sum_drop": (torch.int32, (U,)),
-    "last_sent": (torch.int32, (U,)), "last_drop": (torch.int32, (U,)), "last_inc": (torch.int32, (U,)),
-    "ring_sent": (torch.int32, (capi.WINDOW, U)), "ring_drop": (torch.int32, (capi.WINDOW, U)),
-    "occ1z": (torch.uint8, (U,)), "rb_start": (torch.int16, (U,)), "rb_count": (torch.int16, (U,)),
+    "ue_i": (torch.int32, (U, len(capi.UI_FIELDS))), "ue_d": (torch.float64, (U, len(capi.UD_FIELDS))),
+    "ring": (torch.int32, (U, capi.WINDOW, 2)), "rb": (torch.int16, (U, 2)),
     "step": (torch.int32, ()), "episode": (torch.int32, ()), "scen": (torch.int32, ()),
     "win_len": (torch.int32, ()), "win_head": (torch.int32, ()), "err": (torch.int32, ()),
     "sorted": (torch.int8, (S,)), "acc": (torch.float64, (capi.NUM_METRICS,)),
@@ -78,6 +74,11 @@ class BatchEngine:
                 self.h, self.bank_array.ctypes.data, len(self.bank_array), self.cdf.ctypes.data, self.cdf.shape[0],
                 self._stream()))
         self.v = {name: self._view(name, dt, shp) for name, (dt, shp) in _VIEWS.items()}
+        for k, name in enumerate(capi.UI_FIELDS):  # strided views of the per-UE records
+            self.v[name] = self.v["ue_i"][:, :, k]
+        for k, name in enumerate(capi.UD_FIELDS):
+            self.v[name] = self.v["ue_d"][:, :, k]
+        self.v["rb_start"], self.v["rb_count"] = self.v["rb"][:, :, 0], self.v["rb"][:, :, 1]
         self.buf = self._view("buf", torch.int32, (U, self.row_stride))
         self.metrics_total = self._view1("metrics_total", torch.float64, capi.NUM_METRICS)
         self._raw = None

@@ -55,7 +55,7 @@ def test_create_layout_destroy_without_gpu():
     assert lay.row_stride == 404
     offs = [getattr(lay, n) for n in capi._LAYOUT_ARRAYS]
     assert offs == sorted(offs) and all(o % 256 == 0 for o in offs)
-    assert lay.buf == 0 and lay.occ == 64 * 25 * 404 * 4
+    assert lay.buf == 0 and lay.ue_i == 64 * 25 * 404 * 4
     assert lay.total_bytes > lay.metrics_total
     # stepping an unbound handle is an error code, not a crash
     assert lib.irs_step(h, None, None, None, None) == capi.IRS_ERR_UNBOUND
