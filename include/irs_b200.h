@@ -184,6 +184,9 @@ int irs_step(irs_env* env, const irs_actions* actions_dev, const irs_inject* inj
  * Measurement aid for bench.py (roofline of the dominant kernel); not graph capturable. */
 int irs_step_profiled(irs_env* env, const irs_actions* actions_dev, const irs_inject* inject_dev,
                       const irs_raw_outputs* raw_dev, void* stream, float* kernel_ms_host);
+/* gym's reset(seed=...) (comm_env.py:398-413): re-key the native generators.  Takes effect for
+ * the next reset/step; does not touch the state. */
+int irs_set_seed(irs_env* env, uint64_t seed);
 /* n steps back to back with the on-device policy (cfg.policy != 0) and native generators. */
 int irs_run(irs_env* env, int32_t n_steps, void* stream);
 /* Same as irs_step but actions come from host memory and the env surface is copied back to

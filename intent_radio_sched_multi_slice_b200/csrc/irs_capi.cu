@@ -226,11 +226,12 @@ static int step_args(irs_env* env, const irs_actions* actions, const irs_inject*
 {
     int rc = check_ready(env, inject);
     if (rc) return rc;
-    if (env->cfg.policy == 0 && !(actions && actions->a0)) return fail(env, IRS_ERR_ARG, "policy 0 needs actions.a0");
-    if (env->cfg.policy == 0 && env->cfg.fixed_intra < 0 && !actions->intra) return fail(env, IRS_ERR_ARG, "fixed_intra -1 needs actions.intra");
+    const bool given = actions && actions->a0; // explicit actions override the on-device policy
+    if (env->cfg.policy == 0 && !given) return fail(env, IRS_ERR_ARG, "policy 0 needs actions.a0");
+    if (given && env->cfg.fixed_intra < 0 && !actions->intra) return fail(env, IRS_ERR_ARG, "fixed_intra -1 needs actions.intra");
     if (env->cfg.traffic_mode == 0 && !(inject && inject->traffic)) return fail(env, IRS_ERR_ARG, "traffic_mode 0 needs inject.traffic");
     *A = make_args(env);
-    if (actions) { A->a0 = actions->a0; A->intra = actions->intra; }
+    if (given) { A->a0 = actions->a0; A->intra = actions->intra; A->cfg.policy = 0; }
     if (inject) { A->se = inject->se; A->traffic = inject->traffic; }
     if (raw) A->raw = *raw;
     return IRS_OK;
@@ -259,6 +260,13 @@ int irs_step_profiled(irs_env* env, const irs_actions* actions, const irs_inject
     if (rc) return rc;
     CK(cudaEventSynchronize(env->ev[3]));
     for (int i = 0; i < 3; ++i) CK(cudaEventElapsedTime(&kernel_ms_host[i], env->ev[i], env->ev[i + 1]));
+    return IRS_OK;
+}
+
+int irs_set_seed(irs_env* env, uint64_t seed)
+{
+    if (!env) return IRS_ERR_ARG;
+    env->cfg.seed = seed;
     return IRS_OK;
 }
 
@@ -299,10 +307,12 @@ int irs_step_host(irs_env* env, const irs_actions* actions_host, const irs_host_
     cudaStream_t st = (cudaStream_t)stream;
     const size_t E = (size_t)env->cfg.num_envs;
     StepArgs A = make_args(env);
-    if (env->cfg.policy == 0) {
-        if (!(actions_host && actions_host->a0)) return fail(env, IRS_ERR_ARG, "policy 0 needs actions.a0");
+    const bool given = actions_host && actions_host->a0;
+    if (env->cfg.policy == 0 && !given) return fail(env, IRS_ERR_ARG, "policy 0 needs actions.a0");
+    if (given) {
         CK(cudaMemcpyAsync(env->st.in_a0, actions_host->a0, E * S * 8, cudaMemcpyHostToDevice, st));
         A.a0 = env->st.in_a0;
+        A.cfg.policy = 0;
         if (actions_host->intra) {
             CK(cudaMemcpyAsync(env->st.in_intra, actions_host->intra, E * S * 4, cudaMemcpyHostToDevice, st));
             A.intra = env->st.in_intra;

@@ -1,0 +1,148 @@
+"""GPU suite: the reference-shaped env surface (intent_radio_sched_multi_slice_b200.env) replays
+golden traces through the PUBLIC API - plugin classes passed by type (host tensor hooks feeding
+the recorded SE / traffic frames), dict actions in, dict observations / rewards / terminated out -
+and must reproduce the reference's returns, dict key order included (ib_sched.py:91,186-200;
+marl_comm_env.py:51-66)."""
+import numpy as np
+import pytest
+
+import golden_inputs
+
+pytestmark = pytest.mark.gpu
+
+
+def _trace_plugins(rse, sse, stf):
+    """Channel / Traffic classes (reference plugin interface) that replay recorded frames."""
+    state = {"reset": 0, "step": 0}
+
+    class TraceChannel:
+        def __init__(self, max_number_ues, max_number_basestations, num_available_rbs, rng, root_path, scenario_name):
+            self.fresh = True
+
+        def step(self, step_number, episode_number, mobilities, sched_decision=None):
+            if self.fresh:  # first call after construction = the reset frame (comm_env.py:449-451)
+                self.fresh = False
+                out = rse[state["reset"]]
+                state["reset"] += 1
+            else:
+                out = sse[state["step"]]
+            return out[None]
+
+    class TraceTraffic:
+        def __init__(self, max_number_ues, rng, root_path):
+            pass
+
+        def step(self, slice_ue_assoc, slice_req, step_number, episode_number):
+            return stf[min(state["step"], len(stf) - 1)]
+
+    return TraceChannel, TraceTraffic, state
+
+
+@pytest.mark.parametrize("name,agent,n", [("ibsched_mimic", "IBSched", 150), ("seq_fixed", "IBSched", 100),
+                                          ("cfg1_marr", "MARR", 120), ("mapf", "MAPF", 120)])
+def test_env_api_replays_reference_trace(name, agent, n, bank):
+    from intent_radio_sched_multi_slice_b200 import agents, plugins
+    from intent_radio_sched_multi_slice_b200.env import MARLCommEnv
+
+    meta, d = golden_inputs.load_trace(name)
+    rse, sse, stf = golden_inputs.regenerate(meta, d)
+    Ch, Tr, state = _trace_plugins(rse, sse, stf)
+    Assoc = plugins.MultSliceAssociation if meta["assoc"] == "mult_slice" else plugins.MultSliceAssociationSeq
+    env = MARLCommEnv(Ch, Tr, plugins.SimpleMobility, Assoc, "mult_slice", agent.lower(), int(meta["seed"]),
+                      root_path="/nonexistent", initial_episode_number=int(meta["initial_episode"]),
+                      max_episode_number=int(meta["max_episodes"]), save_hist=False, debug=True, scenario_bank=bank)
+    env.max_number_steps = int(meta["max_steps"])
+    ag = getattr(agents, agent)(env, 25, 5, 1, np.array([135]))
+    env.set_agent_functions(ag.obs_space_format, ag.action_format, ag.calculate_reward, ag.get_obs_space(),
+                            ag.get_action_space())
+    obs, info = env.reset(seed=int(meta["seed"]), options={"initial_episode": int(meta["initial_episode"])})
+    assert info == {}
+
+    def check_obs(obs, o0, m0, oi, mi, order, tag):
+        if agent != "IBSched":
+            assert isinstance(obs, np.ndarray) and obs.shape == (50,)
+            np.testing.assert_allclose(obs, o0, rtol=1e-5, atol=0, err_msg=tag)
+            return
+        assert list(obs.keys()) == [f"player_{int(k)}" for k in order], tag  # insertion order = sorted slices
+        np.testing.assert_allclose(obs["player_0"]["observations"], o0, rtol=1e-5, atol=0, err_msg=tag)
+        assert obs["player_0"]["action_mask"].dtype == np.int8 and np.array_equal(obs["player_0"]["action_mask"], m0)
+        for s in range(5):
+            np.testing.assert_allclose(obs[f"player_{s + 1}"]["observations"], oi[s], rtol=1e-5, atol=0, err_msg=tag)
+            assert np.array_equal(obs[f"player_{s + 1}"]["action_mask"], mi[s])
+
+    check_obs(obs, d["reset_obs0"][0], d["reset_mask0"][0], d["reset_obs_i"][0], d["reset_mask_i"][0],
+              d["reset_order"][0], "reset")
+    ri = 0
+    for k in range(n):
+        state["step"] = k
+        if agent == "IBSched":
+            action = {"player_0": d["a0"][k]}
+            action.update({f"player_{i + 1}": int(d["intra"][k][i]) for i in range(5)})
+        else:
+            action = ag.step(obs)  # DEVICE_POLICY: MARR / MAPF scores are computed on the device
+        obs, reward, term, trunc, info = env.step(action)
+        check_obs(obs, d["obs0"][k], d["mask0"][k], d["obs_i"][k], d["mask_i"][k], d["order"][k], f"step {k}")
+        done = bool(d["done"][k])
+        if agent == "IBSched":
+            assert list(reward.keys()) == [f"player_{i}" for i in range(6)]
+            np.testing.assert_allclose([reward[f"player_{i}"] for i in range(6)], d["reward"][k], rtol=1e-5, atol=1e-300)
+            assert term["__all__"] == done and trunc["__all__"] == done and term["player_3"] == done
+        else:
+            np.testing.assert_allclose(reward, d["reward"][k][0], rtol=1e-5, atol=1e-300)
+            assert term is done and trunc is done
+        assert info == {}
+        if done:
+            ri += 1
+            obs, _ = env.reset()
+            check_obs(obs, d["reset_obs0"][ri], d["reset_mask0"][ri], d["reset_obs_i"][ri], d["reset_mask_i"][ri],
+                      d["reset_order"][ri], f"reset {ri}")
+    env.close()
+
+
+def test_env_api_errors_like_the_reference(bank):
+    from intent_radio_sched_multi_slice_b200 import agents, plugins
+    from intent_radio_sched_multi_slice_b200.env import MARLCommEnv
+
+    env = MARLCommEnv(plugins.FixedSE, plugins.MultSliceTraffic, plugins.SimpleMobility, plugins.MultSliceAssociation,
+                      "mult_slice", "ib_sched", 10, save_hist=False, scenario_bank=bank, root_path="/nonexistent")
+    env.reset(seed=10, options={"initial_episode": 0})
+    bad = {"player_0": np.zeros(5)}
+    bad.update({f"player_{i}": 7 for i in range(1, 6)})
+    with pytest.raises(ValueError, match="Invalid intra-slice scheduling action"):  # ib_sched.py:341-344
+        env.step(bad)
+    with pytest.raises(NotImplementedError):
+        env.set_agent_functions(lambda o: o, lambda a: a, lambda o: 0.0)
+    env.close()
+
+
+def test_batched_env_matches_single_envs(bank):
+    """num_envs=8 with the built-in device plugins: env e of the batch equals a single env created
+    with env_id_base=e (results depend on the global env id only, not on the batch)."""
+    import torch
+
+    from intent_radio_sched_multi_slice_b200 import plugins
+    from intent_radio_sched_multi_slice_b200.env import BatchedMARLCommEnv
+
+    kw = dict(save_hist=False, scenario_bank=bank, root_path="/nonexistent", debug=True)
+    args = (plugins.MimicQuadriga, plugins.MultSliceTraffic, plugins.SimpleMobility, plugins.MultSliceAssociation,
+            "mult_slice", "ib_sched", 33)
+    big = BatchedMARLCommEnv(*args, num_envs=8, auto_reset=False, **kw)
+    ie = torch.arange(8, dtype=torch.int32) * 7
+    ob, _ = big.reset(initial_episodes=ie)
+    rng = np.random.default_rng(5)
+    acts = [(rng.uniform(-1, 1, (8, 5)), rng.integers(0, 3, (8, 5))) for _ in range(25)]
+    outs = []
+    for a0, intra in acts:
+        ob, rew, term, trunc, _ = big.step((a0, intra))
+        outs.append((ob["player_0"]["observations"].cpu().numpy().copy(), rew.cpu().numpy().copy()))
+    for e in (0, 3, 7):
+        one = BatchedMARLCommEnv(*args, num_envs=1, env_id_base=e, **kw)
+        one.reset(options={"initial_episode": int(ie[e])})
+        for k, (a0, intra) in enumerate(acts):
+            action = {"player_0": a0[e]}
+            action.update({f"player_{i + 1}": int(intra[e, i]) for i in range(5)})
+            ob1, rew1, *_ = one.step(action)
+            assert np.array_equal(ob1["player_0"]["observations"], outs[k][0][e])
+            assert np.array_equal([rew1[f"player_{i}"] for i in range(6)], outs[k][1][e])
+        one.close()
+    big.close()
