@@ -324,7 +324,8 @@ def run_b200(args):
         ms_total = float(t.item())
     err = eng.check_errors()
     active = float((torch.from_numpy((arr["ue_slice"][:, :25] >= 0).sum(1)).to(dev)[eng.v["scen"].long()]).double().mean().item())
-    metrics = eng.episode_metrics()
+    from intent_radio_sched_multi_slice_b200 import distributed as D
+    metrics_named = D.all_reduce_metrics(eng.episode_metrics(), dev)  # the path's one collective (NCCL when N > 1)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -342,7 +343,7 @@ def run_b200(args):
                        "state_bytes_per_gpu": state_bytes,
                        "l2": "state larger than L2" if flush is None else "L2 flushed (256 MB fill) between timed steps"},
             "e2e": e2e, "roofline": roofline, "cpu_baseline": cpu, "gpu_launches": 3 * K, "clocks": clocks,
-            "env_errors": err, "episode_metrics": dict(zip(capi.METRIC_NAMES, metrics.tolist())),
+            "env_errors": err, "episode_metrics": metrics_named,
         }
         print(json.dumps(line))
     if world > 1:
