@@ -87,12 +87,15 @@ __device__ __forceinline__ int sel5i(const int (&a)[N], int i)
     return v;
 }
 
-__device__ __forceinline__ void action_to_rb_warp(const StepArgs& A, int e)
+// Core of K3 on register inputs (this lane's UE: previous-frame occupancy, mean SE, window sum
+// of sent packets); returns this lane's RB run.  Shared by k_action and the fused k_env_step.
+__device__ __forceinline__ void action_to_rb_core(const StepArgs& A, int e, const irs_scenario* sc, double occ,
+                                                  double sebar, int sum_sent, int win_len, int step, int episode,
+                                                  int& start_out, int& count_out)
 {
     const DevState& st = A.st;
     const irs_config& cfg = A.cfg;
     const int lane = lane_id();
-    const irs_scenario* sc = st.bank + st.scen[e];
     const int s_mine = lane < U ? (int)sc->ue_slice[lane] : -1;
     uint32_t smask[S], gmask = 0;
 #pragma unroll
@@ -105,11 +108,6 @@ __device__ __forceinline__ void action_to_rb_warp(const StepArgs& A, int e)
 #pragma unroll
     for (int s = 0; s < S; ++s) { active[s] = (__ldg(&sc->sl[s].flags) & IRS_F_ACTIVE) != 0; nact += active[s]; }
 
-    const size_t eu = (size_t)e * U + (lane < U ? lane : 0);
-    const double occ = st.ue_d[eu * UD_N + UD_OCC];
-    const double sebar = st.ue_d[eu * UD_N + UD_SEBAR];
-    const int sum_sent = st.ue_i[eu * UI_N + UI_SUM_SENT];
-    const int win_len = st.win_len[e];
     const UeParams up = ue_params(sc, s_mine);
 
     // ---- where the action comes from ---------------------------------------------------
@@ -157,7 +155,7 @@ __device__ __forceinline__ void action_to_rb_warp(const StepArgs& A, int e)
         const int gid = cfg.env_id_base + e;
 #pragma unroll
         for (int q = 0; q < 3; ++q) {
-            const uint4 v = rng_quad(cfg.seed, K_POLICY, 0, q, st.step[e] + 1, st.episode[e], gid);
+            const uint4 v = rng_quad(cfg.seed, K_POLICY, 0, q, step + 1, episode, gid);
             w[4 * q] = v.x; w[4 * q + 1] = v.y; w[4 * q + 2] = v.z; w[4 * q + 3] = v.w;
         }
 #pragma unroll
@@ -232,11 +230,24 @@ __device__ __forceinline__ void action_to_rb_warp(const StepArgs& A, int e)
         for (int s = 0; s < S; ++s) expect += smask[s] ? rbs_per_slice[s] : 0;
         if (lane == 0 && total != expect) atomicOr(&st.err[e], ERR_RB_SUM);
     }
+    start_out = start;
+    count_out = count;
     if (lane < U) {
-        st.rb[eu] = make_short2((short)start, (short)count);
+        const size_t eu = (size_t)e * U + lane;
         if (A.raw.rb_start) A.raw.rb_start[eu] = (int16_t)start;
         if (A.raw.rb_count) A.raw.rb_count[eu] = (int16_t)count;
     }
+}
+
+__device__ __forceinline__ void action_to_rb_warp(const StepArgs& A, int e)
+{
+    const DevState& st = A.st;
+    const int lane = lane_id();
+    const size_t eu = (size_t)e * U + (lane < U ? lane : 0);
+    int start, count;
+    action_to_rb_core(A, e, st.bank + st.scen[e], st.ue_d[eu * UD_N + UD_OCC], st.ue_d[eu * UD_N + UD_SEBAR],
+                      st.ue_i[eu * UI_N + UI_SUM_SENT], st.win_len[e], st.step[e], st.episode[e], start, count);
+    if (lane < U) st.rb[eu] = make_short2((short)start, (short)count);
 }
 
 __global__ void __launch_bounds__(256) k_action(const __grid_constant__ StepArgs A)

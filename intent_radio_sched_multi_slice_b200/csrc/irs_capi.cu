@@ -3,6 +3,7 @@
 // in irs_step / irs_reset / irs_run (they are CUDA-graph capturable); the *_host variants add
 // the copies a single-process caller with host buffers needs.
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <new>
@@ -10,6 +11,7 @@
 #include "irs_action.cuh"
 #include "irs_env.cuh"
 #include "irs_ue.cuh"
+#include "irs_fused.cuh"
 
 struct irs_env {
     irs_config cfg;
@@ -20,6 +22,7 @@ struct irs_env {
     char* blob;
     cudaEvent_t ev[4];
     bool have_ev;
+    bool split; // IRS_SPLIT_KERNELS=1: three kernels per step instead of the fused one
     char err[256];
 };
 
@@ -97,6 +100,8 @@ int irs_create(const irs_config* cfg, int32_t n_lambda, irs_env** out)
     memset(env, 0, sizeof(*env));
     env->cfg = *cfg;
     env->n_lambda = n_lambda;
+    const char* sp = getenv("IRS_SPLIT_KERNELS");
+    env->split = sp && sp[0] == '1';
     compute_layout(env->cfg, n_lambda, &env->lay);
     *out = env;
     return IRS_OK;
@@ -211,6 +216,13 @@ static int launch_step(irs_env* env, const StepArgs& A, cudaStream_t st, bool pr
 {
     const int E = env->cfg.num_envs;
     if (profile) CK(cudaEventRecord(env->ev[0], st));
+    if (!env->split) {
+        if (profile) CK(cudaEventRecord(env->ev[1], st));
+        k_env_step<<<(E + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(A);
+        if (profile) { CK(cudaEventRecord(env->ev[2], st)); CK(cudaEventRecord(env->ev[3], st)); }
+        CK(cudaGetLastError());
+        return IRS_OK;
+    }
     k_action<<<(E + 7) / 8, 256, 0, st>>>(A);
     if (profile) CK(cudaEventRecord(env->ev[1], st));
     const long long rows = (long long)E * U;

@@ -73,26 +73,19 @@ __device__ __forceinline__ void reset_env_warp(const StepArgs& A, int e, int ini
 }
 
 // Everything of CommunicationEnv.step after UEs.step (comm_env.py:339-373).
-__device__ __forceinline__ void env_tail_warp(const StepArgs& A, int e, double* se_row)
+// Core on register inputs: `f` = this lane's newest frame (already pushed into the per-UE
+// window), dropped / inc of that frame, the env's window length / head / step BEFORE this step.
+__device__ __forceinline__ void env_tail_core(const StepArgs& A, int e, const irs_scenario* sc, UeFrame f,
+                                              int dropped, int inc, int win_len_old, int head_old, int step_old,
+                                              double* se_row)
 {
     const DevState& st = A.st;
     const irs_config& c = A.cfg;
     const int lane = lane_id();
-    const size_t eu = (size_t)e * U + (lane < U ? lane : 0);
-    const int* ui = st.ue_i + eu * UI_N;
-    const double* ud = st.ue_d + eu * UD_N;
-    UeFrame f;
-    f.occ = ud[UD_OCC]; f.lat = ud[UD_LAT]; f.sebar = ud[UD_SEBAR];
-    f.sent = ui[UI_SENT]; f.sum_sent = ui[UI_SUM_SENT]; f.sum_drop = ui[UI_SUM_DROP];
-    f.rb_count = st.rb[eu].y; f.occ1z = ui[UI_OCC1Z] != 0;
-    int dropped = ui[UI_DROP], inc = ui[UI_INC];
     if (lane >= U) { f.sent = 0; f.rb_count = 0; dropped = 0; inc = 0; }
-    // the per-UE part of the window push was done by k_ue_step; finish the per-env part
-    const int win_len_old = st.win_len[e];
     const int win_len = win_len_old < W ? win_len_old + 1 : W;
-    const int head = (st.win_head[e] + 1) % W;
-    const int step = st.step[e] + 1; // comm_env.py:339
-    const irs_scenario* sc = st.bank + st.scen[e];
+    const int head = (head_old + 1) % W;
+    const int step = step_old + 1; // comm_env.py:339
     __syncwarp();
     if (lane == 0) { st.win_len[e] = win_len; st.win_head[e] = head; st.step[e] = step; }
 
@@ -192,6 +185,22 @@ __device__ __forceinline__ void env_tail_warp(const StepArgs& A, int e, double* 
         __syncwarp();
         reset_env_warp(A, e, -1, se_row);
     }
+}
+
+__device__ __forceinline__ void env_tail_warp(const StepArgs& A, int e, double* se_row)
+{
+    const DevState& st = A.st;
+    const int lane = lane_id();
+    const size_t eu = (size_t)e * U + (lane < U ? lane : 0);
+    const int* ui = st.ue_i + eu * UI_N;
+    const double* ud = st.ue_d + eu * UD_N;
+    UeFrame f;
+    f.occ = ud[UD_OCC]; f.lat = ud[UD_LAT]; f.sebar = ud[UD_SEBAR];
+    f.sent = ui[UI_SENT]; f.sum_sent = ui[UI_SUM_SENT]; f.sum_drop = ui[UI_SUM_DROP];
+    f.rb_count = st.rb[eu].y; f.occ1z = ui[UI_OCC1Z] != 0;
+    // the per-UE part of the window push was done by k_ue_step; the core finishes the per-env part
+    env_tail_core(A, e, st.bank + st.scen[e], f, ui[UI_DROP], ui[UI_INC], st.win_len[e], st.win_head[e], st.step[e],
+                  se_row);
 }
 
 __global__ void __launch_bounds__(ENV_WARPS * 32) k_env_tail(const __grid_constant__ StepArgs A)

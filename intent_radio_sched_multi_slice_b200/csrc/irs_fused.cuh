@@ -1,0 +1,231 @@
+// irs_fused.cuh - k_env_step: the whole CommunicationEnv.step of one env in ONE warp.
+//
+// Lane u = UE u for everything that is per-UE scalar work (RB allocation, closed-form buffer
+// arithmetic, intent drift, window push) - the same mapping k_action and k_env_tail use, so
+// their cores are reused on register inputs and nothing makes a round trip through HBM between
+// the stages.  The two warp-wide stages are
+//   * the generators: (UE, Philox quad) tasks of up to 4 associated UEs are packed over the 32
+//     lanes - 4 main passes (lane l = SE quad l of one UE) + 1 auxiliary pass that serves all 4
+//     UEs at once (6 lanes per UE: 4 half-quads for RBs 128..134, the per-episode mean, the
+//     Poisson arrival) - and the 135-term NumPy-order sums of each generated row;
+//   * the buffer rows that need touching (zero-fill / stream paths), one row after the other
+//     with 128-bit accesses (irs_ue.cuh).
+// Compared with one warp per UE row this removes the per-row scalar prologue/epilogue (done
+// once per env, 25 UEs wide), skips unassociated UEs entirely, and replaces three launches by
+// one.  Same reference symbols as irs_action.cuh / irs_ue.cuh / irs_obs.cuh / irs_env.cuh.
+#pragma once
+#include "irs_action.cuh"
+#include "irs_env.cuh"
+#include "irs_ue.cuh"
+
+#define FUSED_WARPS 4 /* envs per block */
+#define GRP 4         /* UE rows generated per group */
+
+template <typename T>
+__device__ __forceinline__ T sel4(const T (&a)[GRP], int j)
+{
+    T v = a[0];
+#pragma unroll
+    for (int k = 1; k < GRP; ++k) v = (j == k) ? a[k] : v;
+    return v;
+}
+
+__global__ void __launch_bounds__(FUSED_WARPS * 32, 4) k_env_step(const __grid_constant__ StepArgs A)
+{
+    __shared__ __align__(16) double sm[FUSED_WARPS][GRP][136];
+    const DevState& st = A.st;
+    const irs_config& cfg = A.cfg;
+    const int lane = lane_id();
+    const int wib = threadIdx.x >> 5;
+    const int e = blockIdx.x * FUSED_WARPS + wib;
+    if (e >= cfg.num_envs) return;
+
+    // ---- phase 0: env scalars and this lane's UE record ------------------------------------
+    const int step = st.step[e], episode = st.episode[e];
+    const int win_len = st.win_len[e], head = st.win_head[e];
+    const int p = (head + 1) % W; // window slot of this frame (deque.appendleft)
+    const irs_scenario* sc = st.bank + st.scen[e];
+    const bool ue_lane = lane < U;
+    const int s_mine = ue_lane ? (int)sc->ue_slice[lane] : -1;
+    UeParams up = ue_params(sc, s_mine);
+    if (up.depth > st.row_stride) up.depth = st.row_stride;
+    const size_t eu = (size_t)e * U + (ue_lane ? lane : 0);
+    const int4 rec_a = *reinterpret_cast<const int4*>(st.ue_i + eu * UI_N); // tot, sum_sent, sum_drop, sent
+    const double2 rec_d0 = *reinterpret_cast<const double2*>(st.ue_d + eu * UD_N);     // occ, lat
+    const double2 rec_d1 = *reinterpret_cast<const double2*>(st.ue_d + eu * UD_N + 2); // sebar, thr
+    int2 evict = make_int2(0, 0);
+    if (ue_lane && win_len == W) evict = st.ring[eu * W + p];
+    const int tot_prev = ue_lane ? rec_a.x : 0;
+    int* row = st.buf + eu * (size_t)st.row_stride;
+    const int expired = (ue_lane && tot_prev != 0) ? row[up.depth - 1] : 0; // buffer.py:60, in flight early
+    const int frame = step + 1, gid = cfg.env_id_base + e;
+
+    // ---- phase 1: action -> RB runs (ib_sched.py:223-349) ---------------------------------
+    int rb_s, rb_c;
+    action_to_rb_core(A, e, sc, rec_d0.x, rec_d1.x, rec_a.y, win_len, step, episode, rb_s, rb_c);
+
+    // ---- phase 2: channel + traffic of this frame, and the two row sums per UE --------------
+    const bool native = cfg.channel_mode == 2 && cfg.traffic_mode == 1;
+    const int fl_mine = s_mine >= 0 ? __ldg(&sc->sl[s_mine].flags) : 0;
+    const bool has_traffic = (fl_mine & IRS_F_REQ) != 0;
+    const int lam_idx = has_traffic ? __ldg(&sc->sl[s_mine].lam_idx) : 0;
+    double sum_t = 0.0, sum_se = 0.0, traffic = 0.0;
+    if (!native) {
+        if (cfg.traffic_mode == 0) traffic = ue_lane ? A.traffic[eu] : 0.0;
+        else if (has_traffic) traffic = native_traffic(cfg.seed, st.cdf, lane, lam_idx, frame, episode, gid);
+    }
+    uint32_t todo = __ballot_sync(FULL, ue_lane && (native ? s_mine >= 0 : true));
+    while (todo) { // warp-uniform
+        int ul[GRP], n = 0;
+#pragma unroll
+        for (int j = 0; j < GRP; ++j) {
+            ul[j] = todo ? (__ffs(todo) - 1) : 0;
+            if (todo) { ++n; todo &= todo - 1; }
+        }
+        if (native) {
+            // auxiliary pass: lane 6j+k serves UE j of the group
+            const int j = lane / 6, k = lane - 6 * j;
+            const bool valid = lane < 6 * GRP && j < n;
+            const int ue_j = sel4(ul, j < GRP ? j : 0);
+            const int kind = k < 4 ? K_SE : (k == 4 ? K_MU : K_TRAFFIC);
+            const int q = k < 2 ? 32 : (k < 4 ? 33 : 0);
+            const uint4 w = rng_quad(cfg.seed, kind, ue_j, q, k == 4 ? 0 : frame, episode, gid);
+            const bool hi_pair = k < 4 && (k & 1);
+            float z0, z1;
+            normal_pair(hi_pair ? w.z : w.x, hi_pair ? w.w : w.y, z0, z1);
+            const double mu_l = fabs(__fma_rn(7.5, (double)z0, 10.0)); // meaningful on k == 4
+            const double mu_aux = __shfl_sync(FULL, mu_l, (valid ? 6 * j : 0) + 4);
+            if (valid && k < 4) {
+                double* se = sm[wib][j];
+                const int i0 = 4 * q + 2 * (k & 1);
+                se[i0] = fabs(__fma_rn(1.5, (double)z0, mu_aux));
+                if (i0 + 1 < R) se[i0 + 1] = fabs(__fma_rn(1.5, (double)z1, mu_aux));
+            }
+            // Poisson arrival of UE j on lane 6j+5 (traffics/mult_slice.py:28-31)
+            const int lam_j = __shfl_sync(FULL, lam_idx, ue_j);
+            const int ht_j = __shfl_sync(FULL, (int)has_traffic, ue_j);
+            int lo = 0;
+            if (valid && k == 5 && ht_j) {
+                const double u01 = ((double)(w.x >> 5) * 67108864.0 + (double)(w.y >> 6)) * (1.0 / 9007199254740992.0);
+                const double* cdf = st.cdf + (size_t)lam_j * IRS_POISSON_K;
+#pragma unroll
+                for (int stp = IRS_POISSON_K / 2; stp > 0; stp >>= 1)
+                    if (__ldg(&cdf[lo + stp - 1]) <= u01) lo += stp;
+                if (__ldg(&cdf[lo]) <= u01) lo += 1;
+            }
+            const double tr_l = (double)lo * 1e6;
+#pragma unroll
+            for (int jj = 0; jj < GRP; ++jj) {
+                const double t = __shfl_sync(FULL, tr_l, 6 * jj + 5);
+                if (jj < n && lane == ul[jj]) traffic = t;
+            }
+            // main passes: lane l = SE quad l of UE jj (channels/mimic_quadriga.py:49-56)
+#pragma unroll
+            for (int jj = 0; jj < GRP; ++jj) {
+                if (jj >= n) break; // warp-uniform
+                const double mu = __shfl_sync(FULL, mu_l, 6 * jj + 4);
+                const uint4 wb = rng_quad(cfg.seed, K_SE, ul[jj], lane, frame, episode, gid);
+                float y0, y1, y2, y3;
+                normal_pair(wb.x, wb.y, y0, y1);
+                normal_pair(wb.z, wb.w, y2, y3);
+                double2* out = reinterpret_cast<double2*>(sm[wib][jj] + 4 * lane);
+                out[0] = make_double2(fabs(__fma_rn(1.5, (double)y0, mu)), fabs(__fma_rn(1.5, (double)y1, mu)));
+                out[1] = make_double2(fabs(__fma_rn(1.5, (double)y2, mu)), fabs(__fma_rn(1.5, (double)y3, mu)));
+            }
+        } else {
+#pragma unroll
+            for (int jj = 0; jj < GRP; ++jj) {
+                if (jj >= n) break;
+                const int assoc = __shfl_sync(FULL, (int)(s_mine >= 0), ul[jj]);
+                channel_row(A, e, ul[jj], assoc != 0, frame, episode, sm[wib][jj]);
+            }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int jj = 0; jj < GRP; ++jj) {
+            if (jj >= n) break;
+            const int rs = __shfl_sync(FULL, rb_s, ul[jj]), rc = __shfl_sync(FULL, rb_c, ul[jj]);
+            const double sums = np_sum135_thr_se(sm[wib][jj], rs, rs + rc, A.bw_rb);
+            const double a = __shfl_sync(FULL, sums, 0), b = __shfl_sync(FULL, sums, 16);
+            if (lane == ul[jj]) { sum_t = a; sum_se = b; }
+            if (A.raw.se_used)
+                for (int r = lane; r < R; r += 32) A.raw.se_used[((size_t)e * U + ul[jj]) * R + r] = sm[wib][jj][r];
+        }
+        __syncwarp();
+    }
+    if (native && A.raw.se_used) { // unassociated UEs have SE 0 in native mode
+        for (int u = 0; u < U; ++u) {
+            if (__shfl_sync(FULL, s_mine, u) >= 0) continue;
+            for (int r = lane; r < R; r += 32) A.raw.se_used[((size_t)e * U + u) * R + r] = 0.0;
+        }
+    }
+
+    // ---- phase 3: throughput, arrivals, closed-form buffer arithmetic - one UE per lane -------
+    const double thr = floor(sum_t / up.pkt_bits);   // ues.py:108-116
+    const double inc = floor(traffic / up.pkt_bits); // ues.py:199
+    const double sebar = sum_se / (double)R;         // np.mean(SE[0,u,:])
+    const int thr_i = (int)fmin(fmax(thr, 0.0), 2147483647.0);
+    const int total = tot_prev - expired;            // occupancy after the age shift (buffer.py:60-62)
+    int dropped = expired, kept;
+    if ((double)total + inc <= (double)up.max_pkts) { // buffer.py:62-80
+        kept = (int)inc;
+    } else {
+        dropped += (int)(long long)(inc - (double)(up.max_pkts - total));
+        kept = up.max_pkts - total;
+    }
+    const int sent_old = min(thr_i, total);          // oldest first (buffer.py:97-103)
+    const int a_left = kept - min(kept, thr_i - sent_old);
+    const int sent = sent_old + (kept - a_left);
+    const int rem = total + kept - sent;
+    int path = ROW_EMPTY;
+    if (ue_lane && tot_prev != 0) path = (sent_old == total) ? ROW_ZERO_FILL : ROW_STREAM;
+
+    // ---- phase 4: the rows -------------------------------------------------------------------
+    if (ue_lane && tot_prev == 0 && a_left != 0) row[0] = a_left; // empty row: only slot 0 changes
+    long long wsum = 0;
+    uint32_t zf = __ballot_sync(FULL, path == ROW_ZERO_FILL);
+    uint32_t stm = __ballot_sync(FULL, path == ROW_STREAM);
+    while (zf) {
+        const int u = __ffs(zf) - 1;
+        zf &= zf - 1;
+        buffer_row_zero_fill(st.buf + ((size_t)e * U + u) * st.row_stride, __shfl_sync(FULL, up.depth, u),
+                             __shfl_sync(FULL, a_left, u));
+    }
+    while (stm) {
+        const int u = __ffs(stm) - 1;
+        stm &= stm - 1;
+        const long long w = buffer_row_stream(st.buf + ((size_t)e * U + u) * st.row_stride,
+                                              __shfl_sync(FULL, up.depth, u), __shfl_sync(FULL, thr_i, u),
+                                              __shfl_sync(FULL, a_left, u));
+        if (lane == u) wsum = w;
+    }
+
+    // ---- phase 5: occupancy, mean delay, window push, record stores ---------------------------
+    const double occ = (double)rem / (double)up.max_pkts;               // buffer.py:106-114
+    const double lat = rem != 0 ? (double)wsum / (double)rem : 0.0;      // buffer.py:116-130
+    const int sum_sent = rec_a.y + sent - evict.x;
+    const int sum_drop = rec_a.z + dropped - evict.y;
+    const bool occ1z = isclose0(rec_d0.x); // win[1].occ of the new window
+    if (ue_lane) {
+        *reinterpret_cast<int4*>(st.ue_i + eu * UI_N) = make_int4(rem, sum_sent, sum_drop, sent);
+        *reinterpret_cast<int4*>(st.ue_i + eu * UI_N + 4) = make_int4(dropped, (int)inc, occ1z ? 1 : 0, path);
+        *reinterpret_cast<double2*>(st.ue_d + eu * UD_N) = make_double2(occ, lat);
+        *reinterpret_cast<double2*>(st.ue_d + eu * UD_N + 2) = make_double2(sebar, thr);
+        st.ring[eu * W + p] = make_int2(sent, dropped);
+        st.rb[eu] = make_short2((short)rb_s, (short)rb_c);
+        if (A.raw.pkt_incoming) A.raw.pkt_incoming[eu] = inc;
+        if (A.raw.pkt_throughputs) A.raw.pkt_throughputs[eu] = thr;
+        if (A.raw.sent) A.raw.sent[eu] = sent;
+        if (A.raw.dropped) A.raw.dropped[eu] = dropped;
+        if (A.raw.occ) A.raw.occ[eu] = occ;
+        if (A.raw.lat) A.raw.lat[eu] = lat;
+        if (A.raw.traffic_used) A.raw.traffic_used[eu] = traffic;
+    }
+
+    // ---- phase 6: observation, reward, metrics, done, rollover (comm_env.py:339-373) ----------
+    UeFrame f;
+    f.occ = occ; f.lat = lat; f.sebar = sebar; f.sent = sent; f.sum_sent = sum_sent; f.sum_drop = sum_drop;
+    f.rb_count = rb_c; f.occ1z = occ1z;
+    __syncwarp();
+    env_tail_core(A, e, sc, f, dropped, (int)inc, win_len, head, step, sm[wib][0]);
+}
