@@ -16,9 +16,9 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "_lib")
-LIB = os.path.join(LIB_DIR, "libirs_b200.so")
+LIB = os.environ.get("IRS_LIB_PATH") or os.path.join(LIB_DIR, "libirs_b200.so")
 SOURCES = ["irs_capi.cu"]
-HEADERS = ["irs_common.cuh", "irs_rng.cuh", "irs_action.cuh", "irs_ue.cuh", "irs_obs.cuh", "irs_env.cuh",
+HEADERS = ["irs_common.cuh", "irs_rng.cuh", "irs_action.cuh", "irs_ue.cuh", "irs_obs.cuh", "irs_env.cuh", "irs_fused.cuh",
            os.path.join("..", "..", "include", "irs_b200.h")]
 
 NVCC_FLAGS = [
@@ -46,7 +46,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not stale():
         return LIB
     os.makedirs(LIB_DIR, exist_ok=True)
-    cmd = [nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
+    cmd = [nvcc()] + NVCC_FLAGS + os.environ.get("IRS_NVCC_EXTRA", "").split() + (["-Xptxas", "-v"] if verbose else []) + \
           ["-o", LIB] + [os.path.join(CSRC, f) for f in SOURCES]
     if verbose:
         print(" ".join(cmd), file=sys.stderr)

@@ -22,7 +22,8 @@ struct irs_env {
     char* blob;
     cudaEvent_t ev[4];
     bool have_ev;
-    bool split; // IRS_SPLIT_KERNELS=1: three kernels per step instead of the fused one
+    int mode; // IRS_STEP_MODE: 0 fused k_env_step, 1 k_action + k_ue_step (warp per row) + k_env_tail,
+              //                2 k_action + k_ue_env (warp per env) + k_env_tail
     char err[256];
 };
 
@@ -100,8 +101,8 @@ int irs_create(const irs_config* cfg, int32_t n_lambda, irs_env** out)
     memset(env, 0, sizeof(*env));
     env->cfg = *cfg;
     env->n_lambda = n_lambda;
-    const char* sp = getenv("IRS_SPLIT_KERNELS");
-    env->split = sp && sp[0] == '1';
+    const char* sp = getenv("IRS_STEP_MODE");
+    env->mode = sp ? atoi(sp) : 2;
     compute_layout(env->cfg, n_lambda, &env->lay);
     *out = env;
     return IRS_OK;
@@ -216,7 +217,7 @@ static int launch_step(irs_env* env, const StepArgs& A, cudaStream_t st, bool pr
 {
     const int E = env->cfg.num_envs;
     if (profile) CK(cudaEventRecord(env->ev[0], st));
-    if (!env->split) {
+    if (env->mode == 0) {
         if (profile) CK(cudaEventRecord(env->ev[1], st));
         k_env_step<<<(E + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(A);
         if (profile) { CK(cudaEventRecord(env->ev[2], st)); CK(cudaEventRecord(env->ev[3], st)); }
@@ -226,7 +227,8 @@ static int launch_step(irs_env* env, const StepArgs& A, cudaStream_t st, bool pr
     k_action<<<(E + 7) / 8, 256, 0, st>>>(A);
     if (profile) CK(cudaEventRecord(env->ev[1], st));
     const long long rows = (long long)E * U;
-    k_ue_step<<<(unsigned)((rows + UE_WARPS - 1) / UE_WARPS), UE_WARPS * 32, 0, st>>>(A);
+    if (env->mode == 1) k_ue_step<<<(unsigned)((rows + UE_WARPS - 1) / UE_WARPS), UE_WARPS * 32, 0, st>>>(A);
+    else k_ue_env<<<(E + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(A);
     if (profile) CK(cudaEventRecord(env->ev[2], st));
     k_env_tail<<<(E + ENV_WARPS - 1) / ENV_WARPS, ENV_WARPS * 32, 0, st>>>(A);
     if (profile) CK(cudaEventRecord(env->ev[3], st));

@@ -71,7 +71,7 @@ __device__ __forceinline__ bool isclose0(double x) { return fabs(x) <= 1e-8; } /
 // slice index order NumPy iterates in.  For n < 8 np.add.reduce is a serial sum starting
 // from 0. (numpy/_core/src/umath/loops_utils.h.src, DOUBLE_pairwise_sum), then added to the
 // reduction identity: 0. + res.
-__device__ __forceinline__ double group_sum_ordered(double x, uint32_t mask)
+__device__ __noinline__ double group_sum_ordered(double x, uint32_t mask)
 {
     double res = 0.;
     uint32_t m = mask;
@@ -86,7 +86,7 @@ __device__ __forceinline__ double group_sum_ordered(double x, uint32_t mask)
     }
     return 0. + res;
 }
-__device__ __forceinline__ int group_sum_int(int x, uint32_t mask)
+__device__ __noinline__ int group_sum_int(int x, uint32_t mask)
 {
     int res = 0;
     uint32_t m = mask;
@@ -101,7 +101,7 @@ __device__ __forceinline__ int group_sum_int(int x, uint32_t mask)
     }
     return res;
 }
-__device__ __forceinline__ double group_max(double x, uint32_t mask)
+__device__ __noinline__ double group_max(double x, uint32_t mask)
 {
     double res = x;
     uint32_t m = mask;
@@ -121,7 +121,7 @@ __device__ __forceinline__ double group_max(double x, uint32_t mask)
 // lane).  np.argsort pinned to kind="stable" (SURVEY 7.1): the +1s go to entries in
 // descending value order, ties -> higher index first, cyclically.  Returns this lane's
 // integer share (0 for non-members and for x == 0).
-__device__ __forceinline__ int group_round_int_equal_sum(double x, uint32_t mask, int target)
+__device__ __noinline__ int group_round_int_equal_sum(double x, uint32_t mask, int target)
 {
     const int lane = lane_id();
     const bool member = (mask >> lane) & 1u;
@@ -163,7 +163,7 @@ __device__ __forceinline__ int group_round_int_equal_sum(double x, uint32_t mask
 }
 
 // Exclusive prefix (ascending lane order) of an int over the members of `mask`.
-__device__ __forceinline__ int group_prefix_excl(int x, uint32_t mask)
+__device__ __noinline__ int group_prefix_excl(int x, uint32_t mask)
 {
     const int lane = lane_id();
     int res = 0;
@@ -185,7 +185,7 @@ __device__ __forceinline__ int group_prefix_excl(int x, uint32_t mask)
 // serially, halves added, then "0. +".  Lanes [g*8, g*8+8) reduce half `g&1` of row `g>>1`,
 // so one warp produces two row sums at once: result 0 valid in lane 0, result 1 in lane 16.
 // ues.py:108-116 (throughput) and np.mean(SE[0,u,:]) (ib_sched.py:111,147) depend on this order.
-__device__ __forceinline__ double np_sum135_pair(const double* rowA, const double* rowB)
+__device__ __noinline__ double np_sum135_pair(const double* rowA, const double* rowB)
 {
     const int lane = lane_id();
     const int j = lane & 7;
@@ -209,7 +209,7 @@ __device__ __forceinline__ double np_sum135_pair(const double* rowA, const doubl
 // Same reduction order, both sums of one SE row at once: lanes 0..15 sum the throughput
 // terms ((BW/R) * sched[r]) * SE[r] (ues.py:108-116; sched is 1 inside the UE's RB run, else
 // 0), lanes 16..31 sum SE[r] itself.  Results valid in lanes 0 and 16.
-__device__ __forceinline__ double np_sum135_thr_se(const double* se, int rb_s, int rb_e, double bw_rb)
+__device__ __noinline__ double np_sum135_thr_se(const double* se, int rb_s, int rb_e, double bw_rb)
 {
     const int lane = lane_id();
     const int j = lane & 7;

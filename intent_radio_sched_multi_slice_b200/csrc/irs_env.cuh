@@ -9,7 +9,7 @@
 // 136-double shared-memory scratch row owned by the warp.  The observation window is NOT
 // cleared (ib_sched.py:51,64: the deque lives in the agent) - the zero frame of the reset is
 // pushed into it (comm_env.py:474-482), quirk Q1 of SURVEY 7.4.
-__device__ __forceinline__ void reset_env_warp(const StepArgs& A, int e, int initial_episode, double* se_row)
+__device__ __noinline__ void reset_env_warp(const StepArgs& A, int e, int initial_episode, double* se_row)
 {
     const DevState& st = A.st;
     const irs_config& c = A.cfg;
@@ -77,7 +77,7 @@ __device__ __forceinline__ void reset_env_warp(const StepArgs& A, int e, int ini
 // window), dropped / inc of that frame, the env's window length / head / step BEFORE this step.
 __device__ __forceinline__ void env_tail_core(const StepArgs& A, int e, const irs_scenario* sc, UeFrame f,
                                               int dropped, int inc, int win_len_old, int head_old, int step_old,
-                                              double* se_row)
+                                              double* se_row, bool block_sync = false)
 {
     const DevState& st = A.st;
     const irs_config& c = A.cfg;
@@ -91,6 +91,7 @@ __device__ __forceinline__ void env_tail_core(const StepArgs& A, int e, const ir
 
     const SliceView v = format_obs_warp(A, e, sc, f, win_len); // comm_env.py:340
 
+    if (block_sync) __syncthreads(); // keeps the block's warps in the same code region (I-cache)
     // ---- calculate_reward (ib_sched.py:206-221, common.py:381-439) ----------------------
     const double prio_raw = __ldg(&sc->sl[lane < S ? lane : 0].priority);
     double a_s = 0, p_s = 0;
@@ -133,6 +134,7 @@ __device__ __forceinline__ void env_tail_core(const StepArgs& A, int e, const ir
     if (lane == 0) st.out_reward[(size_t)e * 6] = r0;
     if (lane < S) st.out_reward[(size_t)e * 6 + 1 + lane] = r_intra;
 
+    if (block_sync) __syncthreads();
     // ---- episode metrics (metrics.py:62-71 as running sums; definitions from
     //      results/gen_results.py:791-809, 874-970, 973-1022) -----------------------------
     long long t_sent = f.sent, t_drop = dropped, t_inc = inc;

@@ -18,7 +18,16 @@
 #include "irs_env.cuh"
 #include "irs_ue.cuh"
 
+#ifndef FUSED_WARPS
 #define FUSED_WARPS 4 /* envs per block */
+#endif
+#ifndef FUSED_SYNC
+#define FUSED_SYNC 0 /* 1: block-wide barriers between phases keep the SM's warps in the same code region */
+#endif
+#define PHASE_SYNC() do { if (FUSED_SYNC) __syncthreads(); } while (0)
+#ifndef FUSED_MINB
+#define FUSED_MINB 4 /* resident blocks per SM the register budget is set for */
+#endif
 #define GRP 4         /* UE rows generated per group */
 
 template <typename T>
@@ -30,9 +39,13 @@ __device__ __forceinline__ T sel4(const T (&a)[GRP], int j)
     return v;
 }
 
-__global__ void __launch_bounds__(FUSED_WARPS * 32, 4) k_env_step(const __grid_constant__ StepArgs A)
+// FULL_STEP = true : the whole step (action -> rows -> observation/reward/rollover) in one kernel.
+// FULL_STEP = false: only the per-UE middle of the step (what k_ue_step does per row), between
+//                    k_action and k_env_tail; every warp of the GPU then runs the same, much
+//                    smaller code region, which the instruction cache holds.
+template <bool FULL_STEP>
+__device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GRP][136])
 {
-    __shared__ __align__(16) double sm[FUSED_WARPS][GRP][136];
     const DevState& st = A.st;
     const irs_config& cfg = A.cfg;
     const int lane = lane_id();
@@ -62,8 +75,14 @@ __global__ void __launch_bounds__(FUSED_WARPS * 32, 4) k_env_step(const __grid_c
 
     // ---- phase 1: action -> RB runs (ib_sched.py:223-349) ---------------------------------
     int rb_s, rb_c;
-    action_to_rb_core(A, e, sc, rec_d0.x, rec_d1.x, rec_a.y, win_len, step, episode, rb_s, rb_c);
+    if (FULL_STEP) {
+        action_to_rb_core(A, e, sc, rec_d0.x, rec_d1.x, rec_a.y, win_len, step, episode, rb_s, rb_c);
+    } else {
+        const short2 run = st.rb[eu];
+        rb_s = run.x; rb_c = run.y;
+    }
 
+    PHASE_SYNC();
     // ---- phase 2: channel + traffic of this frame, and the two row sums per UE --------------
     const bool native = cfg.channel_mode == 2 && cfg.traffic_mode == 1;
     const int fl_mine = s_mine >= 0 ? __ldg(&sc->sl[s_mine].flags) : 0;
@@ -75,7 +94,7 @@ __global__ void __launch_bounds__(FUSED_WARPS * 32, 4) k_env_step(const __grid_c
         else if (has_traffic) traffic = native_traffic(cfg.seed, st.cdf, lane, lam_idx, frame, episode, gid);
     }
     uint32_t todo = __ballot_sync(FULL, ue_lane && (native ? s_mine >= 0 : true));
-    while (todo) { // warp-uniform
+    while (FUSED_SYNC >= 2 ? __syncthreads_or(todo != 0) : (todo != 0)) { // warp-uniform (block-uniform when synced)
         int ul[GRP], n = 0;
 #pragma unroll
         for (int j = 0; j < GRP; ++j) {
@@ -120,11 +139,10 @@ __global__ void __launch_bounds__(FUSED_WARPS * 32, 4) k_env_step(const __grid_c
                 if (jj < n && lane == ul[jj]) traffic = t;
             }
             // main passes: lane l = SE quad l of UE jj (channels/mimic_quadriga.py:49-56)
-#pragma unroll
-            for (int jj = 0; jj < GRP; ++jj) {
-                if (jj >= n) break; // warp-uniform
+#pragma unroll 1
+            for (int jj = 0; jj < n; ++jj) { // a loop, not unrolled: the body must stay I-cache resident
                 const double mu = __shfl_sync(FULL, mu_l, 6 * jj + 4);
-                const uint4 wb = rng_quad(cfg.seed, K_SE, ul[jj], lane, frame, episode, gid);
+                const uint4 wb = rng_quad(cfg.seed, K_SE, sel4(ul, jj), lane, frame, episode, gid);
                 float y0, y1, y2, y3;
                 normal_pair(wb.x, wb.y, y0, y1);
                 normal_pair(wb.z, wb.w, y2, y3);
@@ -133,23 +151,23 @@ __global__ void __launch_bounds__(FUSED_WARPS * 32, 4) k_env_step(const __grid_c
                 out[1] = make_double2(fabs(__fma_rn(1.5, (double)y2, mu)), fabs(__fma_rn(1.5, (double)y3, mu)));
             }
         } else {
-#pragma unroll
-            for (int jj = 0; jj < GRP; ++jj) {
-                if (jj >= n) break;
-                const int assoc = __shfl_sync(FULL, (int)(s_mine >= 0), ul[jj]);
-                channel_row(A, e, ul[jj], assoc != 0, frame, episode, sm[wib][jj]);
+#pragma unroll 1
+            for (int jj = 0; jj < n; ++jj) {
+                const int uj = sel4(ul, jj);
+                const int assoc = __shfl_sync(FULL, (int)(s_mine >= 0), uj);
+                channel_row(A, e, uj, assoc != 0, frame, episode, sm[wib][jj]);
             }
         }
         __syncwarp();
-#pragma unroll
-        for (int jj = 0; jj < GRP; ++jj) {
-            if (jj >= n) break;
-            const int rs = __shfl_sync(FULL, rb_s, ul[jj]), rc = __shfl_sync(FULL, rb_c, ul[jj]);
+#pragma unroll 1
+        for (int jj = 0; jj < n; ++jj) {
+            const int uj = sel4(ul, jj);
+            const int rs = __shfl_sync(FULL, rb_s, uj), rc = __shfl_sync(FULL, rb_c, uj);
             const double sums = np_sum135_thr_se(sm[wib][jj], rs, rs + rc, A.bw_rb);
             const double a = __shfl_sync(FULL, sums, 0), b = __shfl_sync(FULL, sums, 16);
-            if (lane == ul[jj]) { sum_t = a; sum_se = b; }
+            if (lane == uj) { sum_t = a; sum_se = b; }
             if (A.raw.se_used)
-                for (int r = lane; r < R; r += 32) A.raw.se_used[((size_t)e * U + ul[jj]) * R + r] = sm[wib][jj][r];
+                for (int r = lane; r < R; r += 32) A.raw.se_used[((size_t)e * U + uj) * R + r] = sm[wib][jj][r];
         }
         __syncwarp();
     }
@@ -160,6 +178,7 @@ __global__ void __launch_bounds__(FUSED_WARPS * 32, 4) k_env_step(const __grid_c
         }
     }
 
+    PHASE_SYNC();
     // ---- phase 3: throughput, arrivals, closed-form buffer arithmetic - one UE per lane -------
     const double thr = floor(sum_t / up.pkt_bits);   // ues.py:108-116
     const double inc = floor(traffic / up.pkt_bits); // ues.py:199
@@ -212,7 +231,7 @@ __global__ void __launch_bounds__(FUSED_WARPS * 32, 4) k_env_step(const __grid_c
         *reinterpret_cast<double2*>(st.ue_d + eu * UD_N) = make_double2(occ, lat);
         *reinterpret_cast<double2*>(st.ue_d + eu * UD_N + 2) = make_double2(sebar, thr);
         st.ring[eu * W + p] = make_int2(sent, dropped);
-        st.rb[eu] = make_short2((short)rb_s, (short)rb_c);
+        if (FULL_STEP) st.rb[eu] = make_short2((short)rb_s, (short)rb_c);
         if (A.raw.pkt_incoming) A.raw.pkt_incoming[eu] = inc;
         if (A.raw.pkt_throughputs) A.raw.pkt_throughputs[eu] = thr;
         if (A.raw.sent) A.raw.sent[eu] = sent;
@@ -222,10 +241,27 @@ __global__ void __launch_bounds__(FUSED_WARPS * 32, 4) k_env_step(const __grid_c
         if (A.raw.traffic_used) A.raw.traffic_used[eu] = traffic;
     }
 
+    PHASE_SYNC();
+    if (!FULL_STEP) return;
     // ---- phase 6: observation, reward, metrics, done, rollover (comm_env.py:339-373) ----------
     UeFrame f;
     f.occ = occ; f.lat = lat; f.sebar = sebar; f.sent = sent; f.sum_sent = sum_sent; f.sum_drop = sum_drop;
     f.rb_count = rb_c; f.occ1z = occ1z;
     __syncwarp();
-    env_tail_core(A, e, sc, f, dropped, (int)inc, win_len, head, step, sm[wib][0]);
+    env_tail_core(A, e, sc, f, dropped, (int)inc, win_len, head, step, sm[wib][0], FUSED_SYNC >= 2);
+}
+
+__global__ void __launch_bounds__(FUSED_WARPS * 32, FUSED_MINB) k_env_step(const __grid_constant__ StepArgs A)
+{
+    __shared__ __align__(16) double sm[FUSED_WARPS][GRP][136];
+    env_step_body<true>(A, sm);
+}
+
+#ifndef UE_ENV_MINB
+#define UE_ENV_MINB 8 /* 64 registers: 32 warps per SM measured fastest (profiles/r1_notes.md) */
+#endif
+__global__ void __launch_bounds__(FUSED_WARPS * 32, UE_ENV_MINB) k_ue_env(const __grid_constant__ StepArgs A)
+{
+    __shared__ __align__(16) double sm[FUSED_WARPS][GRP][136];
+    env_step_body<false>(A, sm);
 }

@@ -72,7 +72,7 @@ __device__ __forceinline__ void intent_drift_ue(const irs_slice* sl, int flags, 
 
 // ib_sched.py:63-204.  Writes obs0/obs_i/masks/sorted for env e; returns the slice view the
 // reward needs.  `sc` is the scenario the env is playing; all 32 lanes must call.
-__device__ __forceinline__ SliceView format_obs_warp(const StepArgs& A, int e, const irs_scenario* sc,
+__device__ __noinline__ SliceView format_obs_warp(const StepArgs& A, int e, const irs_scenario* sc,
                                                      const UeFrame& f, int win_len)
 {
     const DevState& st = A.st;

@@ -15,7 +15,7 @@
 
 enum { K_SE = 0, K_TRAFFIC = 1, K_MU = 2, K_POLICY = 3 };
 
-__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1)
+__device__ __noinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1)
 {
 #pragma unroll
     for (int r = 0; r < 10; ++r) {
@@ -36,7 +36,7 @@ __device__ __forceinline__ uint4 rng_quad(uint64_t seed, int kind, int ue, int q
 // Two standard normals from two 32-bit words: Box-Muller in binary32 with a fixed polynomial
 // log (atanh series on the mantissa) and octant-reduced sin/cos polynomials; no libm, no
 // fast-math intrinsics, so the result is a pure function of IEEE add/mul/fma/div/sqrt.
-__device__ __forceinline__ void normal_pair(uint32_t wa, uint32_t wb, float& z0, float& z1)
+__device__ __noinline__ float2 normal_pair2(uint32_t wa, uint32_t wb)
 {
     const float u1 = __fmul_rn((float)((wa >> 8) + 1u), 5.9604644775390625e-08f); // (0,1]
     uint32_t bits = __float_as_uint(u1);
@@ -70,8 +70,13 @@ __device__ __forceinline__ void normal_pair(uint32_t wa, uint32_t wb, float& z0,
     float b = swap ? sn : cs;
     if (oct >= 2 && oct <= 5) a = -a;
     if (oct >= 4) b = -b;
-    z0 = __fmul_rn(r, a);
-    z1 = __fmul_rn(r, b);
+    return make_float2(__fmul_rn(r, a), __fmul_rn(r, b));
+}
+__device__ __forceinline__ void normal_pair(uint32_t wa, uint32_t wb, float& z0, float& z1)
+{
+    const float2 z = normal_pair2(wa, wb);
+    z0 = z.x;
+    z1 = z.y;
 }
 
 // channels/mimic_quadriga.py:37-41
@@ -85,7 +90,7 @@ __device__ __forceinline__ double native_mu(uint64_t seed, int ue, int episode, 
 
 // channels/mimic_quadriga.py:49-56: one UE row of SE into `se` (shared memory, 135 doubles),
 // produced cooperatively by the calling warp (quad q -> RBs 4q..4q+3).
-__device__ __forceinline__ void native_se_row(uint64_t seed, int ue, int frame, int episode, int gid, double* se)
+__device__ __noinline__ void native_se_row(uint64_t seed, int ue, int frame, int episode, int gid, double* se)
 {
     const double mu = native_mu(seed, ue, episode, gid);
     for (int q = lane_id(); q < (R + 3) / 4; q += 32) {
@@ -101,7 +106,7 @@ __device__ __forceinline__ void native_se_row(uint64_t seed, int ue, int frame, 
 
 // traffics/mult_slice.py:28-31 by table inversion: k = #{j : cdf[j] <= u}, u a 53-bit uniform.
 // The table is non-decreasing, so the count is an upper bound search.
-__device__ __forceinline__ double native_traffic(uint64_t seed, const double* cdf_all, int ue, int lam_idx,
+__device__ __noinline__ double native_traffic(uint64_t seed, const double* cdf_all, int ue, int lam_idx,
                                                  int frame, int episode, int gid)
 {
     const uint4 w = rng_quad(seed, K_TRAFFIC, ue, 0, frame, episode, gid);
@@ -120,7 +125,7 @@ __device__ __forceinline__ double native_traffic(uint64_t seed, const double* cd
 //           lane 3: the Poisson arrival          (same counters and values as the functions above)
 //   pass B  lane l: SE quad l (RBs 4l..4l+3)
 // Returns the offered traffic in bits (0 when the UE's slice has no requirements).
-__device__ __forceinline__ double native_row(uint64_t seed, const double* cdf_all, int ue, int lam_idx,
+__device__ __noinline__ double native_row(uint64_t seed, const double* cdf_all, int ue, int lam_idx,
                                              bool has_traffic, int frame, int episode, int gid, double* se)
 {
     const int lane = lane_id();

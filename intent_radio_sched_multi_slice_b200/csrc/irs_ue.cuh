@@ -32,7 +32,7 @@ enum { ROW_EMPTY = 0, ROW_ZERO_FILL = 1, ROW_STREAM = 2 };
 // General case: stream the row once.  `total` = packets in slots >= 1 after the shift,
 // `thr_i` = packets that may leave (thr_i < total here), `a_left` = what stays in slot 0.
 // Returns sum(age * packets left), reduced over the warp.
-__device__ __forceinline__ long long buffer_row_stream(int* __restrict__ row, int depth, int thr_i, int a_left)
+__device__ __noinline__ long long buffer_row_stream(int* __restrict__ row, int depth, int thr_i, int a_left)
 {
     const int lane = lane_id();
     const int nch = (depth + 127) >> 7;
@@ -89,7 +89,7 @@ __device__ __forceinline__ long long buffer_row_stream(int* __restrict__ row, in
 }
 
 // Everything older than the new arrivals was sent: the row becomes [a_left, 0, 0, ...].
-__device__ __forceinline__ void buffer_row_zero_fill(int* __restrict__ row, int depth, int a_left)
+__device__ __noinline__ void buffer_row_zero_fill(int* __restrict__ row, int depth, int a_left)
 {
     const int lane = lane_id();
     for (int i0 = 4 * lane; i0 < depth; i0 += 128)
@@ -98,7 +98,7 @@ __device__ __forceinline__ void buffer_row_zero_fill(int* __restrict__ row, int 
 
 // SE row of (e, u) for `frame` into shared memory, by the calling warp (reset path and the
 // injected / fixed channel modes of the step).
-__device__ __forceinline__ void channel_row(const StepArgs& A, int e, int u, bool associated, int frame,
+__device__ __noinline__ void channel_row(const StepArgs& A, int e, int u, bool associated, int frame,
                                             int episode, double* se)
 {
     const int lane = lane_id();
