@@ -252,7 +252,7 @@ __device__ __forceinline__ void action_to_rb_warp(const StepArgs& A, int e)
 
 __global__ void __launch_bounds__(256) k_action(const __grid_constant__ StepArgs A)
 {
-    const int e = (int)((blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 5);
-    if (e >= A.cfg.num_envs) return;
+    const int e = A.env_begin + (int)((blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 5);
+    if (e >= A.env_end) return;
     action_to_rb_warp(A, e);
 }

@@ -13,6 +13,8 @@
 #include "irs_ue.cuh"
 #include "irs_fused.cuh"
 
+#define IRS_MAX_HOST_CHUNKS 16
+
 struct irs_env {
     irs_config cfg;
     irs_layout lay;
@@ -22,6 +24,10 @@ struct irs_env {
     char* blob;
     cudaEvent_t ev[4];
     bool have_ev;
+    cudaStream_t copy_stream;      // irs_step_host: device->host copies of finished chunks
+    cudaEvent_t chunk_ev[IRS_MAX_HOST_CHUNKS];
+    bool have_copy;
+    int host_chunks;               // IRS_HOST_CHUNKS (0 = choose from the batch size)
     int mode; // IRS_STEP_MODE: 0 fused k_env_step, 1 k_action + k_ue_step (warp per row) + k_env_tail,
               //                2 k_action + k_ue_env (warp per env) + k_env_tail
     char err[256];
@@ -78,6 +84,8 @@ static StepArgs make_args(const irs_env* env)
     A.cfg = env->cfg;
     A.bw_rb = env->cfg.bandwidth / (double)R; // ues.py:110
     A.initial_episode = -1;
+    A.env_begin = 0;
+    A.env_end = env->cfg.num_envs;
     return A;
 }
 
@@ -103,6 +111,8 @@ int irs_create(const irs_config* cfg, int32_t n_lambda, irs_env** out)
     env->n_lambda = n_lambda;
     const char* sp = getenv("IRS_STEP_MODE");
     env->mode = sp ? atoi(sp) : 2;
+    const char* hc = getenv("IRS_HOST_CHUNKS");
+    env->host_chunks = hc ? atoi(hc) : 0;
     compute_layout(env->cfg, n_lambda, &env->lay);
     *out = env;
     return IRS_OK;
@@ -112,6 +122,10 @@ int irs_destroy(irs_env* env)
 {
     if (env && env->have_ev)
         for (int i = 0; i < 4; ++i) cudaEventDestroy(env->ev[i]);
+    if (env && env->have_copy) {
+        for (int i = 0; i < IRS_MAX_HOST_CHUNKS; ++i) cudaEventDestroy(env->chunk_ev[i]);
+        cudaStreamDestroy(env->copy_stream);
+    }
     delete env;
     return IRS_OK;
 }
@@ -215,7 +229,8 @@ int irs_reset(irs_env* env, const uint8_t* mask_dev, int32_t initial_episode, co
 
 static int launch_step(irs_env* env, const StepArgs& A, cudaStream_t st, bool profile = false)
 {
-    const int E = env->cfg.num_envs;
+    const int E = A.env_end - A.env_begin;
+    if (E <= 0) return IRS_OK;
     if (profile) CK(cudaEventRecord(env->ev[0], st));
     if (env->mode == 0) {
         if (profile) CK(cudaEventRecord(env->ev[1], st));
@@ -297,19 +312,45 @@ int irs_run(irs_env* env, int32_t n_steps, void* stream)
     return IRS_OK;
 }
 
-static int copy_surface(irs_env* env, const irs_host_surface* o, bool with_reward, cudaStream_t st)
+// Device->host copies of the env surface for envs [e0, e1), enqueued on `st` (no synchronisation).
+static int copy_surface_range(irs_env* env, const irs_host_surface* o, bool with_reward, size_t e0, size_t e1, cudaStream_t st)
 {
-    const size_t E = (size_t)env->cfg.num_envs;
+    const size_t n = e1 - e0;
     const irs_layout& L = env->lay;
     char* b = env->blob;
-    if (o->obs0) CK(cudaMemcpyAsync(o->obs0, b + L.out_obs0, E * IRS_OBS0 * 8, cudaMemcpyDeviceToHost, st));
-    if (o->obsi) CK(cudaMemcpyAsync(o->obsi, b + L.out_obsi, E * S * IRS_OBSI * 8, cudaMemcpyDeviceToHost, st));
-    if (o->mask0) CK(cudaMemcpyAsync(o->mask0, b + L.out_mask0, E * S, cudaMemcpyDeviceToHost, st));
-    if (o->maski) CK(cudaMemcpyAsync(o->maski, b + L.out_maski, E * S * NS, cudaMemcpyDeviceToHost, st));
-    if (with_reward && o->reward) CK(cudaMemcpyAsync(o->reward, b + L.out_reward, E * 6 * 8, cudaMemcpyDeviceToHost, st));
-    if (with_reward && o->done) CK(cudaMemcpyAsync(o->done, b + L.out_done, E, cudaMemcpyDeviceToHost, st));
+    auto d2h = [&](void* host, size_t dev_off, size_t per_env) -> cudaError_t {
+        if (!host) return cudaSuccess;
+        return cudaMemcpyAsync((char*)host + e0 * per_env, b + dev_off + e0 * per_env, n * per_env, cudaMemcpyDeviceToHost, st);
+    };
+    CK(d2h(o->obs0, L.out_obs0, IRS_OBS0 * 8));
+    CK(d2h(o->obsi, L.out_obsi, S * IRS_OBSI * 8));
+    CK(d2h(o->mask0, L.out_mask0, S));
+    CK(d2h(o->maski, L.out_maski, S * NS));
+    if (with_reward) {
+        CK(d2h(o->reward, L.out_reward, 6 * 8));
+        CK(d2h(o->done, L.out_done, 1));
+    }
+    return IRS_OK;
+}
+
+static int copy_surface(irs_env* env, const irs_host_surface* o, bool with_reward, cudaStream_t st)
+{
+    int rc = copy_surface_range(env, o, with_reward, 0, (size_t)env->cfg.num_envs, st);
+    if (rc) return rc;
     CK(cudaStreamSynchronize(st));
     return IRS_OK;
+}
+
+// How many chunks irs_step_host splits the batch into: the surface of a finished chunk crosses
+// PCIe while the next chunk computes.  Small batches stay whole (launch latency dominates).
+static int host_chunk_count(const irs_env* env)
+{
+    int c = env->host_chunks;
+    if (c <= 0) c = env->cfg.num_envs / 8192;
+    if (c < 1) c = 1;
+    if (c > 8 && env->host_chunks <= 0) c = 8;
+    if (c > IRS_MAX_HOST_CHUNKS) c = IRS_MAX_HOST_CHUNKS;
+    return c;
 }
 
 int irs_step_host(irs_env* env, const irs_actions* actions_host, const irs_host_surface* out_host, void* stream)
@@ -332,9 +373,32 @@ int irs_step_host(irs_env* env, const irs_actions* actions_host, const irs_host_
             A.intra = env->st.in_intra;
         } else if (env->cfg.fixed_intra < 0) return fail(env, IRS_ERR_ARG, "fixed_intra -1 needs actions.intra");
     }
-    rc = launch_step(env, A, st);
-    if (rc) return rc;
-    return copy_surface(env, out_host, true, st);
+    const int chunks = host_chunk_count(env);
+    if (chunks == 1) {
+        rc = launch_step(env, A, st);
+        if (rc) return rc;
+        return copy_surface(env, out_host, true, st);
+    }
+    if (!env->have_copy) {
+        CK(cudaStreamCreateWithFlags(&env->copy_stream, cudaStreamNonBlocking));
+        for (int i = 0; i < IRS_MAX_HOST_CHUNKS; ++i) CK(cudaEventCreateWithFlags(&env->chunk_ev[i], cudaEventDisableTiming));
+        env->have_copy = true;
+    }
+    const size_t per = (E + chunks - 1) / chunks;
+    for (int c = 0; c < chunks; ++c) {
+        const size_t e0 = c * per, e1 = e0 + per < E ? e0 + per : E;
+        if (e0 >= e1) break;
+        A.env_begin = (int32_t)e0;
+        A.env_end = (int32_t)e1;
+        rc = launch_step(env, A, st);
+        if (rc) return rc;
+        CK(cudaEventRecord(env->chunk_ev[c], st));
+        CK(cudaStreamWaitEvent(env->copy_stream, env->chunk_ev[c], 0));
+        rc = copy_surface_range(env, out_host, true, e0, e1, env->copy_stream);
+        if (rc) return rc;
+    }
+    CK(cudaStreamSynchronize(env->copy_stream)); // implies every chunk's kernels on `st` finished
+    return IRS_OK;
 }
 
 int irs_reset_host(irs_env* env, int32_t initial_episode, const irs_host_surface* out_host, void* stream)

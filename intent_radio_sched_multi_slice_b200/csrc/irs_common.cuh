@@ -60,6 +60,7 @@ struct StepArgs {
     const uint8_t* reset_mask;
     const int32_t* initial_episode_dev;
     int32_t initial_episode;
+    int32_t env_begin, env_end; // env range of this launch (irs_step_host pipelines chunks of the batch)
 };
 
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }

@@ -208,8 +208,8 @@ __device__ __forceinline__ void env_tail_warp(const StepArgs& A, int e, double* 
 __global__ void __launch_bounds__(ENV_WARPS * 32) k_env_tail(const __grid_constant__ StepArgs A)
 {
     __shared__ double sm[ENV_WARPS][136];
-    const int e = blockIdx.x * ENV_WARPS + (threadIdx.x >> 5);
-    if (e >= A.cfg.num_envs) return;
+    const int e = A.env_begin + blockIdx.x * ENV_WARPS + (threadIdx.x >> 5);
+    if (e >= A.env_end) return;
     env_tail_warp(A, e, sm[threadIdx.x >> 5]);
 }
 

@@ -50,8 +50,8 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
     const irs_config& cfg = A.cfg;
     const int lane = lane_id();
     const int wib = threadIdx.x >> 5;
-    const int e = blockIdx.x * FUSED_WARPS + wib;
-    if (e >= cfg.num_envs) return;
+    const int e = A.env_begin + blockIdx.x * FUSED_WARPS + wib;
+    if (e >= A.env_end) return;
 
     // ---- phase 0: env scalars and this lane's UE record ------------------------------------
     const int step = st.step[e], episode = st.episode[e];

@@ -121,8 +121,8 @@ __global__ void __launch_bounds__(UE_WARPS * 32, 4) k_ue_step(const __grid_const
     const irs_config& cfg = A.cfg;
     const int lane = lane_id();
     const int wib = threadIdx.x >> 5;
-    const unsigned gw = blockIdx.x * UE_WARPS + wib; // row index e * 25 + u (host checks E * 25 < 2^31)
-    if (gw >= (unsigned)cfg.num_envs * U) return;
+    const unsigned gw = (unsigned)A.env_begin * U + blockIdx.x * UE_WARPS + wib; // row index e * 25 + u (host checks E * 25 < 2^31)
+    if (gw >= (unsigned)A.env_end * U) return;
     const int e = gw / U, u = gw - e * U;
     const size_t eu = gw;
 

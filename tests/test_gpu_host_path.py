@@ -1,0 +1,48 @@
+"""GPU suite: irs_step_host (host actions in, host surface out) must return exactly what the
+device-resident irs_step produces - also when the batch is pipelined in chunks (kernels of chunk
+c+1 overlap the device->host copy of chunk c) and the chunk size does not divide the batch."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("chunks", [1, 3, 8])
+def test_step_host_equals_device_step(bank, chunks, monkeypatch):
+    import torch
+
+    from intent_radio_sched_multi_slice_b200 import capi
+    from intent_radio_sched_multi_slice_b200.engine import BatchEngine
+
+    E = 1000  # not a multiple of 3 or 8
+    kw = dict(channel_mode=2, traffic_mode=1, sort_slices=1, fixed_intra=-1, policy=0, scen_mod=200, max_steps=9,
+              auto_reset=1, seed=21, env_id_base=3, depth_cap=401)
+    monkeypatch.setenv("IRS_HOST_CHUNKS", str(chunks))
+    host = BatchEngine(bank, E, **kw)
+    monkeypatch.delenv("IRS_HOST_CHUNKS")
+    dev = BatchEngine(bank, E, **kw)
+    ep = (np.arange(E) % 200).astype(np.int32)
+    host.reset(initial_episodes=ep)
+    dev.reset(initial_episodes=ep)
+    pin = lambda *s, dt: torch.empty(*s, dtype=dt).pin_memory()
+    hs = {"obs0": pin(E, 50, dt=torch.float64), "obsi": pin(E, 5, 19, dt=torch.float64),
+          "mask0": pin(E, 5, dt=torch.int8), "maski": pin(E, 5, 5, dt=torch.int8),
+          "reward": pin(E, 6, dt=torch.float64), "done": pin(E, dt=torch.uint8)}
+    surf = capi.HostSurface(*[hs[n].data_ptr() for n in capi.SURFACE_FIELDS])
+    rng = np.random.default_rng(5)
+    names = {"obs0": "obs0", "obsi": "obs_i", "mask0": "mask0", "maski": "mask_i", "reward": "reward", "done": "done"}
+    for k in range(25):  # crosses two auto-resets (max_steps = 9)
+        a0 = torch.from_numpy(rng.uniform(-1, 1, (E, 5))).pin_memory()
+        intra = torch.from_numpy(rng.integers(0, 3, (E, 5)).astype(np.int32)).pin_memory()
+        host.step_host(a0, intra, surf)
+        dev.step(a0, intra)
+        torch.cuda.synchronize()
+        s = dev.surface()
+        for hn, dn in names.items():
+            assert np.array_equal(hs[hn].numpy(), s[dn].cpu().numpy()), f"step {k}: {hn} differs (chunks={chunks})"
+    assert host.check_errors() is None
+    assert torch.equal(host.buf, dev.buf)
+    host.close()
+    dev.close()
