@@ -101,7 +101,7 @@ def load(build_if_missing: bool = True):
     if _lib is not None:
         return _lib
     path = lib_path()
-    if not os.path.exists(path) or (build_if_missing and _build.stale()):
+    if not os.path.exists(path) or (build_if_missing and not os.environ.get("IRS_LIB_PATH") and _build.stale()):
         if not build_if_missing:
             raise RuntimeError(f"{path} is missing: run `python -m intent_radio_sched_multi_slice_b200.build`")
         try:

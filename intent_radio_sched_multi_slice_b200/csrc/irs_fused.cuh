@@ -138,18 +138,63 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
                 const double t = __shfl_sync(FULL, tr_l, 6 * jj + 5);
                 if (jj < n && lane == ul[jj]) traffic = t;
             }
-            // main passes: lane l = SE quad l of UE jj (channels/mimic_quadriga.py:49-56)
+            __syncwarp(); // tail elements 128..134 of the group's rows are in shared memory
+            // pair passes: lanes 0..15 serve UE ul[2p], lanes 16..31 UE ul[2p+1].  Lane m of a side
+            // generates SE quads 2m, 2m+1 = the 8 elements accumulator m & 7 of row half m >> 3
+            // visits (se_index), and adds them up in registers in NumPy's order: both 135-term
+            // sums (ues.py:108-116 throughput terms, np.mean(SE)) without a shared-memory row.
 #pragma unroll 1
-            for (int jj = 0; jj < n; ++jj) { // a loop, not unrolled: the body must stay I-cache resident
+            for (int pp = 0; 2 * pp < n; ++pp) {
+                const int side = lane >> 4;
+                const int jj = (2 * pp + side < n) ? 2 * pp + side : 2 * pp; // odd n: side 1 shadows side 0
+                const int uj = sel4(ul, jj);
                 const double mu = __shfl_sync(FULL, mu_l, 6 * jj + 4);
-                const uint4 wb = rng_quad(cfg.seed, K_SE, sel4(ul, jj), lane, frame, episode, gid);
-                float y0, y1, y2, y3;
-                normal_pair(wb.x, wb.y, y0, y1);
-                normal_pair(wb.z, wb.w, y2, y3);
-                double2* out = reinterpret_cast<double2*>(sm[wib][jj] + 4 * lane);
-                out[0] = make_double2(fabs(__fma_rn(1.5, (double)y0, mu)), fabs(__fma_rn(1.5, (double)y1, mu)));
-                out[1] = make_double2(fabs(__fma_rn(1.5, (double)y2, mu)), fabs(__fma_rn(1.5, (double)y3, mu)));
+                const int rs = __shfl_sync(FULL, rb_s, uj), re = rs + __shfl_sync(FULL, rb_c, uj);
+                const int l16 = lane & 15, base = ((l16 >> 3) << 6) + (l16 & 7);
+                double acc_se = 0.0, acc_t = 0.0;
+                double* se_out = A.raw.se_used ? A.raw.se_used + ((size_t)e * U + uj) * R : nullptr;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const uint4 wb = rng_quad(cfg.seed, K_SE, uj, 2 * l16 + h, frame, episode, gid);
+                    float y[4];
+                    normal_pair(wb.x, wb.y, y[0], y[1]);
+                    normal_pair(wb.z, wb.w, y[2], y[3]);
+#pragma unroll
+                    for (int w = 0; w < 4; ++w) {
+                        const int r = base + 8 * (4 * h + w);
+                        const double x = fabs(__fma_rn(1.5, (double)y[w], mu)); // channels/mimic_quadriga.py:49-56
+                        const double t = (r >= rs && r < re) ? A.bw_rb * x : 0.0; // ((BW/R) * sched) * SE
+                        if (h == 0 && w == 0) { acc_se = x; acc_t = t; }
+                        else { acc_se += x; acc_t += t; }
+                        if (se_out) se_out[r] = x;
+                    }
+                }
+                acc_se = acc_se + __shfl_down_sync(FULL, acc_se, 1);
+                acc_t = acc_t + __shfl_down_sync(FULL, acc_t, 1);
+                acc_se = acc_se + __shfl_down_sync(FULL, acc_se, 2);
+                acc_t = acc_t + __shfl_down_sync(FULL, acc_t, 2);
+                acc_se = acc_se + __shfl_down_sync(FULL, acc_se, 4);
+                acc_t = acc_t + __shfl_down_sync(FULL, acc_t, 4);
+                if (l16 == 8) { // second half: the 7-element tail is added serially after the tree
+                    const double* tail = sm[wib][jj] + 128;
+#pragma unroll
+                    for (int k = 0; k < 7; ++k) {
+                        const double x = tail[k];
+                        acc_se += x;
+                        acc_t += (128 + k >= rs && 128 + k < re) ? A.bw_rb * x : 0.0;
+                    }
+                }
+                if (se_out && l16 < 7) se_out[128 + l16] = sm[wib][jj][128 + l16];
+                const double res_se = 0. + (acc_se + __shfl_down_sync(FULL, acc_se, 8)); // valid on lanes 0, 16
+                const double res_t = 0. + (acc_t + __shfl_down_sync(FULL, acc_t, 8));
+#pragma unroll
+                for (int sd = 0; sd < 2; ++sd) {
+                    const double a = __shfl_sync(FULL, res_t, 16 * sd), b = __shfl_sync(FULL, res_se, 16 * sd);
+                    if (2 * pp + sd < n && lane == sel4(ul, 2 * pp + sd)) { sum_t = a; sum_se = b; }
+                }
             }
+            __syncwarp();
+            continue;
         } else {
 #pragma unroll 1
             for (int jj = 0; jj < n; ++jj) {

@@ -33,6 +33,16 @@ __device__ __forceinline__ uint4 rng_quad(uint64_t seed, int kind, int ue, int q
     return philox4x32_10(c, (uint32_t)seed, (uint32_t)(seed >> 32));
 }
 
+// Where word w of SE quad q lands in the 135-RB row.  Quads 0..31 are laid out so that the two
+// quads 2m, 2m+1 hold exactly the 8 elements one accumulator of NumPy's pairwise sum visits
+// (row half m >> 3, accumulator m & 7: elements half * 64 + (m & 7) + 8k, k = 0..7 in order), so a
+// lane that generates both quads can add them up in registers in NumPy's order; quads 32, 33
+// are the serial tail 128..134 (word 3 of quad 33 is unused).
+__host__ __device__ __forceinline__ int se_index(int q, int w)
+{
+    return q < 32 ? ((q >> 4) << 6) + ((q >> 1) & 7) + 8 * (4 * (q & 1) + w) : 4 * q + w;
+}
+
 // Two standard normals from two 32-bit words: Box-Muller in binary32 with a fixed polynomial
 // log (atanh series on the mantissa) and octant-reduced sin/cos polynomials; no libm, no
 // fast-math intrinsics, so the result is a pure function of IEEE add/mul/fma/div/sqrt.
@@ -100,7 +110,7 @@ __device__ __noinline__ void native_se_row(uint64_t seed, int ue, int frame, int
         normal_pair(w.z, w.w, z[2], z[3]);
 #pragma unroll
         for (int j = 0; j < 4; ++j)
-            if (4 * q + j < R) se[4 * q + j] = fabs(__fma_rn(1.5, (double)z[j], mu));
+            if (se_index(q, j) < R) se[se_index(q, j)] = fabs(__fma_rn(1.5, (double)z[j], mu));
     }
 }
 
@@ -155,8 +165,7 @@ __device__ __noinline__ double native_row(uint64_t seed, const double* cdf_all, 
     const uint4 wb = rng_quad(seed, K_SE, ue, lane, frame, episode, gid);
     normal_pair(wb.x, wb.y, z[0], z[1]);
     normal_pair(wb.z, wb.w, z[2], z[3]);
-    double2* out = reinterpret_cast<double2*>(se + 4 * lane);
-    out[0] = make_double2(fabs(__fma_rn(1.5, (double)z[0], mu)), fabs(__fma_rn(1.5, (double)z[1], mu)));
-    out[1] = make_double2(fabs(__fma_rn(1.5, (double)z[2], mu)), fabs(__fma_rn(1.5, (double)z[3], mu)));
+#pragma unroll
+    for (int j = 0; j < 4; ++j) se[se_index(lane, j)] = fabs(__fma_rn(1.5, (double)z[j], mu));
     return traffic;
 }

@@ -154,6 +154,12 @@ static double native_mu(const orc_config *cfg, int ue, int episode, int gid)
     normal_pair(w[0], w[1], &z0, &z1);
     return fabs(fma(7.5, (double)z0, 10.0));
 }
+/* where word w of SE quad q lands in the row: quads 2m, 2m+1 hold the 8 elements that accumulator
+ * m & 7 of half m >> 3 of NumPy's pairwise sum visits, in order; quads 32, 33 are the tail 128..134 */
+static int se_index(int q, int w)
+{
+    return q < 32 ? ((q >> 4) << 6) + ((q >> 1) & 7) + 8 * (4 * (q & 1) + w) : 4 * q + w;
+}
 /* channels/mimic_quadriga.py:49-56: SE[u,r] = abs(N(mu_u, 1.5)) */
 static void native_se_row(const orc_config *cfg, int ue, int frame, int episode, int gid, double *se)
 {
@@ -164,7 +170,7 @@ static void native_se_row(const orc_config *cfg, int ue, int frame, int episode,
         normal_pair(w[0], w[1], &z[0], &z[1]);
         normal_pair(w[2], w[3], &z[2], &z[3]);
         for (int j = 0; j < 4; ++j)
-            if (4 * q + j < R) se[4 * q + j] = fabs(fma(1.5, (double)z[j], mu));
+            if (se_index(q, j) < R) se[se_index(q, j)] = fabs(fma(1.5, (double)z[j], mu));
     }
 }
 /* traffics/mult_slice.py:28-31: Poisson(lambda) * 1e6 bits, by table inversion */
