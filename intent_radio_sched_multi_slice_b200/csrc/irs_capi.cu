@@ -243,6 +243,7 @@ static int launch_step(irs_env* env, const StepArgs& A, cudaStream_t st, bool pr
     if (profile) CK(cudaEventRecord(env->ev[1], st));
     const long long rows = (long long)E * U;
     if (env->mode == 1) k_ue_step<<<(unsigned)((rows + UE_WARPS - 1) / UE_WARPS), UE_WARPS * 32, 0, st>>>(A);
+    else if (A.raw.se_used) k_ue_env_raw<<<(E + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(A);
     else k_ue_env<<<(E + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(A);
     if (profile) CK(cudaEventRecord(env->ev[2], st));
     k_env_tail<<<(E + ENV_WARPS - 1) / ENV_WARPS, ENV_WARPS * 32, 0, st>>>(A);

@@ -43,7 +43,7 @@ __device__ __forceinline__ T sel4(const T (&a)[GRP], int j)
 // FULL_STEP = false: only the per-UE middle of the step (what k_ue_step does per row), between
 //                    k_action and k_env_tail; every warp of the GPU then runs the same, much
 //                    smaller code region, which the instruction cache holds.
-template <bool FULL_STEP>
+template <bool FULL_STEP, bool RAWSE>
 __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GRP][136])
 {
     const DevState& st = A.st;
@@ -88,57 +88,64 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
     const int fl_mine = s_mine >= 0 ? __ldg(&sc->sl[s_mine].flags) : 0;
     const bool has_traffic = (fl_mine & IRS_F_REQ) != 0;
     const int lam_idx = has_traffic ? __ldg(&sc->sl[s_mine].lam_idx) : 0;
-    double sum_t = 0.0, sum_se = 0.0, traffic = 0.0;
+    double sum_t = 0.0, sum_se = 0.0, traffic = 0.0, mu_l = 0.0;
     if (!native) {
         if (cfg.traffic_mode == 0) traffic = ue_lane ? A.traffic[eu] : 0.0;
         else if (has_traffic) traffic = native_traffic(cfg.seed, st.cdf, lane, lam_idx, frame, episode, gid);
     }
-    uint32_t todo = __ballot_sync(FULL, ue_lane && (native ? s_mine >= 0 : true));
-    while (FUSED_SYNC >= 2 ? __syncthreads_or(todo != 0) : (todo != 0)) { // warp-uniform (block-uniform when synced)
-        int ul[GRP], n = 0;
+    if (native) {
+        // Per-warp scratch in shared memory: tail (SE, throughput term) pairs of the group's rows at
+        // ws[16 j .. 16 j + 13], per-UE results (sum_t, sum_se, traffic) at ws[64 + 4 u ..].
+        double* ws = &sm[wib][0][0];
+        uint32_t todo = __ballot_sync(FULL, ue_lane && s_mine >= 0);
+        while (FUSED_SYNC >= 2 ? __syncthreads_or(todo != 0) : (todo != 0)) { // warp-uniform (block-uniform when synced)
+            uint32_t ulp = 0; // lane ids of the group's UEs, one byte each
+            int n = 0;
 #pragma unroll
-        for (int j = 0; j < GRP; ++j) {
-            ul[j] = todo ? (__ffs(todo) - 1) : 0;
-            if (todo) { ++n; todo &= todo - 1; }
-        }
-        if (native) {
-            // auxiliary pass: lane 6j+k serves UE j of the group
-            const int j = lane / 6, k = lane - 6 * j;
-            const bool valid = lane < 6 * GRP && j < n;
-            const int ue_j = sel4(ul, j < GRP ? j : 0);
-            const int kind = k < 4 ? K_SE : (k == 4 ? K_MU : K_TRAFFIC);
-            const int q = k < 2 ? 32 : (k < 4 ? 33 : 0);
-            const uint4 w = rng_quad(cfg.seed, kind, ue_j, q, k == 4 ? 0 : frame, episode, gid);
-            const bool hi_pair = k < 4 && (k & 1);
-            float z0, z1;
-            normal_pair(hi_pair ? w.z : w.x, hi_pair ? w.w : w.y, z0, z1);
-            const double mu_l = fabs(__fma_rn(7.5, (double)z0, 10.0)); // meaningful on k == 4
-            const double mu_aux = __shfl_sync(FULL, mu_l, (valid ? 6 * j : 0) + 4);
-            if (valid && k < 4) {
-                double* se = sm[wib][j];
-                const int i0 = 4 * q + 2 * (k & 1);
-                se[i0] = fabs(__fma_rn(1.5, (double)z0, mu_aux));
-                if (i0 + 1 < R) se[i0 + 1] = fabs(__fma_rn(1.5, (double)z1, mu_aux));
-            }
-            // Poisson arrival of UE j on lane 6j+5 (traffics/mult_slice.py:28-31)
-            const int lam_j = __shfl_sync(FULL, lam_idx, ue_j);
-            const int ht_j = __shfl_sync(FULL, (int)has_traffic, ue_j);
-            int lo = 0;
-            if (valid && k == 5 && ht_j) {
-                const double u01 = ((double)(w.x >> 5) * 67108864.0 + (double)(w.y >> 6)) * (1.0 / 9007199254740992.0);
-                const double* cdf = st.cdf + (size_t)lam_j * IRS_POISSON_K;
+            for (int j = 0; j < GRP; ++j)
+                if (todo) { ulp |= (uint32_t)(__ffs(todo) - 1) << (8 * j); ++n; todo &= todo - 1; }
+            // auxiliary pass: lane 6j+k serves UE j of the group - k < 4: a pair of the tail elements
+            // 128..134 (half of quad 32 / 33), k == 4: the per-episode mean, k == 5: the Poisson arrival
+            {
+                const int j = lane / 6, k = lane - 6 * j;
+                const bool valid = j < n;
+                const int ue_j = (ulp >> (8 * (j & 3))) & 31;
+                const int kind = k < 4 ? K_SE : (k == 4 ? K_MU : K_TRAFFIC);
+                const int q = k < 2 ? 32 : (k < 4 ? 33 : 0);
+                const uint4 w = rng_quad(cfg.seed, kind, ue_j, q, k == 4 ? 0 : frame, episode, gid);
+                const bool hi_pair = k < 4 && (k & 1);
+                float z0, z1;
+                normal_pair(hi_pair ? w.z : w.x, hi_pair ? w.w : w.y, z0, z1);
+                mu_l = fabs(__fma_rn(7.5, (double)z0, 10.0)); // meaningful on k == 4 (mimic_quadriga.py:37-41)
+                const double mu_aux = __shfl_sync(FULL, mu_l, (valid ? 6 * j : 0) + 4);
+                const int rs_a = __shfl_sync(FULL, rb_s, ue_j), rc_a = __shfl_sync(FULL, rb_c, ue_j);
+                if (valid && k < 4) {
+                    const int t0 = 4 * (q - 32) + 2 * (k & 1); // tail index 0, 2, 4, 6 -> RB 128 + t0
+                    double2* tp = reinterpret_cast<double2*>(ws + 16 * j);
+                    const double x0 = fabs(__fma_rn(1.5, (double)z0, mu_aux));
+                    tp[t0] = make_double2(x0, (unsigned)(128 + t0 - rs_a) < (unsigned)rc_a ? A.bw_rb * x0 : 0.0);
+                    if (t0 + 1 < 7) {
+                        const double x1 = fabs(__fma_rn(1.5, (double)z1, mu_aux));
+                        tp[t0 + 1] = make_double2(x1, (unsigned)(129 + t0 - rs_a) < (unsigned)rc_a ? A.bw_rb * x1 : 0.0);
+                    }
+                }
+                // Poisson arrival of UE j on lane 6j+5 (traffics/mult_slice.py:28-31)
+                const int lam_j = __shfl_sync(FULL, lam_idx, ue_j);
+                const int ht_j = __shfl_sync(FULL, (int)has_traffic, ue_j);
+                if (valid && k == 5) {
+                    int lo = 0;
+                    if (ht_j) {
+                        const double u01 = ((double)(w.x >> 5) * 67108864.0 + (double)(w.y >> 6)) * (1.0 / 9007199254740992.0);
+                        const double* cdf = st.cdf + (size_t)lam_j * IRS_POISSON_K;
 #pragma unroll
-                for (int stp = IRS_POISSON_K / 2; stp > 0; stp >>= 1)
-                    if (__ldg(&cdf[lo + stp - 1]) <= u01) lo += stp;
-                if (__ldg(&cdf[lo]) <= u01) lo += 1;
+                        for (int stp = IRS_POISSON_K / 2; stp > 0; stp >>= 1)
+                            if (__ldg(&cdf[lo + stp - 1]) <= u01) lo += stp;
+                        if (__ldg(&cdf[lo]) <= u01) lo += 1;
+                    }
+                    ws[64 + 4 * ue_j + 2] = (double)lo * 1e6;
+                }
             }
-            const double tr_l = (double)lo * 1e6;
-#pragma unroll
-            for (int jj = 0; jj < GRP; ++jj) {
-                const double t = __shfl_sync(FULL, tr_l, 6 * jj + 5);
-                if (jj < n && lane == ul[jj]) traffic = t;
-            }
-            __syncwarp(); // tail elements 128..134 of the group's rows are in shared memory
+            __syncwarp();
             // pair passes: lanes 0..15 serve UE ul[2p], lanes 16..31 UE ul[2p+1].  Lane m of a side
             // generates SE quads 2m, 2m+1 = the 8 elements accumulator m & 7 of row half m >> 3
             // visits (se_index), and adds them up in registers in NumPy's order: both 135-term
@@ -146,13 +153,15 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
 #pragma unroll 1
             for (int pp = 0; 2 * pp < n; ++pp) {
                 const int side = lane >> 4;
-                const int jj = (2 * pp + side < n) ? 2 * pp + side : 2 * pp; // odd n: side 1 shadows side 0
-                const int uj = sel4(ul, jj);
+                const bool live = 2 * pp + side < n;      // odd n: side 1 of the last pass shadows side 0
+                const int jj = live ? 2 * pp + side : 2 * pp;
+                const int uj = (ulp >> (8 * jj)) & 31;
                 const double mu = __shfl_sync(FULL, mu_l, 6 * jj + 4);
-                const int rs = __shfl_sync(FULL, rb_s, uj), re = rs + __shfl_sync(FULL, rb_c, uj);
+                const int rs = __shfl_sync(FULL, rb_s, uj), rc = __shfl_sync(FULL, rb_c, uj);
                 const int l16 = lane & 15, base = ((l16 >> 3) << 6) + (l16 & 7);
+                const unsigned d0 = (unsigned)(base - rs);
                 double acc_se = 0.0, acc_t = 0.0;
-                double* se_out = A.raw.se_used ? A.raw.se_used + ((size_t)e * U + uj) * R : nullptr;
+                double* se_out = (RAWSE && A.raw.se_used) ? A.raw.se_used + ((size_t)e * U + uj) * R : nullptr;
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
                     const uint4 wb = rng_quad(cfg.seed, K_SE, uj, 2 * l16 + h, frame, episode, gid);
@@ -161,12 +170,11 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
                     normal_pair(wb.z, wb.w, y[2], y[3]);
 #pragma unroll
                     for (int w = 0; w < 4; ++w) {
-                        const int r = base + 8 * (4 * h + w);
                         const double x = fabs(__fma_rn(1.5, (double)y[w], mu)); // channels/mimic_quadriga.py:49-56
-                        const double t = (r >= rs && r < re) ? A.bw_rb * x : 0.0; // ((BW/R) * sched) * SE
+                        const double t = (d0 + 8u * (4 * h + w) < (unsigned)rc) ? A.bw_rb * x : 0.0; // ((BW/R) * sched) * SE
                         if (h == 0 && w == 0) { acc_se = x; acc_t = t; }
                         else { acc_se += x; acc_t += t; }
-                        if (se_out) se_out[r] = x;
+                        if (RAWSE && se_out) se_out[base + 8 * (4 * h + w)] = x;
                     }
                 }
                 acc_se = acc_se + __shfl_down_sync(FULL, acc_se, 1);
@@ -175,33 +183,41 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
                 acc_t = acc_t + __shfl_down_sync(FULL, acc_t, 2);
                 acc_se = acc_se + __shfl_down_sync(FULL, acc_se, 4);
                 acc_t = acc_t + __shfl_down_sync(FULL, acc_t, 4);
+                const double2* tp = reinterpret_cast<const double2*>(ws + 16 * jj);
                 if (l16 == 8) { // second half: the 7-element tail is added serially after the tree
-                    const double* tail = sm[wib][jj] + 128;
 #pragma unroll
                     for (int k = 0; k < 7; ++k) {
-                        const double x = tail[k];
-                        acc_se += x;
-                        acc_t += (128 + k >= rs && 128 + k < re) ? A.bw_rb * x : 0.0;
+                        const double2 xt = tp[k];
+                        acc_se += xt.x;
+                        acc_t += xt.y;
                     }
                 }
-                if (se_out && l16 < 7) se_out[128 + l16] = sm[wib][jj][128 + l16];
+                if (RAWSE && se_out && l16 < 7) se_out[128 + l16] = tp[l16].x;
                 const double res_se = 0. + (acc_se + __shfl_down_sync(FULL, acc_se, 8)); // valid on lanes 0, 16
                 const double res_t = 0. + (acc_t + __shfl_down_sync(FULL, acc_t, 8));
-#pragma unroll
-                for (int sd = 0; sd < 2; ++sd) {
-                    const double a = __shfl_sync(FULL, res_t, 16 * sd), b = __shfl_sync(FULL, res_se, 16 * sd);
-                    if (2 * pp + sd < n && lane == sel4(ul, 2 * pp + sd)) { sum_t = a; sum_se = b; }
-                }
+                if (l16 == 0 && live) *reinterpret_cast<double2*>(ws + 64 + 4 * uj) = make_double2(res_t, res_se);
             }
             __syncwarp();
-            continue;
-        } else {
+        }
+        if (ue_lane && s_mine >= 0) {
+            const double2 r2 = *reinterpret_cast<const double2*>(ws + 64 + 4 * lane);
+            sum_t = r2.x; sum_se = r2.y;
+            traffic = ws[64 + 4 * lane + 2];
+        }
+    } else {
+    uint32_t todo = __ballot_sync(FULL, ue_lane);
+    while (FUSED_SYNC >= 2 ? __syncthreads_or(todo != 0) : (todo != 0)) { // warp-uniform (block-uniform when synced)
+        int ul[GRP], n = 0;
+#pragma unroll
+        for (int j = 0; j < GRP; ++j) {
+            ul[j] = todo ? (__ffs(todo) - 1) : 0;
+            if (todo) { ++n; todo &= todo - 1; }
+        }
 #pragma unroll 1
-            for (int jj = 0; jj < n; ++jj) {
-                const int uj = sel4(ul, jj);
-                const int assoc = __shfl_sync(FULL, (int)(s_mine >= 0), uj);
-                channel_row(A, e, uj, assoc != 0, frame, episode, sm[wib][jj]);
-            }
+        for (int jj = 0; jj < n; ++jj) {
+            const int uj = sel4(ul, jj);
+            const int assoc = __shfl_sync(FULL, (int)(s_mine >= 0), uj);
+            channel_row(A, e, uj, assoc != 0, frame, episode, sm[wib][jj]);
         }
         __syncwarp();
 #pragma unroll 1
@@ -211,12 +227,13 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
             const double sums = np_sum135_thr_se(sm[wib][jj], rs, rs + rc, A.bw_rb);
             const double a = __shfl_sync(FULL, sums, 0), b = __shfl_sync(FULL, sums, 16);
             if (lane == uj) { sum_t = a; sum_se = b; }
-            if (A.raw.se_used)
+            if (RAWSE && A.raw.se_used)
                 for (int r = lane; r < R; r += 32) A.raw.se_used[((size_t)e * U + uj) * R + r] = sm[wib][jj][r];
         }
         __syncwarp();
     }
-    if (native && A.raw.se_used) { // unassociated UEs have SE 0 in native mode
+    }
+    if (RAWSE && native && A.raw.se_used) { // unassociated UEs have SE 0 in native mode
         for (int u = 0; u < U; ++u) {
             if (__shfl_sync(FULL, s_mine, u) >= 0) continue;
             for (int r = lane; r < R; r += 32) A.raw.se_used[((size_t)e * U + u) * R + r] = 0.0;
@@ -299,7 +316,7 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
 __global__ void __launch_bounds__(FUSED_WARPS * 32, FUSED_MINB) k_env_step(const __grid_constant__ StepArgs A)
 {
     __shared__ __align__(16) double sm[FUSED_WARPS][GRP][136];
-    env_step_body<true>(A, sm);
+    env_step_body<true, true>(A, sm);
 }
 
 #ifndef UE_ENV_MINB
@@ -308,5 +325,11 @@ __global__ void __launch_bounds__(FUSED_WARPS * 32, FUSED_MINB) k_env_step(const
 __global__ void __launch_bounds__(FUSED_WARPS * 32, UE_ENV_MINB) k_ue_env(const __grid_constant__ StepArgs A)
 {
     __shared__ __align__(16) double sm[FUSED_WARPS][GRP][136];
-    env_step_body<false>(A, sm);
+    env_step_body<false, false>(A, sm);
+}
+// same kernel with the optional per-RB SE output (irs_raw_outputs.se_used; tests and trace dumps)
+__global__ void __launch_bounds__(FUSED_WARPS * 32, UE_ENV_MINB) k_ue_env_raw(const __grid_constant__ StepArgs A)
+{
+    __shared__ __align__(16) double sm[FUSED_WARPS][GRP][136];
+    env_step_body<false, true>(A, sm);
 }
