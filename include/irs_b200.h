@@ -72,7 +72,8 @@ typedef struct {
 typedef struct {
     int32_t num_envs;
     int32_t depth_cap;       /* max buffer depth (buffer_latency + 1) of any scenario row */
-    int32_t channel_mode;    /* 0 SE injected per call, 1 fixed_se (2.0), 2 native mimic_quadriga */
+    int32_t channel_mode;    /* 0 SE injected per call, 1 fixed_se (2.0), 2 native mimic_quadriga,
+                                3 device-resident SE trace bank (irs_set_se_trace; channels/quadriga.py) */
     int32_t traffic_mode;    /* 0 traffic (bits) injected per call, 1 native Poisson */
     int32_t sort_slices;     /* IBSched.enable_sort_slices (ib_sched.py:57); MARR/MAPF: 0 */
     int32_t fixed_intra;     /* -1 per-slice action (player_1..5), 0 rr, 1 pf, 2 mt */
@@ -187,6 +188,24 @@ int irs_step_profiled(irs_env* env, const irs_actions* actions_dev, const irs_in
 /* gym's reset(seed=...) (comm_env.py:398-413): re-key the native generators.  Takes effect for
  * the next reset/step; does not touch the state. */
 int irs_set_seed(irs_env* env, uint64_t seed);
+
+/* channel_mode 3 - QuadrigaChannel / QuadrigaChannelSeq (channels/quadriga.py:38-87,
+ * channels/quadriga_seq.py:28-39) as a device-resident trace: `se_bank_dev` is f64
+ * [n_episodes][n_steps][25][135], owned by the caller and kept alive while the env uses it.  An env
+ * in episode `ep` at step counter `k` reads frame [ep % n_episodes][min(k, n_steps-1)]: like the
+ * reference, reset and the first step of an episode both read frame 0 (comm_env.py:303-305,449-451
+ * call channel.step with the step counter before it is incremented).  The (association, episode)
+ * file choice of choose_episode (quadriga.py:79-87, quadriga_seq.py:28-39) is the order in which
+ * the caller lays the episodes out in the bank. */
+int irs_set_se_trace(irs_env* env, const double* se_bank_dev, int32_t n_episodes, int32_t n_steps);
+
+/* The per-frame transform of QuadrigaChannel.step (channels/quadriga.py:56-74):
+ *   SE = log2(1 + ((tx_power / 135) * p) / (0 + noise_power)),
+ * over `n_frames` frames of 25 x 135 powers.  layout 0: each input frame is [135][25] (UE fastest:
+ * the order h5py sees in target_cell_power.mat, which the reference transposes), layout 1: [25][135].
+ * Output frames are always [25][135].  Device pointers; asynchronous on `stream`. */
+int irs_power_to_se(const double* power_dev, double* se_dev, int64_t n_frames, int32_t layout, double tx_power,
+                    double noise_power, void* stream);
 /* n steps back to back with the on-device policy (cfg.policy != 0) and native generators. */
 int irs_run(irs_env* env, int32_t n_steps, void* stream);
 /* Same as irs_step but actions come from host memory and the env surface is copied back to

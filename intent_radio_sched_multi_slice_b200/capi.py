@@ -80,6 +80,8 @@ SYMBOLS = {
     "irs_step_profiled": (C.c_int, [_P, C.POINTER(Actions), C.POINTER(Inject), C.POINTER(RawOutputs), _P,
                                     C.POINTER(C.c_float)]),
     "irs_set_seed": (C.c_int, [_P, C.c_uint64]),
+    "irs_set_se_trace": (C.c_int, [_P, _P, C.c_int32, C.c_int32]),
+    "irs_power_to_se": (C.c_int, [_P, _P, C.c_int64, C.c_int32, C.c_double, C.c_double, _P]),
     "irs_run": (C.c_int, [_P, C.c_int32, _P]),
     "irs_step_host": (C.c_int, [_P, C.POINTER(Actions), C.POINTER(HostSurface), _P]),
     "irs_reset_host": (C.c_int, [_P, C.c_int32, C.POINTER(HostSurface), _P]),

@@ -28,6 +28,8 @@ struct irs_env {
     cudaEvent_t chunk_ev[IRS_MAX_HOST_CHUNKS];
     bool have_copy;
     int host_chunks;               // IRS_HOST_CHUNKS (0 = choose from the batch size)
+    const double* se_bank;         // channel_mode 3 (irs_set_se_trace)
+    int32_t bank_eps, bank_steps;
     int mode; // IRS_STEP_MODE: 0 fused k_env_step, 1 k_action + k_ue_step (warp per row) + k_env_tail,
               //                2 k_action + k_ue_env (warp per env) + k_env_tail
     char err[256];
@@ -84,9 +86,30 @@ static StepArgs make_args(const irs_env* env)
     A.cfg = env->cfg;
     A.bw_rb = env->cfg.bandwidth / (double)R; // ues.py:110
     A.initial_episode = -1;
+    A.se_bank = env->se_bank;
+    A.bank_eps = env->bank_eps;
+    A.bank_steps = env->bank_steps;
     A.env_begin = 0;
     A.env_end = env->cfg.num_envs;
     return A;
+}
+
+// channels/quadriga.py:56-74: SE = log2(1 + ((P_tx / R) * p) / (0 + N0)); one block per frame, the
+// [R][U] file order transposed to [U][R] through shared memory so both sides stay coalesced.
+__global__ void __launch_bounds__(256) k_power_to_se(const double* __restrict__ power, double* __restrict__ se, int layout,
+                                                     double tx_per_rb, double noise)
+{
+    __shared__ double tile[U * R];
+    const double* in = power + (size_t)blockIdx.x * (U * R);
+    double* out = se + (size_t)blockIdx.x * (U * R);
+    const double den = 0.0 + noise; // intercell_interference (zeros) + thermal_noise_power
+    for (int i = threadIdx.x; i < U * R; i += blockDim.x) {
+        const double v = log2(1.0 + (tx_per_rb * in[i]) / den);
+        if (layout == 0) { const int r = i / U, u = i - r * U; tile[u * R + r] = v; }
+        else tile[i] = v;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < U * R; i += blockDim.x) out[i] = tile[i];
 }
 
 extern "C" {
@@ -98,7 +121,7 @@ int irs_create(const irs_config* cfg, int32_t n_lambda, irs_env** out)
     if (!cfg || !out) return IRS_ERR_ARG;
     *out = nullptr;
     if (cfg->num_envs <= 0 || cfg->depth_cap <= 0 || cfg->n_scen <= 0 || cfg->max_steps <= 0 ||
-        cfg->channel_mode < 0 || cfg->channel_mode > 2 || cfg->traffic_mode < 0 || cfg->traffic_mode > 1 ||
+        cfg->channel_mode < 0 || cfg->channel_mode > 3 || cfg->traffic_mode < 0 || cfg->traffic_mode > 1 ||
         cfg->policy < 0 || cfg->policy > 3 || cfg->fixed_intra < -1 || cfg->fixed_intra > 2 ||
         (cfg->assoc_mode == 0 && cfg->scen_mod <= 0) || (cfg->assoc_mode == 1 && cfg->scen_div <= 0) ||
         cfg->assoc_mode < 0 || cfg->assoc_mode > 1 || !(cfg->bandwidth > 0) ||
@@ -207,6 +230,7 @@ static int check_ready(irs_env* env, const irs_inject* inj)
     if (!env) return IRS_ERR_ARG;
     if (!env->bound || !env->loaded) return fail(env, IRS_ERR_UNBOUND, "irs_bind and irs_load_scenarios first");
     if (env->cfg.channel_mode == 0 && !(inj && inj->se)) return fail(env, IRS_ERR_ARG, "channel_mode 0 needs inject.se");
+    if (env->cfg.channel_mode == 3 && !env->se_bank) return fail(env, IRS_ERR_ARG, "channel_mode 3 needs irs_set_se_trace");
     return IRS_OK;
 }
 
@@ -300,6 +324,31 @@ int irs_set_seed(irs_env* env, uint64_t seed)
     return IRS_OK;
 }
 
+int irs_set_se_trace(irs_env* env, const double* se_bank_dev, int32_t n_episodes, int32_t n_steps)
+{
+    if (!env) return IRS_ERR_ARG;
+    if (!se_bank_dev || n_episodes <= 0 || n_steps <= 0) return fail(env, IRS_ERR_ARG, "irs_set_se_trace: empty bank");
+    if (((uintptr_t)se_bank_dev & 7) != 0) return fail(env, IRS_ERR_ARG, "irs_set_se_trace: bank must be 8-byte aligned");
+    env->se_bank = se_bank_dev;
+    env->bank_eps = n_episodes;
+    env->bank_steps = n_steps;
+    return IRS_OK;
+}
+
+int irs_power_to_se(const double* power_dev, double* se_dev, int64_t n_frames, int32_t layout, double tx_power,
+                    double noise_power, void* stream)
+{
+    if (!power_dev || !se_dev || n_frames < 0 || layout < 0 || layout > 1 || !(noise_power > 0)) return IRS_ERR_ARG;
+    if (n_frames == 0) return IRS_OK;
+    const long long per_launch = 1ll << 30;
+    for (long long f0 = 0; f0 < n_frames; f0 += per_launch) {
+        const long long nf = n_frames - f0 < per_launch ? n_frames - f0 : per_launch;
+        k_power_to_se<<<(unsigned)nf, 256, 0, (cudaStream_t)stream>>>(power_dev + f0 * U * R, se_dev + f0 * U * R, layout,
+                                                                        tx_power / (double)R, noise_power);
+    }
+    return cudaGetLastError() == cudaSuccess ? IRS_OK : IRS_ERR_CUDA;
+}
+
 int irs_run(irs_env* env, int32_t n_steps, void* stream)
 {
     int rc = check_ready(env, nullptr);
@@ -358,7 +407,7 @@ int irs_step_host(irs_env* env, const irs_actions* actions_host, const irs_host_
 {
     int rc = check_ready(env, nullptr);
     if (rc) return rc;
-    if (env->cfg.channel_mode == 0 || env->cfg.traffic_mode == 0) return fail(env, IRS_ERR_ARG, "irs_step_host needs native or fixed generators");
+    if (env->cfg.channel_mode == 0 || env->cfg.traffic_mode == 0) return fail(env, IRS_ERR_ARG, "irs_step_host needs device-side channel and traffic (channel_mode 1/2/3, traffic_mode 1)");
     if (!out_host) return IRS_ERR_ARG;
     cudaStream_t st = (cudaStream_t)stream;
     const size_t E = (size_t)env->cfg.num_envs;

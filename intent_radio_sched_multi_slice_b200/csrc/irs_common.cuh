@@ -56,6 +56,8 @@ struct StepArgs {
     const int32_t* intra;  // or NULL
     const double* se;      // injected SE or NULL
     const double* traffic; // injected traffic or NULL
+    const double* se_bank; // channel_mode 3: [bank_eps][bank_steps][U][R] SE trace (irs_set_se_trace)
+    int32_t bank_eps, bank_steps;
     irs_raw_outputs raw;   // optional extra outputs (all may be NULL)
     const uint8_t* reset_mask;
     const int32_t* initial_episode_dev;
@@ -239,6 +241,13 @@ __device__ __forceinline__ int scen_of_episode(const irs_config& c, int episode)
 {
     const int s = c.assoc_mode == 0 ? episode % c.scen_mod : episode / c.scen_div;
     return s % c.n_scen;
+}
+
+// channel_mode 3: the SE frame env state (episode, step counter k) reads (channels/quadriga.py:38-87)
+__device__ __forceinline__ const double* trace_frame(const StepArgs& A, int episode, int k)
+{
+    const int f = k < A.bank_steps ? k : A.bank_steps - 1;
+    return A.se_bank + ((size_t)(episode % A.bank_eps) * A.bank_steps + (size_t)(f < 0 ? 0 : f)) * (U * R);
 }
 
 // per-UE buffer parameters: the UE's slice (associations/mult_slice.py:468-488 update_ues);

@@ -204,6 +204,72 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
             sum_t = r2.x; sum_se = r2.y;
             traffic = ws[64 + 4 * lane + 2];
         }
+    } else if (cfg.channel_mode != 2) {
+        // Rows that come from memory (injected frame, SE trace bank) or are constant (fixed_se):
+        // the same two-UEs-per-pass register reduction, each lane loading the 8 elements of its
+        // accumulator straight from global memory (every 32-byte sector fully used).  Rows of
+        // unassociated UEs are not read: their RB run is empty, so their throughput is 0 whatever
+        // the row holds (ues.py:108-116), and their mean SE is never observed (ib_sched.py:111,147).
+        const double* frame_base = nullptr;
+        if (cfg.channel_mode == 0) frame_base = A.se + (size_t)e * U * R;
+        else if (cfg.channel_mode == 3) frame_base = trace_frame(A, episode, step);
+        double* ws = &sm[wib][0][0];
+        const bool all_rows = RAWSE && A.raw.se_used;
+        uint32_t todo = __ballot_sync(FULL, ue_lane && (s_mine >= 0 || all_rows));
+        while (FUSED_SYNC >= 2 ? __syncthreads_or(todo != 0) : (todo != 0)) {
+            const int u0 = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const bool live1 = todo != 0;
+            const int u1 = live1 ? __ffs(todo) - 1 : u0;
+            todo &= todo - 1;
+            const int side = lane >> 4;
+            const int uj = side ? u1 : u0;
+            const bool live = side ? live1 : true;
+            const int rs = __shfl_sync(FULL, rb_s, uj), rc = __shfl_sync(FULL, rb_c, uj);
+            const int l16 = lane & 15, base = ((l16 >> 3) << 6) + (l16 & 7);
+            const unsigned d0 = (unsigned)(base - rs);
+            const double* rowp = frame_base ? frame_base + (size_t)uj * R : nullptr;
+            double x[8], xt[7];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) x[k] = rowp ? __ldg(rowp + base + 8 * k) : 2.0; // channels/fixed_se.py:26
+#pragma unroll
+            for (int k = 0; k < 7; ++k) xt[k] = (l16 == 8 || all_rows) ? (rowp ? __ldg(rowp + 128 + k) : 2.0) : 0.0;
+            double acc_se = x[0];
+            double acc_t = (d0 < (unsigned)rc) ? A.bw_rb * x[0] : 0.0; // ((BW/R) * sched) * SE, ues.py:108-116
+#pragma unroll
+            for (int k = 1; k < 8; ++k) {
+                acc_se += x[k];
+                acc_t += (d0 + 8u * k < (unsigned)rc) ? A.bw_rb * x[k] : 0.0;
+            }
+            acc_se = acc_se + __shfl_down_sync(FULL, acc_se, 1);
+            acc_t = acc_t + __shfl_down_sync(FULL, acc_t, 1);
+            acc_se = acc_se + __shfl_down_sync(FULL, acc_se, 2);
+            acc_t = acc_t + __shfl_down_sync(FULL, acc_t, 2);
+            acc_se = acc_se + __shfl_down_sync(FULL, acc_se, 4);
+            acc_t = acc_t + __shfl_down_sync(FULL, acc_t, 4);
+            if (l16 == 8) { // second half: 7-element tail added serially after the tree
+#pragma unroll
+                for (int k = 0; k < 7; ++k) {
+                    acc_se += xt[k];
+                    acc_t += ((unsigned)(128 + k - rs) < (unsigned)rc) ? A.bw_rb * xt[k] : 0.0;
+                }
+            }
+            const double res_se = 0. + (acc_se + __shfl_down_sync(FULL, acc_se, 8)); // valid on lanes 0, 16
+            const double res_t = 0. + (acc_t + __shfl_down_sync(FULL, acc_t, 8));
+            if (l16 == 0 && live) *reinterpret_cast<double2*>(ws + 64 + 4 * uj) = make_double2(res_t, res_se);
+            if (all_rows && live) {
+                double* se_out = A.raw.se_used + ((size_t)e * U + uj) * R;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) se_out[base + 8 * k] = x[k];
+                if (l16 == 8)
+                    for (int k = 0; k < 7; ++k) se_out[128 + k] = xt[k];
+            }
+        }
+        __syncwarp();
+        if (ue_lane && (s_mine >= 0 || all_rows)) {
+            const double2 r2 = *reinterpret_cast<const double2*>(ws + 64 + 4 * lane);
+            sum_t = r2.x; sum_se = r2.y;
+        }
     } else {
     uint32_t todo = __ballot_sync(FULL, ue_lane);
     while (FUSED_SYNC >= 2 ? __syncthreads_or(todo != 0) : (todo != 0)) { // warp-uniform (block-uniform when synced)

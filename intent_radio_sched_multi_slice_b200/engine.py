@@ -118,6 +118,34 @@ class BatchEngine:
             t = torch.from_numpy(np.ascontiguousarray(x)).to(device=self.device, dtype=dtype)
         return t
 
+    # -- channel_mode 3: device-resident SE trace (channels/quadriga.py) ------------------------
+    def set_se_trace(self, se_bank: torch.Tensor):
+        """Bind a float64 [n_episodes, n_steps, 25, 135] SE bank living on this engine's device
+        (irs_set_se_trace).  The engine keeps a reference so the memory outlives its use."""
+        if se_bank.dtype != torch.float64 or se_bank.dim() != 4 or tuple(se_bank.shape[2:]) != (U, R):
+            raise ValueError("se_bank must be float64 [n_episodes, n_steps, 25, 135]")
+        if se_bank.device != self.device or not se_bank.is_contiguous():
+            raise ValueError("se_bank must be a contiguous tensor on the engine's device")
+        self._se_bank = se_bank
+        capi.check(self.h, self.lib.irs_set_se_trace(self.h, se_bank.data_ptr(), se_bank.shape[0], se_bank.shape[1]))
+
+    def power_to_se(self, power: torch.Tensor, layout: int = 0, tx_power: float = 100.0, noise_power: float = 10e-14):
+        """QuadrigaChannel.step's transform (channels/quadriga.py:56-74) over a device tensor of
+        target-cell powers [..., 135, 25] (layout 0, the .mat file order) or [..., 25, 135]
+        (layout 1); returns float64 [..., 25, 135] spectral efficiencies."""
+        want = (R, U) if layout == 0 else (U, R)
+        if power.dtype != torch.float64 or tuple(power.shape[-2:]) != want or power.device != self.device:
+            raise ValueError(f"power must be float64 [..., {want[0]}, {want[1]}] on the engine's device")
+        power = power.contiguous()
+        out = torch.empty(tuple(power.shape[:-2]) + (U, R), dtype=torch.float64, device=self.device)
+        n = power.numel() // (U * R)
+        with torch.cuda.device(self.device):
+            rc = self.lib.irs_power_to_se(power.data_ptr(), out.data_ptr(), n, int(layout), float(tx_power),
+                                          float(noise_power), self._stream())
+        capi.check(self.h, rc)
+        self._keep_power = power
+        return out
+
     # -- the path ---------------------------------------------------------------------------
     def reset(self, mask=None, initial_episode=-1, initial_episodes=None, se=None):
         """CommunicationEnv.reset for the masked envs (comm_env.py:375-482)."""

@@ -32,7 +32,7 @@ class BatchedMARLCommEnv:
                  calculate_reward=None, obs_space=None, action_space=None, debug=True, root_path=".",
                  initial_episode_number=0, max_episode_number=None, simu_name=None, save_hist=True,
                  enable_random_episodes=False, *, num_envs=1, device="cuda:0", scenario_bank=None,
-                 auto_reset=None, env_id_base=0):
+                 auto_reset=None, env_id_base=0, channel_episodes=None):
         path = os.path.join(root_path, "env_config", f"{config_file}.yml")
         if not os.path.exists(path):
             path = os.path.join(HERE, "env_config", f"{config_file}.yml")
@@ -77,6 +77,7 @@ class BatchedMARLCommEnv:
         self.bank = scenario_bank
         self.auto_reset = (self.num_envs > 1) if auto_reset is None else bool(auto_reset)
         self.env_id_base = env_id_base
+        self.channel_episodes = channel_episodes  # channel_mode 3: env episodes whose files form the SE bank
         self.agents = {f"player_{i}" for i in range(self.max_number_slices + 1)}  # marl_comm_env.py:20-24
         self._agent_ids = set(self.agents)
         self.comm_env = self  # the reference exposes the wrapped CommunicationEnv here
@@ -113,6 +114,14 @@ class BatchedMARLCommEnv:
                                    max_episodes=self.max_number_episodes, initial_episode=self.initial_episode_number,
                                    auto_reset=int(self.auto_reset), env_id_base=self.env_id_base, seed=self.seed,
                                    bandwidth=float(self.bandwidths[0]), **kw)
+            if kw["channel_mode"] == 3:  # QuadrigaChannel[Seq]: transform the power files once, keep SE in HBM
+                ch = self.ChannelClass if hasattr(self.ChannelClass, "power_bank") else \
+                    plugins.BUILTIN[self.ChannelClass.__name__]
+                eps = self.channel_episodes if self.channel_episodes is not None else \
+                    range(self.initial_episode_number, self.initial_episode_number + 1)
+                power = torch.from_numpy(ch.power_bank(self.root_path, eps)).to(self.device)
+                self.eng.set_se_trace(self.eng.power_to_se(power, layout=0, tx_power=ch.transmission_power,
+                                                           noise_power=ch.thermal_noise_power))
         return self.eng
 
     # ---- host tensor hooks (slow path; any Channel/Traffic class) -------------------------------

@@ -61,6 +61,84 @@ class FixedSE:
         return 2.0 * np.ones(self.shape)
 
 
+class QuadrigaChannel:
+    """channels/quadriga.py:8-87: per step, SE = log2(1 + ((100 W / 135) * target_cell_power) / 1e-13)
+    from `<root>/mult_slice_channel_generation/results/mult_slice/freq_channel/assoc_A/ep_E/
+    target_cell_power.mat`, with (A, E) = (episode, 0).
+
+    Device mode: the files of `episodes` are transformed once (irs_power_to_se) into a float64
+    [n_episodes, n_steps, 25, 135] bank that stays in HBM (irs_set_se_trace, channel_mode 3); an env in
+    episode `ep` reads bank slot `ep % n_episodes`.  Supply the powers either as .mat files under
+    root_path (needs h5py, like the reference) or through `register_power(power)` with an array
+    [n_episodes, n_steps, 135, 25] (the file order) - e.g. synthetic or pre-converted data."""
+    device_mode = {"channel_mode": 3}
+    transmission_power, thermal_noise_power = 100.0, 10e-14  # quadriga.py:33-34
+    channel_eps_per_scenario = 100
+    _registered = None
+
+    def __init__(self, max_number_ues, max_number_basestations, num_available_rbs, rng=np.random.default_rng(),
+                 root_path="", scenario_name="mult_slice"):
+        self.root_path = root_path
+        self.num_available_rbs = num_available_rbs
+        self.current_episode_number, self._power = -1, None
+
+    @classmethod
+    def register_power(cls, power):
+        """Use an in-memory array [n_episodes, n_steps, 135, 25] instead of .mat files."""
+        power = np.ascontiguousarray(power, np.float64)
+        if power.ndim != 4 or power.shape[2:] != (135, 25):
+            raise ValueError("power must be [n_episodes, n_steps, 135, 25] (target_cell_power.mat order)")
+        cls._registered = power
+
+    @classmethod
+    def choose_episode(cls, episode_number):
+        """(association, episode) of the file an env episode reads (quadriga.py:79-87)."""
+        return episode_number, 0
+
+    @classmethod
+    def channels_path(cls, root_path):
+        return os.path.join(root_path, "mult_slice_channel_generation", "results", "mult_slice", "freq_channel")
+
+    @classmethod
+    def read_file(cls, root_path, episode_number):
+        """One file as [n_steps, 135, 25] float64 (h5py order of simu.m:103's array, singletons dropped)."""
+        try:
+            import h5py
+        except ImportError as exc:
+            raise RuntimeError("reading target_cell_power.mat needs h5py; use register_power(array) instead") from exc
+        a, e = cls.choose_episode(episode_number)
+        with h5py.File(os.path.join(cls.channels_path(root_path), f"assoc_{a}", f"ep_{e}", "target_cell_power.mat"), "r") as f:
+            return np.asarray(f["target_cell_power"], np.float64)[:, :, 0, 0, :]
+
+    @classmethod
+    def power_bank(cls, root_path, episodes):
+        """Powers of `episodes` (env episode numbers) as [len(episodes), n_steps, 135, 25]."""
+        if cls._registered is not None:
+            return cls._registered
+        return np.stack([cls.read_file(root_path, ep) for ep in episodes])
+
+    def step(self, step_number, episode_number, mobilities, sched_decision=None):
+        """Host-side value with the reference's semantics (not used on the device path)."""
+        if episode_number != self.current_episode_number:
+            self.current_episode_number = episode_number
+            bank = type(self)._registered
+            self._power = (bank[episode_number % len(bank)] if bank is not None
+                           else self.read_file(self.root_path, episode_number))
+        p = self._power[step_number]
+        se = np.log2(1 + np.divide((self.transmission_power / self.num_available_rbs[0]) * p,
+                                   (np.zeros_like(p) + self.thermal_noise_power)))
+        return np.array([se.transpose()])
+
+
+class QuadrigaChannelSeq(QuadrigaChannel):
+    """channels/quadriga_seq.py:8-39: (association, episode) = (episode // 100, episode % 100)."""
+    _registered = None
+
+    @classmethod
+    def choose_episode(cls, episode_number):
+        return episode_number // cls.channel_eps_per_scenario, episode_number % cls.channel_eps_per_scenario
+
+
 # ---- traffic --------------------------------------------------------------------------------
 class MultSliceTraffic:
     """traffics/mult_slice.py:8-34: Poisson(slice traffic in Mbps) * 1e6 bits per UE of every
@@ -133,7 +211,7 @@ class MultSliceAssociationSeq(MultSliceAssociation):
     device_mode = {"assoc_mode": 1, "scen_div": 100}
 
 
-BUILTIN = {c.__name__: c for c in (MimicQuadriga, FixedSE, MultSliceTraffic, SimpleMobility, MultSliceAssociation,
+BUILTIN = {c.__name__: c for c in (MimicQuadriga, FixedSE, QuadrigaChannel, QuadrigaChannelSeq, MultSliceTraffic, SimpleMobility, MultSliceAssociation,
                                    MultSliceAssociationSeq)}
 
 

@@ -78,6 +78,8 @@ typedef struct {
     int32_t *buf; /* [E][U][depth_cap] age histograms (buffer.py:47) */
     const orc_scenario *bank;
     const double *poisson_cdf; /* [n_lambda][POISSON_K] */
+    const double *se_bank;     /* channel_mode 3: [bank_eps][bank_steps][U][R] (channels/quadriga.py) */
+    int32_t bank_eps, bank_steps;
 } orc_handle;
 
 /* ------------------------------------------------------------------------------------
@@ -760,6 +762,12 @@ static void channel_frame(const orc_handle *h, int e, const orc_env *env, int fr
     const orc_scenario *sc = &h->bank[env->scen];
     if (h->cfg.channel_mode == 0) {
         memcpy(se, se_in + (size_t)e * U * R, sizeof(double) * U * R);
+    } else if (h->cfg.channel_mode == 3) {
+        /* channels/quadriga.py:38-77: the file of this episode, frame = the env's step counter
+         * (0 at reset AND at the first step: comm_env.py:303-305 runs before step_number += 1) */
+        int k = frame > 0 ? frame - 1 : 0;
+        if (k >= h->bank_steps) k = h->bank_steps - 1;
+        memcpy(se, h->se_bank + ((size_t)(env->episode % h->bank_eps) * h->bank_steps + k) * U * R, sizeof(double) * U * R);
     } else if (h->cfg.channel_mode == 1) {
         for (int i = 0; i < U * R; ++i) se[i] = 2.0; /* channels/fixed_se.py:26 */
     } else {
@@ -867,6 +875,21 @@ orc_handle *orc_create(const orc_config *cfg, const orc_scenario *bank, const do
         for (int s = 0; s < S; ++s) h->envs[e].sorted_slices[s] = s; /* ib_sched.py:58 */
     }
     return h;
+}
+void orc_set_se_trace(orc_handle *h, const double *bank, int32_t n_eps, int32_t n_steps)
+{
+    h->se_bank = bank; h->bank_eps = n_eps; h->bank_steps = n_steps;
+}
+/* channels/quadriga.py:56-74 on one frame in file order [R][U] -> SE [U][R] */
+void orc_power_to_se(const double *power, double *se, int64_t n_frames, int layout, double tx_power, double noise)
+{
+    const double c = tx_power / (double)R, den = 0.0 + noise;
+    for (int64_t f = 0; f < n_frames; ++f)
+        for (int i = 0; i < U * R; ++i) {
+            double v = log2(1.0 + (c * power[f * U * R + i]) / den);
+            if (layout == 0) { int r = i / U, u = i - r * U; se[f * U * R + u * R + r] = v; }
+            else se[f * U * R + i] = v;
+        }
 }
 void orc_destroy(orc_handle *h) { if (h) { free(h->envs); free(h->buf); free(h); } }
 int orc_reset(orc_handle *h, const uint8_t *mask, int initial_episode, const double *se, const orc_io *io)

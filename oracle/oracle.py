@@ -54,6 +54,8 @@ def lib():
         _lib.orc_create.restype = C.c_void_p
         _lib.orc_create.argtypes = [C.POINTER(Config), C.c_void_p, C.c_void_p]
         _lib.orc_destroy.argtypes = [C.c_void_p]
+        _lib.orc_set_se_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32]
+        _lib.orc_power_to_se.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_double, C.c_double]
         _lib.orc_reset.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.POINTER(IO)]
         _lib.orc_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(IO)]
         _lib.orc_buffers.restype = C.POINTER(C.c_int32)
@@ -84,6 +86,14 @@ def buffer_main(max_pkts, max_age, arrivals, send_per_step):
     sent = np.zeros(n, np.int64)
     delay = lib().orc_buffer_main(max_pkts, max_age, _ptr(arr), n, send_per_step, _ptr(rows), _ptr(dropped), _ptr(sent))
     return rows, dropped, sent, delay
+
+
+def power_to_se(power, layout=0, tx_power=100.0, noise=10e-14):
+    """channels/quadriga.py:56-74 over frames [..., 135, 25] (layout 0) or [..., 25, 135] (layout 1)."""
+    p = np.ascontiguousarray(power, np.float64)
+    out = np.empty(p.shape[:-2] + (U, R))
+    lib().orc_power_to_se(_ptr(p), _ptr(out), p.size // (U * R), layout, tx_power, noise)
+    return out
 
 
 def np_sum(a):
@@ -141,6 +151,12 @@ class OracleEnv:
             "se_used": None, "traffic_used": np.zeros((E, U)),
         }
         self._io = None
+
+    def set_se_trace(self, se_bank):
+        """channel_mode 3: float64 [n_episodes, n_steps, 25, 135] (kept alive by this object)."""
+        self._se_bank = np.ascontiguousarray(se_bank, np.float64)
+        assert self._se_bank.ndim == 4 and self._se_bank.shape[2:] == (U, R)
+        lib().orc_set_se_trace(self.h, _ptr(self._se_bank), self._se_bank.shape[0], self._se_bank.shape[1])
 
     def want_se(self):
         self.out["se_used"] = np.zeros((self.E, U, R))

@@ -46,6 +46,9 @@ TRACES = {
     "seq_mimic": ("ib_sched", "mimic", "mult_slice_seq", 14, 98, 240, 40, None, 3),
     "seq_fixed": ("ib_sched", "fixed", "mult_slice_seq", 15, 99, 160, 40, None, 4),
     "sweep_scen": ("ib_sched", "mimic", "mult_slice", 16, 20, 600, 25, 36, 5),
+    # QuadrigaChannel / QuadrigaChannelSeq over synthetic power files (shims._install_h5py)
+    "quadriga": ("ib_sched", "quadriga", "mult_slice", 17, 3, 100, 30, None, 6),
+    "quadriga_seq": ("ib_sched", "quadriga_seq", "mult_slice_seq", 18, 99, 100, 30, None, 7),
 }
 
 
@@ -59,6 +62,7 @@ def record(name):
         os.makedirs(dst, exist_ok=True)
         if not os.path.exists(f"{dst}/mult_slice"):
             os.symlink(src, f"{dst}/mult_slice")
+    shims.QUADRIGA_STEPS["n"] = max_steps
     env, ag = refenv.make_env(wd, agent=agent, channel=channel, assoc=assoc, seed=seed,
                               initial_episode=init_ep, max_episode_number=max_eps)
     fn = policy if act_seed is None else rand_actions(act_seed)
@@ -72,6 +76,9 @@ def record(name):
         "meta_numpy": np.array(np.__version__),
         "se_checksum": bits_checksum(steps["se"]), "reset_se_checksum": bits_checksum(resets["se"]),
     }
+    if channel.startswith("quadriga"):
+        out["se_sum"] = steps["se"].reshape(len(steps["se"]), -1).sum(1)
+        out["reset_se_sum"] = resets["se"].reshape(len(resets["se"]), -1).sum(1)
     for k, v in steps.items():
         if k != "se":
             out[k] = v

@@ -116,6 +116,7 @@ def install():
     for name in ("matplotlib", "matplotlib.figure", "matplotlib.pyplot", "matplotlib.pylab"):
         m = _mod(name)
         m.__getattr__ = lambda k: _Any()  # type: ignore
+    _install_h5py()
     for pkg in ("agents", "channels", "traffics", "associations", "mobilities"):
         m = types.ModuleType(pkg)
         m.__path__ = [f"{REF}/{pkg}"]
@@ -123,6 +124,37 @@ def install():
     for p in (REF, f"{REF}/sixg_radio_mgmt"):
         if p not in sys.path:
             sys.path.insert(0, p)
+
+
+QUADRIGA_STEPS = {"n": 1000}  # frames per synthetic target_cell_power.mat
+
+
+def _install_h5py():
+    """h5py is absent and the QuaDRiGa channel files are an external MATLAB product.  The stand-in
+    serves the synthetic recipe of tests/golden_inputs.quadriga_power for the path the reference
+    opens (channels/quadriga.py:52-55: .../assoc_A/ep_E/target_cell_power.mat); the reference's
+    own indexing, transform and transposition (quadriga.py:56-77) run unmodified on it."""
+    import os
+    import re
+
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))), "tests"))
+
+    class File:
+        def __init__(self, path, mode="r"):
+            import golden_inputs
+
+            m = re.search(r"assoc_(\d+)/ep_(\d+)/target_cell_power.mat$", path)
+            assert m, path
+            self.data = golden_inputs.quadriga_power(int(m.group(1)), int(m.group(2)), QUADRIGA_STEPS["n"])
+
+        def get(self, name):
+            assert name == "target_cell_power"
+            return self.data
+
+        def close(self):
+            self.data = None
+
+    _mod("h5py", File=File)
 
 
 _orig_argsort = np.argsort

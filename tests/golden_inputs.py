@@ -22,6 +22,29 @@ U, S, R = 25, 5, 135
 _LAMBDA = [5, 10, 30, 15, 10, 100, 20, 100, 50, 30]
 
 
+QUADRIGA_TX_POWER, QUADRIGA_NOISE = 100.0, 10e-14  # channels/quadriga.py:33-34
+
+
+def quadriga_power(assoc: int, ep: int, n_steps: int):
+    """Synthetic stand-in for mult_slice_channel_generation/.../assoc_A/ep_E/target_cell_power.mat
+    (the real files are an external QuaDRiGa/MATLAB product): a fixed recipe, in the order h5py
+    shows the MATLAB array of simu.m:103 - [step][rb][sector=1][1][ue]."""
+    rng = np.random.default_rng(7_000_000 + 1000 * int(assoc) + int(ep))
+    return 10.0 ** rng.uniform(-13.5, -9.5, size=(n_steps, R, 1, 1, U))
+
+
+def quadriga_file_of_episode(channel: str, episode: int):
+    """choose_episode of channels/quadriga.py:79-87 / channels/quadriga_seq.py:28-39."""
+    return (episode, 0) if channel == "quadriga" else (episode // 100, episode % 100)
+
+
+def quadriga_se_numpy(power_frame):
+    """channels/quadriga.py:56-77 on one frame [R,1,1,U] -> [U,R], NumPy restatement."""
+    se = np.log2(1 + np.divide((QUADRIGA_TX_POWER / np.array([R])[0]) * power_frame,
+                               (np.zeros_like(power_frame) + QUADRIGA_NOISE)))
+    return np.squeeze(se.transpose())
+
+
 def load_scenarios():
     f = np.load(os.path.join(GOLDEN, "scenarios_seed10.npz"))
     return f["slice_type"], f["ue_slice"]
@@ -35,8 +58,18 @@ class FrameSource:
         self.channel = channel
         self.slice_type, self.ue_slice = slice_type, ue_slice
         self.mu = None
+        self.n_steps = None  # quadriga channels: frames per file
+        self._files = {}
 
-    def _se(self):
+    def _quadriga(self, episode, k):
+        key = quadriga_file_of_episode(self.channel, episode)
+        if key not in self._files:
+            self._files = {key: quadriga_power(key[0], key[1], self.n_steps)}
+        return quadriga_se_numpy(self._files[key][k])
+
+    def _se(self, episode=None, k=None):
+        if self.channel.startswith("quadriga"):
+            return self._quadriga(episode, k)
         if self.channel == "fixed":
             return 2.0 * np.ones((U, R))
         se = np.empty((U, R))
@@ -53,15 +86,15 @@ class FrameSource:
                 out[idx] = self.rng.poisson(_LAMBDA[t], len(idx)) * 1e6
         return out
 
-    def reset_frame(self, scen):
+    def reset_frame(self, scen, episode=None):
         if self.channel == "mimic":  # a fresh channel object per reset -> means are redrawn
             self.mu = np.abs(self.rng.normal(10, 7.5, size=(U,)))
-        se = self._se()
+        se = self._se(episode, 0)
         self._traffic(scen)  # drawn and discarded (comm_env.py:468-473)
         return se
 
-    def step_frame(self, scen):
-        se = self._se()
+    def step_frame(self, scen, episode=None, k=None):
+        se = self._se(episode, k)
         return se, self._traffic(scen)
 
 
@@ -90,16 +123,30 @@ def regenerate(meta, d):
     st, us = load_scenarios()
     src = FrameSource(meta["seed"], meta["channel"], st, us)
     n = int(meta["n_steps"])
+    src.n_steps = int(meta["max_steps"])
     reset_se, step_se, step_tr = [], np.empty((n, U, R)), np.empty((n, U))
     ri = 0
-    reset_se.append(src.reset_frame(scen_of_episode(meta, int(d["reset_episode"][0]))))
+    ep0 = int(d["reset_episode"][0])
+    reset_se.append(src.reset_frame(scen_of_episode(meta, ep0), ep0))
+    k_in_ep = 0  # the env's step counter when channel.step is called (comm_env.py:303-305)
     for k in range(n):
-        scen = scen_of_episode(meta, int(d["episode"][k]))
-        step_se[k], step_tr[k] = src.step_frame(scen)
+        ep = int(d["episode"][k])
+        step_se[k], step_tr[k] = src.step_frame(scen_of_episode(meta, ep), ep, k_in_ep)
+        k_in_ep += 1
         if d["done"][k]:
             ri += 1
-            reset_se.append(src.reset_frame(scen_of_episode(meta, int(d["reset_episode"][ri]))))
+            epr = int(d["reset_episode"][ri])
+            reset_se.append(src.reset_frame(scen_of_episode(meta, epr), epr))
+            k_in_ep = 0
     reset_se = np.stack(reset_se)
+    if meta["channel"].startswith("quadriga"):
+        # np.log2 may round differently on another CPU (SIMD dispatch): frames are pinned by their
+        # sums to 1e-13 instead of by bit patterns
+        np.testing.assert_allclose(step_se.reshape(n, -1).sum(1), d["se_sum"], rtol=1e-13)
+        np.testing.assert_allclose(reset_se.reshape(len(reset_se), -1).sum(1), d["reset_se_sum"], rtol=1e-13)
+        if not np.array_equal(step_tr, d["traffic"]):
+            raise AssertionError("regenerated traffic frames do not match the fixture")
+        return reset_se, step_se, step_tr
     if not np.array_equal(bits_checksum(step_se), d["se_checksum"]):
         raise AssertionError("regenerated SE frames do not match the fixture checksum (NumPy RNG stream differs)")
     if not np.array_equal(bits_checksum(reset_se), d["reset_se_checksum"]):
@@ -107,3 +154,16 @@ def regenerate(meta, d):
     if not np.array_equal(step_tr, d["traffic"]):
         raise AssertionError("regenerated traffic frames do not match the fixture")
     return reset_se, step_se, step_tr
+
+
+def quadriga_bank_powers(meta, d, n_eps=8):
+    """Target-cell powers of the files a quadriga trace visits, laid out as an SE-trace bank wants
+    them: [n_eps][T][135][25] (file order per frame), slot = episode % n_eps, unused slots zero."""
+    T = int(meta["max_steps"])
+    eps = sorted(set(d["episode"].tolist()) | set(d["reset_episode"].tolist()))
+    assert len({e % n_eps for e in eps}) == len(eps)
+    power = np.zeros((n_eps, T, R, U))
+    for e in eps:
+        a, f = quadriga_file_of_episode(meta["channel"], int(e))
+        power[e % n_eps] = quadriga_power(a, f, T)[:, :, 0, 0, :]
+    return power

@@ -63,7 +63,7 @@ def test_create_layout_destroy_without_gpu():
     assert lib.irs_destroy(h) == 0
 
 
-@pytest.mark.parametrize("bad", [dict(num_envs=0), dict(channel_mode=3), dict(policy=9), dict(fixed_intra=3),
+@pytest.mark.parametrize("bad", [dict(num_envs=0), dict(channel_mode=4), dict(policy=9), dict(fixed_intra=3),
                                  dict(bandwidth=0.0), dict(assoc_mode=1, scen_div=0)])
 def test_create_rejects_bad_config(bad):
     lib = capi.load()

@@ -39,7 +39,8 @@ def _trace_plugins(rse, sse, stf):
 
 
 @pytest.mark.parametrize("name,agent,n", [("ibsched_mimic", "IBSched", 150), ("seq_fixed", "IBSched", 100),
-                                          ("cfg1_marr", "MARR", 120), ("mapf", "MAPF", 120)])
+                                          ("cfg1_marr", "MARR", 120), ("mapf", "MAPF", 120),
+                                          ("quadriga", "IBSched", 100), ("quadriga_seq", "IBSched", 100)])
 def test_env_api_replays_reference_trace(name, agent, n, bank):
     from intent_radio_sched_multi_slice_b200 import agents, plugins
     from intent_radio_sched_multi_slice_b200.env import MARLCommEnv
@@ -47,6 +48,9 @@ def test_env_api_replays_reference_trace(name, agent, n, bank):
     meta, d = golden_inputs.load_trace(name)
     rse, sse, stf = golden_inputs.regenerate(meta, d)
     Ch, Tr, state = _trace_plugins(rse, sse, stf)
+    if meta["channel"].startswith("quadriga"):  # the built-in device channel: SE bank in HBM (channel_mode 3)
+        Ch = plugins.QuadrigaChannel if meta["channel"] == "quadriga" else plugins.QuadrigaChannelSeq
+        Ch.register_power(golden_inputs.quadriga_bank_powers(meta, d))
     Assoc = plugins.MultSliceAssociation if meta["assoc"] == "mult_slice" else plugins.MultSliceAssociationSeq
     env = MARLCommEnv(Ch, Tr, plugins.SimpleMobility, Assoc, "mult_slice", agent.lower(), int(meta["seed"]),
                       root_path="/nonexistent", initial_episode_number=int(meta["initial_episode"]),
