@@ -35,7 +35,9 @@ def parse():
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
     p.add_argument("--envs", type=int, default=65536, help="env instances per GPU (weak scaling)")
     p.add_argument("--depth", type=int, default=0, help="force every UE to a deep buffer profile (config 5 sweep)")
-    p.add_argument("--workload", default="mix", choices=["mix", "cfg2"])
+    p.add_argument("--workload", default="mix", choices=["mix", "cfg2", "trace"],
+                   help="mix: native generators (default); cfg2: 1,024 envs; trace: QuadrigaChannel-shaped SE bank in HBM")
+    p.add_argument("--trace-steps", type=int, default=16, help="frames per episode of the SE bank (wraps around)")
     p.add_argument("--cpu-envs", type=int, default=2048, help="env instances of the CPU baseline sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
@@ -65,7 +67,7 @@ def make_bank(depth: int):
 
 
 def engine_kwargs(args, rank):
-    return dict(channel_mode=2, traffic_mode=1, sort_slices=1, fixed_intra=-1, policy=0, assoc_mode=0,
+    return dict(channel_mode=3 if args.workload == "trace" else 2, traffic_mode=1, sort_slices=1, fixed_intra=-1, policy=0, assoc_mode=0,
                 scen_mod=200, max_steps=1000, max_episodes=10000, auto_reset=1, seed=10,
                 env_id_base=rank * args.envs)
 
@@ -129,6 +131,10 @@ def cpu_oracle_run(args, bank, n_envs, warmup, steps=None, budget_s=12.0):
     rng = np.random.default_rng(1234)
     pool = [(rng.uniform(-1, 1, (n_envs, 5)), rng.integers(0, 3, (n_envs, 5)).astype(np.int32)) for _ in range(4)]
     m = np.ones(n_envs, np.uint8)
+    if args.workload == "trace":  # one bank slot per env, like the GPU arm
+        power = 10.0 ** rng.uniform(-13.5, -9.5, (n_envs, args.trace_steps, 135, 25))
+        env.set_se_trace(oracle.power_to_se(power, layout=0))
+        del power
     for e0 in range(200):  # stagger the scenarios like the GPU arm: env e starts at episode e % 200
         m[:] = (np.arange(n_envs) % 200) == e0
         if m.any():
@@ -194,7 +200,29 @@ def run_b200(args):
     bank, wl = make_bank(args.depth)
     eng = BatchEngine(bank, E, device=dev, depth_cap=max(bank.max_depth(), 101), **engine_kwargs(args, rank))
     gid = torch.arange(E, device=dev, dtype=torch.int32) + rank * E
-    eng.reset(initial_episodes=(gid % 200).to(torch.int32), initial_episode=0)
+    trace_bytes = 0
+    if args.workload == "trace":
+        # QuadrigaChannel-shaped input: every env reads its own episode file, so each step streams
+        # E distinct 25 x 135 float64 frames from HBM.  Synthetic target-cell powers (10^U(-13.5,-9.5) W)
+        # go through the library's own transform (channels/quadriga.py:56-74) chunk by chunk.
+        T = args.trace_steps
+        se_bank = torch.empty((E, T, U, 135), dtype=torch.float64, device=dev)
+        g0 = torch.Generator(device=dev)
+        g0.manual_seed(77 + rank)
+        chunk = max(1, (1 << 28) // (T * U * 135))
+        for c0 in range(0, E, chunk):
+            n = min(chunk, E - c0)
+            power = torch.pow(10.0, torch.rand((n, T, 135, U), generator=g0, device=dev, dtype=torch.float64) * 4.0 - 13.5)
+            eng.power_to_se(power, layout=0, out=se_bank[c0:c0 + n])
+        torch.cuda.synchronize(dev)
+        del power
+        eng.set_se_trace(se_bank)
+        trace_bytes = se_bank.numel() * 8
+        wl = (f"SE trace channel (QuadrigaChannel-shaped): one {T}-frame episode file per env resident in HBM, "
+              "mult_slice scenario mix (200 scenarios, D 21..401)")
+    # env e starts at episode gid: scenario gid % 200 (and SE bank slot gid % E in the trace workload)
+    eng.reset(initial_episodes=gid.to(torch.int32) if args.workload == "trace" else (gid % 200).to(torch.int32),
+              initial_episode=0)
     g = torch.Generator(device=dev)
     g.manual_seed(1234 + rank)
     pool = [(torch.rand(E, 5, generator=g, device=dev, dtype=torch.float64) * 2 - 1,
@@ -247,6 +275,7 @@ def run_b200(args):
             if s_ >= 0:
                 depth_tab[i, u] = int(arr["sl"]["buffer_latency"][i, s_]) + 1
     depth_tab_t = torch.from_numpy(depth_tab).to(dev)
+    assoc_tab_t = torch.from_numpy((arr["ue_slice"][:, :U] >= 0).astype(np.int64)).to(dev)
     P = max(3, min(K, 20))
     kms = np.zeros(3)
     ue_bytes = 0.0
@@ -260,6 +289,8 @@ def run_b200(args):
         path = eng.v["path"].long()
         dep = depth_tab_t[eng.v["scen"].long()]
         row_b = torch.where(path == 2, 8 * dep, torch.where(path == 1, 4 * dep, torch.full_like(dep, 4)))
+        if args.workload == "trace":  # + the 135 float64 SE values of every associated UE's row
+            row_b = row_b + 1080 * assoc_tab_t[eng.v["scen"].long()]
         ue_bytes += float((row_b + FIXED_ROW_BYTES).sum().item())
         path_frac += np.array([(path == i).float().mean().item() for i in range(3)])
     kms /= P
@@ -274,17 +305,18 @@ def run_b200(args):
     achieved = ue_bytes / (kms[1] * 1e-3) / 1e9
     traffic = None
     try:
-        tj = json.load(open(os.path.join(ROOT, "profiles", "ue_step_traffic.json")))
-        if tj.get("envs") == E and tj.get("depth", 0) == args.depth:
-            traffic = tj["dram_bytes_per_launch"]
+        for tj in json.load(open(os.path.join(ROOT, "profiles", "ue_step_traffic.json"))):  # ncu --set full captures
+            if tj.get("envs") == E and tj.get("depth", 0) == args.depth and tj.get("workload", "mix") == args.workload:
+                traffic = tj["dram_bytes_per_launch"]
     except Exception:
         pass
-    roofline = {"bound": "hbm", "kernel": "k_ue_step", "achieved": achieved, "peak": peak, "unit": "GB/s",
+    roofline = {"bound": "hbm", "kernel": "k_ue_env", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic,
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650 GB/s",
                 "algorithmic_bytes_per_launch": ue_bytes, "kernel_ms": kms[1],
-                "kernel_ms_all": {"k_action": kms[0], "k_ue_step": kms[1], "k_env_tail": kms[2]},
-                "bytes_per_ue_row": "%d (per-UE records) + buffer row: 8*D_u streamed, 4*D_u zero-filled, 4 empty" % FIXED_ROW_BYTES,
+                "kernel_ms_all": {"k_action": kms[0], "k_ue_env": kms[1], "k_env_tail": kms[2]},
+                "bytes_per_ue_row": ("%d (per-UE records) + buffer row: 8*D_u streamed, 4*D_u zero-filled, 4 empty" % FIXED_ROW_BYTES)
+                + (" + 1080 (SE row) per associated UE" if args.workload == "trace" else ""),
                 "row_paths": {"empty": path_frac[0], "zero_fill": path_frac[1], "stream": path_frac[2]}}
 
     # ---- e2e: host actions in, host surface out, through irs_step_host ------------------------
@@ -339,7 +371,8 @@ def run_b200(args):
             "vs_baseline": None, "dtype": "i32 buffers + f64", "data": "synthetic",
             "config": {"workload": wl, "envs_per_gpu": E, "ues_per_env": U, "active_ues_per_env": active,
                        "surface": "IBSched dict obs + action masks + 6 rewards, random actions supplied on device",
-                       "channel": "native mimic_quadriga", "traffic": "native Poisson",
+                       "channel": "SE trace bank in HBM (channel_mode 3)" if args.workload == "trace" else "native mimic_quadriga",
+                       "trace_bank_bytes": trace_bytes, "traffic": "native Poisson",
                        "state_bytes_per_gpu": state_bytes,
                        "l2": "state larger than L2" if flush is None else "L2 flushed (256 MB fill) between timed steps"},
             "e2e": e2e, "roofline": roofline, "cpu_baseline": cpu, "gpu_launches": 3 * K, "clocks": clocks,

@@ -192,7 +192,7 @@ int irs_set_seed(irs_env* env, uint64_t seed);
 /* channel_mode 3 - QuadrigaChannel / QuadrigaChannelSeq (channels/quadriga.py:38-87,
  * channels/quadriga_seq.py:28-39) as a device-resident trace: `se_bank_dev` is f64
  * [n_episodes][n_steps][25][135], owned by the caller and kept alive while the env uses it.  An env
- * in episode `ep` at step counter `k` reads frame [ep % n_episodes][min(k, n_steps-1)]: like the
+ * in episode `ep` at step counter `k` reads frame [ep % n_episodes][k % n_steps]: like the
  * reference, reset and the first step of an episode both read frame 0 (comm_env.py:303-305,449-451
  * call channel.step with the step counter before it is incremented).  The (association, episode)
  * file choice of choose_episode (quadriga.py:79-87, quadriga_seq.py:28-39) is the order in which

@@ -246,8 +246,8 @@ __device__ __forceinline__ int scen_of_episode(const irs_config& c, int episode)
 // channel_mode 3: the SE frame env state (episode, step counter k) reads (channels/quadriga.py:38-87)
 __device__ __forceinline__ const double* trace_frame(const StepArgs& A, int episode, int k)
 {
-    const int f = k < A.bank_steps ? k : A.bank_steps - 1;
-    return A.se_bank + ((size_t)(episode % A.bank_eps) * A.bank_steps + (size_t)(f < 0 ? 0 : f)) * (U * R);
+    const int f = (k < 0 ? 0 : k) % A.bank_steps; // a trace shorter than the episode wraps around
+    return A.se_bank + ((size_t)(episode % A.bank_eps) * A.bank_steps + (size_t)f) * (U * R);
 }
 
 // per-UE buffer parameters: the UE's slice (associations/mult_slice.py:468-488 update_ues);

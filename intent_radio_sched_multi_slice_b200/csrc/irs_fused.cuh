@@ -216,7 +216,26 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
         double* ws = &sm[wib][0][0];
         const bool all_rows = RAWSE && A.raw.se_used;
         uint32_t todo = __ballot_sync(FULL, ue_lane && (s_mine >= 0 || all_rows));
+        // L2 prefetch of the rows of the pair after next (lanes 0..9 / 16..25: the <= 10 128-byte lines a
+        // 1080-byte row touches): the loads of a pass then find their rows in L2 instead of waiting on HBM
+        auto prefetch_pair = [&](uint32_t m, int skip_pairs) {
+            if (!frame_base) return;
+            for (int i = 0; i < 2 * skip_pairs; ++i) m &= m - 1;
+            if (!m) return;
+            const int ua = __ffs(m) - 1;
+            m &= m - 1;
+            const int ub = m ? __ffs(m) - 1 : -1;
+            const int up_ = (lane >> 4) ? ub : ua, line = lane & 15;
+            if (up_ >= 0 && line < 10) {
+                const char* row0 = reinterpret_cast<const char*>(frame_base + (size_t)up_ * R);
+                const char* pl = reinterpret_cast<const char*>(reinterpret_cast<uintptr_t>(row0) & ~(uintptr_t)127) + 128 * line;
+                if (pl < row0 + R * 8) asm volatile("prefetch.global.L2 [%0];" ::"l"(pl));
+            }
+        };
+        prefetch_pair(todo, 0);
+        prefetch_pair(todo, 1);
         while (FUSED_SYNC >= 2 ? __syncthreads_or(todo != 0) : (todo != 0)) {
+            prefetch_pair(todo, 2);
             const int u0 = __ffs(todo) - 1;
             todo &= todo - 1;
             const bool live1 = todo != 0;

@@ -129,7 +129,8 @@ class BatchEngine:
         self._se_bank = se_bank
         capi.check(self.h, self.lib.irs_set_se_trace(self.h, se_bank.data_ptr(), se_bank.shape[0], se_bank.shape[1]))
 
-    def power_to_se(self, power: torch.Tensor, layout: int = 0, tx_power: float = 100.0, noise_power: float = 10e-14):
+    def power_to_se(self, power: torch.Tensor, layout: int = 0, tx_power: float = 100.0, noise_power: float = 10e-14,
+                    out: torch.Tensor | None = None):
         """QuadrigaChannel.step's transform (channels/quadriga.py:56-74) over a device tensor of
         target-cell powers [..., 135, 25] (layout 0, the .mat file order) or [..., 25, 135]
         (layout 1); returns float64 [..., 25, 135] spectral efficiencies."""
@@ -137,7 +138,11 @@ class BatchEngine:
         if power.dtype != torch.float64 or tuple(power.shape[-2:]) != want or power.device != self.device:
             raise ValueError(f"power must be float64 [..., {want[0]}, {want[1]}] on the engine's device")
         power = power.contiguous()
-        out = torch.empty(tuple(power.shape[:-2]) + (U, R), dtype=torch.float64, device=self.device)
+        shape = tuple(power.shape[:-2]) + (U, R)
+        if out is None:
+            out = torch.empty(shape, dtype=torch.float64, device=self.device)
+        elif tuple(out.shape) != shape or out.dtype != torch.float64 or not out.is_contiguous() or out.device != self.device:
+            raise ValueError("out must be a contiguous float64 tensor of shape [..., 25, 135] on the engine's device")
         n = power.numel() // (U * R)
         with torch.cuda.device(self.device):
             rc = self.lib.irs_power_to_se(power.data_ptr(), out.data_ptr(), n, int(layout), float(tx_power),

@@ -766,7 +766,7 @@ static void channel_frame(const orc_handle *h, int e, const orc_env *env, int fr
         /* channels/quadriga.py:38-77: the file of this episode, frame = the env's step counter
          * (0 at reset AND at the first step: comm_env.py:303-305 runs before step_number += 1) */
         int k = frame > 0 ? frame - 1 : 0;
-        if (k >= h->bank_steps) k = h->bank_steps - 1;
+        k %= h->bank_steps; /* a trace shorter than the episode wraps around */
         memcpy(se, h->se_bank + ((size_t)(env->episode % h->bank_eps) * h->bank_steps + k) * U * R, sizeof(double) * U * R);
     } else if (h->cfg.channel_mode == 1) {
         for (int i = 0; i < U * R; ++i) se[i] = 2.0; /* channels/fixed_se.py:26 */
