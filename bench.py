@@ -125,7 +125,7 @@ def cpu_oracle_run(args, bank, n_envs, warmup, steps=None, budget_s=12.0):
     kw = engine_kwargs(args, 0)
     kw["env_id_base"] = 0
     cores = os.cpu_count() or 1
-    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    cores = oracle.set_threads(cores)  # explicit: torchrun exports OMP_NUM_THREADS=1
     env = oracle.OracleEnv(bank.array(), bank.poisson_cdf(), n_envs,
                            depth_cap=max(bank.max_depth(), 101), **kw)
     rng = np.random.default_rng(1234)

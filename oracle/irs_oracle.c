@@ -876,6 +876,14 @@ orc_handle *orc_create(const orc_config *cfg, const orc_scenario *bank, const do
     }
     return h;
 }
+#ifdef _OPENMP
+#include <omp.h>
+void orc_set_threads(int n) { if (n > 0) omp_set_num_threads(n); }
+int orc_max_threads(void) { return omp_get_max_threads(); }
+#else
+void orc_set_threads(int n) { (void)n; }
+int orc_max_threads(void) { return 1; }
+#endif
 void orc_set_se_trace(orc_handle *h, const double *bank, int32_t n_eps, int32_t n_steps)
 {
     h->se_bank = bank; h->bank_eps = n_eps; h->bank_steps = n_steps;

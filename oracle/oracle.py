@@ -96,6 +96,12 @@ def power_to_se(power, layout=0, tx_power=100.0, noise=10e-14):
     return out
 
 
+def set_threads(n: int) -> int:
+    """OpenMP threads of orc_step/orc_reset (torchrun exports OMP_NUM_THREADS=1); returns the count in force."""
+    lib().orc_set_threads(int(n))
+    return int(lib().orc_max_threads())
+
+
 def np_sum(a):
     a = np.ascontiguousarray(a, np.float64)
     return lib().orc_np_sum(_ptr(a), a.size)
