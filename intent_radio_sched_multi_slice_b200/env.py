@@ -32,7 +32,8 @@ class BatchedMARLCommEnv:
                  calculate_reward=None, obs_space=None, action_space=None, debug=True, root_path=".",
                  initial_episode_number=0, max_episode_number=None, simu_name=None, save_hist=True,
                  enable_random_episodes=False, *, num_envs=1, device="cuda:0", scenario_bank=None,
-                 auto_reset=None, env_id_base=0, channel_episodes=None):
+                 auto_reset=None, env_id_base=0, channel_episodes=None, hist_envs=None, hist_with_se=False,
+                 hist_root_path=None):
         path = os.path.join(root_path, "env_config", f"{config_file}.yml")
         if not os.path.exists(path):
             path = os.path.join(HERE, "env_config", f"{config_file}.yml")
@@ -56,9 +57,14 @@ class BatchedMARLCommEnv:
         if enable_random_episodes:
             raise NotImplementedError("enable_random_episodes (comm_env.py:219-226) is not built; pass explicit "
                                       "initial episodes per env instead")
-        if save_hist:
-            warnings.warn("save_hist: per-step history files (metrics.py:73-100) are replaced by on-device episode "
-                          "accumulators (episode_metrics()); no hist/*.npz is written", stacklevel=2)
+        # save_hist (comm_env.py:345-350): hist/<simu>/<agent>/ep_N.npz per finished episode, for the envs in
+        # `hist_envs` (default: the single env of a MARLCommEnv; nothing for a batch unless asked)
+        self.save_hist = bool(save_hist)
+        self.hist_envs = hist_envs
+        self.hist_with_se = bool(hist_with_se)
+        self.hist_root_path = hist_root_path if hist_root_path is not None else \
+            data["simulation"].get("hist_root_path", "./")  # comm_env.py:211,682
+        self._recorder = None
         self.num_envs, self.device = int(num_envs), torch.device(device)
         self.ChannelClass, self.TrafficClass = ChannelClass, TrafficClass
         self.MobilityClass, self.AssociationClass = MobilityClass, AssociationClass
@@ -103,6 +109,7 @@ class BatchedMARLCommEnv:
         if self.eng is not None:
             self.eng.close()
             self.eng = None
+            self._recorder = None
 
     def _engine(self):
         if self.eng is None:
@@ -197,15 +204,36 @@ class BatchedMARLCommEnv:
             eng.v["step"].copy_(torch.from_numpy(saved[0])); eng.v["episode"].copy_(torch.from_numpy(saved[1]))
         eng.reset(mask=mask, initial_episode=initial_episode, initial_episodes=initial_episodes, se=se)
         self._check()
+        rec = self._history()
+        if rec is not None:
+            rec.mark_reset()
         return self._format_obs(), {}
+
+    def _history(self):
+        if not self.save_hist:
+            return None
+        if self._recorder is None:
+            ids = self.hist_envs if self.hist_envs is not None else ([0] if self.num_envs == 1 else [])
+            if len(ids) == 0:
+                self.save_hist = False
+                return None
+            from .history import HistoryRecorder
+            self._recorder = HistoryRecorder(self._engine(), self.bank, ids, self.max_number_steps, self.hist_root_path,
+                                             self.simu_name, self.agent_name, flat_surface=self._surface.flat,
+                                             with_se=self.hist_with_se)
+        return self._recorder
 
     # ---- comm_env.py:271-373 / marl_comm_env.py:42-66 ------------------------------------------
     def step(self, action):
         eng = self._engine()
         a0, intra = self._parse_action(action)
         se, tr = self._hook_frames()
+        rec = self._history()
         eng.step(a0, intra, se, tr)
         self._check()
+        if rec is not None:
+            rec.record()
+            rec.flush()
         obs = self._format_obs()
         s = eng.surface()
         if self.num_envs > 1:

@@ -73,6 +73,8 @@ class ScenarioBank:
     def __init__(self):
         self.rows = []
         self.lambdas: list[float] = []
+        self.reqs: list[dict] = []          # the slice_req dicts as given (history files, metrics.py:43-60)
+        self.assocs: list[np.ndarray] = []  # slice_ue_assoc [5, 25] of every row
 
     def _lam_idx(self, lam: float) -> int:
         lam = float(lam)
@@ -130,6 +132,8 @@ class ScenarioBank:
                 sl["buffer_size"], sl["buffer_latency"], sl["message_size"] = 10240, 100, 65536
             sl["flags"] = flags
         self.rows.append(row)
+        self.reqs.append(slice_req)
+        self.assocs.append(sua.astype(np.float64))
         return len(self.rows) - 1
 
     def add_typed(self, slice_type, ue_slice) -> int:

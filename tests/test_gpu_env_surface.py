@@ -150,3 +150,60 @@ def test_batched_env_matches_single_envs(bank):
             assert np.array_equal([rew1[f"player_{i}"] for i in range(6)], outs[k][1][e])
         one.close()
     big.close()
+
+
+def test_history_file_matches_reference_trace(bank, tmp_path):
+    """save_hist=True: the episode file hist/<simu>/<agent>/ep_N.npz (metrics.py:73-100) written from
+    the on-device recorder holds, for every step of the episode, the values the unmodified reference
+    produced (golden trace seq_fixed, 40-step episodes) under the reference's 16 keys and shapes."""
+    from intent_radio_sched_multi_slice_b200 import agents, history, plugins
+    from intent_radio_sched_multi_slice_b200.env import MARLCommEnv
+
+    meta, d = golden_inputs.load_trace("seq_fixed")
+    rse, sse, stf = golden_inputs.regenerate(meta, d)
+    Ch, Tr, state = _trace_plugins(rse, sse, stf)
+    env = MARLCommEnv(Ch, Tr, plugins.SimpleMobility, plugins.MultSliceAssociationSeq, "mult_slice", "ib_sched",
+                      int(meta["seed"]), root_path="/nonexistent", initial_episode_number=int(meta["initial_episode"]),
+                      max_episode_number=int(meta["max_episodes"]), save_hist=True, debug=True, scenario_bank=bank,
+                      hist_root_path=str(tmp_path), hist_with_se=True, simu_name="golden")
+    env.max_number_steps = T = int(meta["max_steps"])
+    ag = agents.IBSched(env, 25, 5, 1, np.array([135]))
+    env.set_agent_functions(ag.obs_space_format, ag.action_format, ag.calculate_reward, ag.get_obs_space(),
+                            ag.get_action_space())
+    env.reset(seed=int(meta["seed"]), options={"initial_episode": int(meta["initial_episode"])})
+    n_eps = 2
+    for k in range(n_eps * T):
+        state["step"] = k
+        action = {"player_0": d["a0"][k]}
+        action.update({f"player_{i + 1}": int(d["intra"][k][i]) for i in range(5)})
+        *_, term, _, _ = env.step(action)
+        if term["__all__"]:
+            env.reset()
+    env.close()
+    for e in range(n_eps):
+        ep = int(meta["initial_episode"]) + e
+        h = history.read(str(tmp_path), "golden", "ib_sched", ep)
+        sl = slice(e * T, (e + 1) * T)
+        assert set(history.KEYS) - {"obs"} == set(h.keys())
+        assert h["pkt_effective_thr"].dtype == np.int64 and h["pkt_effective_thr"].shape == (T, 25)
+        for key, gold in (("pkt_incoming", "pkt_incoming"), ("pkt_throughputs", "pkt_throughputs"),
+                          ("pkt_effective_thr", "pkt_effective_thr"), ("dropped_pkts", "dropped_pkts")):
+            assert np.array_equal(h[key], d[gold][sl]), key
+        np.testing.assert_allclose(h["buffer_occupancies"], d["buffer_occupancies"][sl], rtol=1e-12)
+        np.testing.assert_allclose(h["buffer_latencies"], d["buffer_latencies"][sl], rtol=1e-12)
+        assert h["sched_decision"].shape == (T, 1, 25, 135) and h["spectral_efficiencies"].shape == (T, 1, 25, 135)
+        assert np.array_equal(h["sched_decision"][:, 0].sum(-1), d["rb_count"][sl])
+        first = np.argmax(h["sched_decision"][:, 0], -1)
+        assert np.array_equal(np.where(d["rb_count"][sl] > 0, first, 0), d["rb_start"][sl])
+        assert np.array_equal(h["spectral_efficiencies"][:, 0], sse[sl])
+        assert h["slice_ue_assoc"].shape == (T, 5, 25) and h["basestation_slice_assoc"].shape == (T, 1, 5)
+        assert h["mobility"].shape == (T, 25, 2) and h["basestation_ue_assoc"].shape == (T, 1, 25)
+        scen = golden_inputs.scen_of_episode(meta, ep)
+        st, us = golden_inputs.load_scenarios()
+        for s in range(5):
+            assert np.array_equal(np.flatnonzero(h["slice_ue_assoc"][0, s]), np.flatnonzero(us[scen] == s))
+            assert (h["slice_req"][0][f"slice_{s}"] != {}) == (st[scen, s] >= 0) == bool(h["basestation_slice_assoc"][0, 0, s])
+        for k in (0, T // 2, T - 1):
+            np.testing.assert_allclose([h["reward"][k][f"player_{i}"] for i in range(6)], d["reward"][sl][k], rtol=1e-12)
+            assert np.array_equal(h["agent_action"][k]["player_0"], d["a0"][sl][k])
+            assert [h["agent_action"][k][f"player_{i + 1}"] for i in range(5)] == d["intra"][sl][k].tolist()
