@@ -320,7 +320,7 @@ def run_b200(args):
                 "row_paths": {"empty": path_frac[0], "zero_fill": path_frac[1], "stream": path_frac[2]}}
 
     # ---- e2e: host actions in, host surface out, through irs_step_host ------------------------
-    e2e = None
+    e2e = e2e_f32 = None
     if not args.no_e2e:
         Ke = max(3, min(K, 30))
         pin = lambda *s, dt: torch.empty(*s, dtype=dt).pin_memory()
@@ -331,24 +331,35 @@ def run_b200(args):
         surf = capi.HostSurface(*[hs[n].data_ptr() for n in capi.SURFACE_FIELDS])
         h2d = sum(a.numel() * a.element_size() + b.numel() * b.element_size() for a, b in h_pool[:1])
         d2h = sum(t.numel() * t.element_size() for t in hs.values())
-        for k in range(3):
-            eng.step_host(h_pool[k % 4][0], h_pool[k % 4][1], surf)
-        barrier()
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        ev0.record()
-        tw = time.perf_counter()
-        for k in range(Ke):
-            eng.step_host(h_pool[k % 4][0], h_pool[k % 4][1], surf)
-        ev1.record()
-        barrier()
-        ms_e2e = max(ev0.elapsed_time(ev1), (time.perf_counter() - tw) * 1e3)
-        if world > 1:
-            t = torch.tensor([ms_e2e], device=dev, dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms_e2e = float(t.item())
-        e2e = {"value": world * E * U * Ke / (ms_e2e * 1e-3), "unit": "UE-steps/s", "h2d_bytes_per_step": h2d,
-               "d2h_bytes_per_step": d2h, "steps": Ke, "ms_per_step": ms_e2e / Ke,
-               "api": "irs_step_host (pinned host actions in, obs/masks/rewards/done out, stream drained)"}
+        def time_host(surface, bytes_out):
+            for k in range(3):
+                eng.step_host(h_pool[k % 4][0], h_pool[k % 4][1], surface)
+            barrier()
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ev0.record()
+            tw = time.perf_counter()
+            for k in range(Ke):
+                eng.step_host(h_pool[k % 4][0], h_pool[k % 4][1], surface)
+            ev1.record()
+            barrier()
+            ms = max(ev0.elapsed_time(ev1), (time.perf_counter() - tw) * 1e3)
+            if world > 1:
+                t = torch.tensor([ms], device=dev, dtype=torch.float64)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ms = float(t.item())
+            return {"value": world * E * U * Ke / (ms * 1e-3), "unit": "UE-steps/s", "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": bytes_out, "steps": Ke, "ms_per_step": ms / Ke}
+
+        e2e = time_host(surf, d2h)
+        e2e["api"] = "irs_step_host (pinned host actions in, float64 obs/masks/rewards/done out, stream drained)"
+        # the same call with the optional binary32 surface (converted on the device): half the bytes over PCIe
+        h32 = {"obs0_f32": pin(E, 50, dt=torch.float32), "obsi_f32": pin(E, 5, 19, dt=torch.float32),
+               "reward_f32": pin(E, 6, dt=torch.float32)}
+        surf32 = capi.HostSurface(None, None, hs["mask0"].data_ptr(), hs["maski"].data_ptr(), None, hs["done"].data_ptr(),
+                                  *[h32[n].data_ptr() for n in capi.SURFACE_F32_FIELDS])
+        d2h32 = sum(t.numel() * t.element_size() for t in list(h32.values()) + [hs["mask0"], hs["maski"], hs["done"]])
+        e2e_f32 = time_host(surf32, d2h32)
+        e2e_f32["api"] = "irs_step_host with the float32 surface option (obs/rewards converted on the device)"
 
     if world > 1:
         t = torch.tensor([ms_total], device=dev, dtype=torch.float64)
@@ -375,7 +386,7 @@ def run_b200(args):
                        "trace_bank_bytes": trace_bytes, "traffic": "native Poisson",
                        "state_bytes_per_gpu": state_bytes,
                        "l2": "state larger than L2" if flush is None else "L2 flushed (256 MB fill) between timed steps"},
-            "e2e": e2e, "roofline": roofline, "cpu_baseline": cpu, "gpu_launches": 3 * K, "clocks": clocks,
+            "e2e": e2e, "e2e_f32_surface": e2e_f32, "roofline": roofline, "cpu_baseline": cpu, "gpu_launches": 3 * K, "clocks": clocks,
             "env_errors": err, "episode_metrics": metrics_named,
         }
         print(json.dumps(line))

@@ -118,6 +118,8 @@ typedef struct {
     size_t out_reward;       /* f64 [E][6] */
     size_t out_done;         /* u8  [E] */
     size_t metrics_total;    /* f64 [16] result of irs_episode_metrics */
+    size_t out32;            /* f32 [E][151] staging of the binary32 host surface (obs0 | obsi | reward per env
+                                block: [E][50], then [E][95], then [E][6]) */
 } irs_layout;
 
 typedef struct {
@@ -156,6 +158,12 @@ typedef struct {
     int8_t* maski;           /* [E][5][5] */
     double* reward;          /* [E][6] */
     uint8_t* done;           /* [E] */
+    /* Optional binary32 copies of the float64 surfaces, converted on the device (round to nearest) so
+     * that half the bytes cross PCIe: RL front ends cast observations to float32 anyway, and 2^-24 is
+     * inside the 1e-5 tolerance of the path.  A NULL pointer (float64 or float32) skips that copy. */
+    float* obs0_f32;         /* [E][50] */
+    float* obsi_f32;         /* [E][5][19] */
+    float* reward_f32;       /* [E][6] */
 } irs_host_surface;
 
 typedef struct irs_env irs_env;

@@ -32,7 +32,7 @@ class Config(C.Structure):
 _LAYOUT_ARRAYS = [
     "buf", "ue_i", "ue_d", "ring", "rb", "step", "episode", "scen", "win_len",
     "win_head", "err", "sorted", "acc", "bank", "cdf", "in_a0", "in_intra", "out_obs0", "out_obsi",
-    "out_mask0", "out_maski", "out_reward", "out_done", "metrics_total",
+    "out_mask0", "out_maski", "out_reward", "out_done", "metrics_total", "out32",
 ]
 UI_FIELDS = ["tot", "sum_sent", "sum_drop", "last_sent", "last_drop", "last_inc", "occ1z", "path"]
 UD_FIELDS = ["occ", "lat", "sebar", "thr"]
@@ -60,10 +60,11 @@ class RawOutputs(C.Structure):
 
 
 SURFACE_FIELDS = ["obs0", "obsi", "mask0", "maski", "reward", "done"]
+SURFACE_F32_FIELDS = ["obs0_f32", "obsi_f32", "reward_f32"]  # optional binary32 copies (converted on the device)
 
 
 class HostSurface(C.Structure):
-    _fields_ = [(n, C.c_void_p) for n in SURFACE_FIELDS]
+    _fields_ = [(n, C.c_void_p) for n in SURFACE_FIELDS + SURFACE_F32_FIELDS]
 
 
 # every symbol include/irs_b200.h declares: (restype, argtypes)

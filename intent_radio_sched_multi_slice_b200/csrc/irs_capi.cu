@@ -25,6 +25,7 @@ struct irs_env {
     cudaEvent_t ev[4];
     bool have_ev;
     cudaStream_t copy_stream;      // irs_step_host: device->host copies of finished chunks
+
     cudaEvent_t chunk_ev[IRS_MAX_HOST_CHUNKS];
     bool have_copy;
     int host_chunks;               // IRS_HOST_CHUNKS (0 = choose from the batch size)
@@ -63,6 +64,7 @@ static void compute_layout(const irs_config& c, int32_t n_lambda, irs_layout* L)
     L->out_reward = take(E * 6 * 8);
     L->out_done = take(E);
     L->metrics_total = take(IRS_NUM_METRICS * 8);
+    L->out32 = take(E * (IRS_OBS0 + S * IRS_OBSI + 6) * 4);
     L->total_bytes = off;
 }
 
@@ -362,12 +364,31 @@ int irs_run(irs_env* env, int32_t n_steps, void* stream)
     return IRS_OK;
 }
 
+// float64 -> float32 of one surface array for envs [e0, e1) (the binary32 host surface)
+__global__ void k_to_f32(const double* __restrict__ src, float* __restrict__ dst, size_t n)
+{
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = (float)src[i];
+}
+
 // Device->host copies of the env surface for envs [e0, e1), enqueued on `st` (no synchronisation).
 static int copy_surface_range(irs_env* env, const irs_host_surface* o, bool with_reward, size_t e0, size_t e1, cudaStream_t st)
 {
     const size_t n = e1 - e0;
     const irs_layout& L = env->lay;
     char* b = env->blob;
+    const size_t E = (size_t)env->cfg.num_envs;
+    auto d2h32 = [&](float* host, size_t dev_off64, size_t stage_off, size_t per_env) -> cudaError_t {
+        if (!host) return cudaSuccess;
+        const double* src = (const double*)(b + dev_off64) + e0 * per_env;
+        float* stage = (float*)(b + L.out32) + stage_off + e0 * per_env;
+        const size_t cnt = n * per_env;
+        k_to_f32<<<(unsigned)((cnt + 255) / 256), 256, 0, st>>>(src, stage, cnt);
+        return cudaMemcpyAsync(host + e0 * per_env, stage, cnt * 4, cudaMemcpyDeviceToHost, st);
+    };
+    CK(d2h32(o->obs0_f32, L.out_obs0, 0, IRS_OBS0));
+    CK(d2h32(o->obsi_f32, L.out_obsi, E * IRS_OBS0, S * IRS_OBSI));
+    if (with_reward) CK(d2h32(o->reward_f32, L.out_reward, E * (IRS_OBS0 + S * IRS_OBSI), 6));
     auto d2h = [&](void* host, size_t dev_off, size_t per_env) -> cudaError_t {
         if (!host) return cudaSuccess;
         return cudaMemcpyAsync((char*)host + e0 * per_env, b + dev_off + e0 * per_env, n * per_env, cudaMemcpyDeviceToHost, st);
@@ -434,6 +455,8 @@ int irs_step_host(irs_env* env, const irs_actions* actions_host, const irs_host_
         for (int i = 0; i < IRS_MAX_HOST_CHUNKS; ++i) CK(cudaEventCreateWithFlags(&env->chunk_ev[i], cudaEventDisableTiming));
         env->have_copy = true;
     }
+    // One compute stream: a chunk must FINISH early for its copy to start early (two alternating compute
+    // streams were measured slower - both chunks then finish late, profiles/r1_notes.md).
     const size_t per = (E + chunks - 1) / chunks;
     for (int c = 0; c < chunks; ++c) {
         const size_t e0 = c * per, e1 = e0 + per < E ? e0 + per : E;
@@ -447,7 +470,7 @@ int irs_step_host(irs_env* env, const irs_actions* actions_host, const irs_host_
         rc = copy_surface_range(env, out_host, true, e0, e1, env->copy_stream);
         if (rc) return rc;
     }
-    CK(cudaStreamSynchronize(env->copy_stream)); // implies every chunk's kernels on `st` finished
+    CK(cudaStreamSynchronize(env->copy_stream));
     return IRS_OK;
 }
 

@@ -30,7 +30,10 @@ def test_step_host_equals_device_step(bank, chunks, monkeypatch):
     hs = {"obs0": pin(E, 50, dt=torch.float64), "obsi": pin(E, 5, 19, dt=torch.float64),
           "mask0": pin(E, 5, dt=torch.int8), "maski": pin(E, 5, 5, dt=torch.int8),
           "reward": pin(E, 6, dt=torch.float64), "done": pin(E, dt=torch.uint8)}
-    surf = capi.HostSurface(*[hs[n].data_ptr() for n in capi.SURFACE_FIELDS])
+    h32 = {"obs0_f32": pin(E, 50, dt=torch.float32), "obsi_f32": pin(E, 5, 19, dt=torch.float32),
+           "reward_f32": pin(E, 6, dt=torch.float32)}
+    surf = capi.HostSurface(*[hs[n].data_ptr() for n in capi.SURFACE_FIELDS],
+                            *[h32[n].data_ptr() for n in capi.SURFACE_F32_FIELDS])
     rng = np.random.default_rng(5)
     names = {"obs0": "obs0", "obsi": "obs_i", "mask0": "mask0", "maski": "mask_i", "reward": "reward", "done": "done"}
     for k in range(25):  # crosses two auto-resets (max_steps = 9)
@@ -42,6 +45,8 @@ def test_step_host_equals_device_step(bank, chunks, monkeypatch):
         s = dev.surface()
         for hn, dn in names.items():
             assert np.array_equal(hs[hn].numpy(), s[dn].cpu().numpy()), f"step {k}: {hn} differs (chunks={chunks})"
+        for hn, dn in (("obs0_f32", "obs0"), ("obsi_f32", "obs_i"), ("reward_f32", "reward")):  # binary32 copies
+            assert np.array_equal(h32[hn].numpy(), s[dn].cpu().numpy().astype(np.float32)), f"step {k}: {hn}"
     assert host.check_errors() is None
     assert torch.equal(host.buf, dev.buf)
     host.close()
