@@ -12,6 +12,7 @@
 #include "irs_env.cuh"
 #include "irs_ue.cuh"
 #include "irs_fused.cuh"
+#include "irs_serial.cuh"
 
 #define IRS_MAX_HOST_CHUNKS 16
 
@@ -29,6 +30,8 @@ struct irs_env {
     cudaEvent_t chunk_ev[IRS_MAX_HOST_CHUNKS];
     bool have_copy;
     int host_chunks;               // IRS_HOST_CHUNKS (0 = choose from the batch size)
+    int serial_min;                // IRS_SERIAL_MIN_ENVS: launches covering at least this many envs use the
+                                   // thread-per-env action / tail kernels (irs_serial.cuh)
     const double* se_bank;         // channel_mode 3 (irs_set_se_trace)
     int32_t bank_eps, bank_steps;
     int mode; // IRS_STEP_MODE: 0 fused k_env_step, 1 k_action + k_ue_step (warp per row) + k_env_tail,
@@ -138,6 +141,8 @@ int irs_create(const irs_config* cfg, int32_t n_lambda, irs_env** out)
     env->mode = sp ? atoi(sp) : 2;
     const char* hc = getenv("IRS_HOST_CHUNKS");
     env->host_chunks = hc ? atoi(hc) : 0;
+    const char* sm_ = getenv("IRS_SERIAL_MIN_ENVS");
+    env->serial_min = sm_ ? atoi(sm_) : 8192;
     compute_layout(env->cfg, n_lambda, &env->lay);
     *out = env;
     return IRS_OK;
@@ -265,14 +270,21 @@ static int launch_step(irs_env* env, const StepArgs& A, cudaStream_t st, bool pr
         CK(cudaGetLastError());
         return IRS_OK;
     }
-    k_action<<<(E + 7) / 8, 256, 0, st>>>(A);
+    const bool serial = E >= env->serial_min;
+    if (serial) k_action_t<<<(E + SERIAL_THREADS - 1) / SERIAL_THREADS, SERIAL_THREADS, 0, st>>>(A);
+    else k_action<<<(E + 7) / 8, 256, 0, st>>>(A);
     if (profile) CK(cudaEventRecord(env->ev[1], st));
     const long long rows = (long long)E * U;
     if (env->mode == 1) k_ue_step<<<(unsigned)((rows + UE_WARPS - 1) / UE_WARPS), UE_WARPS * 32, 0, st>>>(A);
     else if (A.raw.se_used) k_ue_env_raw<<<(E + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(A);
     else k_ue_env<<<(E + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(A);
     if (profile) CK(cudaEventRecord(env->ev[2], st));
-    k_env_tail<<<(E + ENV_WARPS - 1) / ENV_WARPS, ENV_WARPS * 32, 0, st>>>(A);
+    if (serial) {
+        k_env_tail_t<<<(E + SERIAL_THREADS - 1) / SERIAL_THREADS, SERIAL_THREADS, 0, st>>>(A);
+        if (env->cfg.auto_reset) k_rollover<<<(E + ENV_WARPS - 1) / ENV_WARPS, ENV_WARPS * 32, 0, st>>>(A);
+    } else {
+        k_env_tail<<<(E + ENV_WARPS - 1) / ENV_WARPS, ENV_WARPS * 32, 0, st>>>(A);
+    }
     if (profile) CK(cudaEventRecord(env->ev[3], st));
     CK(cudaGetLastError());
     return IRS_OK;

@@ -15,6 +15,14 @@ from gpu_adapter import CudaEnv, compare_outputs
 
 pytestmark = pytest.mark.gpu
 
+
+@pytest.fixture(autouse=True, params=["warp_per_env", "thread_per_env"])
+def per_env_kernels(request, monkeypatch):
+    """Every test of this file runs with both families of per-env kernels: k_action / k_env_tail (one warp
+    per env, small batches) and k_action_t / k_env_tail_t + k_rollover (one thread per env, the default from
+    8,192 envs per launch; irs_serial.cuh)."""
+    monkeypatch.setenv("IRS_SERIAL_MIN_ENVS", "1" if request.param == "thread_per_env" else str(1 << 30))
+
 TRACES = ["cfg1_marr", "mapf", "ibsched_mimic", "ibsched_fixed", "seq_mimic", "seq_fixed", "sweep_scen"]
 
 
