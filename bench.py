@@ -34,14 +34,22 @@ def parse():
     p.add_argument("--warmup", type=int, default=20)
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
     p.add_argument("--envs", type=int, default=65536, help="env instances per GPU (weak scaling)")
-    p.add_argument("--depth", type=int, default=0, help="force every UE to a deep buffer profile (config 5 sweep)")
-    p.add_argument("--workload", default="mix", choices=["mix", "cfg2", "trace"],
-                   help="mix: native generators (default); cfg2: 1,024 envs; trace: QuadrigaChannel-shaped SE bank in HBM")
+    p.add_argument("--depth", type=int, default=0,
+                   help="buffer depth of the sweep workload (BASELINE config 5: 401, 1024, 4096); default 1024")
+    p.add_argument("--workload", default="sweep", choices=["sweep", "mix", "cfg2", "trace"],
+                   help="sweep (default): BASELINE config 5, 65,536 envs x 25 UEs x deep buffers, the HBM-roofline "
+                        "configuration the metric is quoted on at 1/2/4/8 GPUs; mix: the 200-scenario mult_slice mix "
+                        "(D 21..401); cfg2: BASELINE config 2 (1,024 envs); trace: QuadrigaChannel-shaped SE bank in HBM")
     p.add_argument("--trace-steps", type=int, default=16, help="frames per episode of the SE bank (wraps around)")
     p.add_argument("--cpu-envs", type=int, default=2048, help="env instances of the CPU baseline sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
-    return p.parse_args()
+    a = p.parse_args()
+    if a.workload == "sweep" and a.depth <= 0:
+        a.depth = 1024
+    if a.workload != "sweep" and a.depth > 0:
+        a.workload = "sweep"  # --depth D alone selects the sweep
+    return a
 
 
 def make_bank(depth: int):
@@ -63,7 +71,8 @@ def make_bank(depth: int):
             req[f"slice_{s}"]["parameters"]["par1"]["value"] = depth // 2
             sua[s, 5 * s:5 * s + 5] = 1
         bank.add(req, sua)
-    return bank, f"scale sweep: 25 UEs x buffer depth {depth} (uav_app_case_1 profile)"
+    return bank, (f"BASELINE config 5 (scale sweep): envs x 25 UEs x packet-buffer depth {depth} "
+                  "(every UE on the uav_app_case_1 profile, native mimic_quadriga SE + Poisson traffic, random actions)")
 
 
 def engine_kwargs(args, rank):

@@ -30,8 +30,9 @@ struct irs_env {
     cudaEvent_t chunk_ev[IRS_MAX_HOST_CHUNKS];
     bool have_copy;
     int host_chunks;               // IRS_HOST_CHUNKS (0 = choose from the batch size)
-    int serial_min;                // IRS_SERIAL_MIN_ENVS: launches covering at least this many envs use the
-                                   // thread-per-env action / tail kernels (irs_serial.cuh)
+    int serial_min;                // IRS_SERIAL_MIN_ENVS (default 49,152): launches covering at least this many envs
+                                   // use the thread-per-env action / tail kernels (irs_serial.cuh); below that one
+                                   // thread per env leaves the SMs too empty to hide its serial latency
     const double* se_bank;         // channel_mode 3 (irs_set_se_trace)
     int32_t bank_eps, bank_steps;
     int mode; // IRS_STEP_MODE: 0 fused k_env_step, 1 k_action + k_ue_step (warp per row) + k_env_tail,
@@ -142,7 +143,7 @@ int irs_create(const irs_config* cfg, int32_t n_lambda, irs_env** out)
     const char* hc = getenv("IRS_HOST_CHUNKS");
     env->host_chunks = hc ? atoi(hc) : 0;
     const char* sm_ = getenv("IRS_SERIAL_MIN_ENVS");
-    env->serial_min = sm_ ? atoi(sm_) : 8192;
+    env->serial_min = sm_ ? atoi(sm_) : 49152;
     compute_layout(env->cfg, n_lambda, &env->lay);
     *out = env;
     return IRS_OK;
@@ -499,7 +500,7 @@ int irs_episode_metrics(irs_env* env, double* host_out, void* stream)
     if (!env || !env->bound) return IRS_ERR_UNBOUND;
     cudaStream_t st = (cudaStream_t)stream;
     StepArgs A = make_args(env);
-    k_metrics<<<1, 32, 0, st>>>(A);
+    k_metrics<<<IRS_NUM_METRICS, 256, 0, st>>>(A);
     CK(cudaGetLastError());
     if (host_out) {
         CK(cudaMemcpyAsync(host_out, env->st.metrics_total, IRS_NUM_METRICS * 8, cudaMemcpyDeviceToHost, st));

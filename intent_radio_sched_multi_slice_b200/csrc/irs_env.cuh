@@ -233,12 +233,21 @@ __global__ void k_init(const __grid_constant__ StepArgs A)
     for (int s = 0; s < S; ++s) A.st.sorted[(size_t)e * S + s] = (int8_t)s;
 }
 
-// Sum of the per-env accumulators in env order (fixed order -> reproducible bits).
-__global__ void k_metrics(const __grid_constant__ StepArgs A)
+// Sum of the per-env accumulators in a FIXED order (reproducible bits for a given batch size): block k sums
+// metric k; thread t adds its contiguous range of envs serially, then a shared-memory tree over the threads.
+__global__ void __launch_bounds__(256) k_metrics(const __grid_constant__ StepArgs A)
 {
-    const int k = threadIdx.x;
-    if (k >= IRS_NUM_METRICS) return;
-    double t = 0;
-    for (int e = 0; e < A.cfg.num_envs; ++e) t += A.st.acc[(size_t)e * IRS_NUM_METRICS + k];
-    A.st.metrics_total[k] = t;
+    __shared__ double part[256];
+    const int k = blockIdx.x, t = threadIdx.x;
+    const int E = A.cfg.num_envs, per = (E + 255) / 256;
+    const int e0 = t * per, e1 = e0 + per < E ? e0 + per : E;
+    double acc = 0;
+    for (int e = e0; e < e1; ++e) acc += A.st.acc[(size_t)e * IRS_NUM_METRICS + k];
+    part[t] = acc;
+    __syncthreads();
+    for (int d = 128; d > 0; d >>= 1) {
+        if (t < d) part[t] += part[t + d];
+        __syncthreads();
+    }
+    if (t == 0) A.st.metrics_total[k] = part[0];
 }

@@ -6,7 +6,7 @@
 // the code becomes the plain serial algorithm (NumPy's serial sums are just loops), a warp
 // advances 32 envs at once, and the issue slots per env drop by ~10x.  Same reference symbols,
 // same arithmetic order, same state layout as irs_action.cuh; selected by the launcher when the
-// launch covers >= IRS_SERIAL_MIN_ENVS envs (env var, default 8192).
+// launch covers >= IRS_SERIAL_MIN_ENVS envs (env var, default 49,152).
 #pragma once
 #include "irs_action.cuh"
 
