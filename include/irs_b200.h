@@ -79,7 +79,11 @@ typedef struct {
     int32_t fixed_intra;     /* -1 per-slice action (player_1..5), 0 rr, 1 pf, 2 mt */
     int32_t policy;          /* 0 actions supplied, 1 MARR, 2 MAPF, 3 random (device RNG) */
     int32_t assoc_mode;      /* 0 scenario = episode % scen_mod (mult_slice.py:444-452),
-                                1 scenario = episode / scen_div (mult_slice_seq.py:38-46) */
+                                1 scenario = episode / scen_div (mult_slice_seq.py:38-46),
+                                2 generated on the device per (env, episode) with the distribution of the
+                                  reference's generator mode (associations/mult_slice.py:359-416): the n_scen
+                                  bank rows are then slice-TYPE templates (sl[0] = the type's parameters,
+                                  sl[0].n_ues = max UEs, sl[0].pad = min UEs; 5 <= n_scen <= 32) */
     int32_t scen_mod, scen_div, n_scen;
     int32_t max_steps, max_episodes, initial_episode;
     int32_t auto_reset;      /* step() resets a finished env in the same call (VecEnv style) */

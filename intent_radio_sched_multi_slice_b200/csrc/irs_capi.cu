@@ -58,7 +58,8 @@ static void compute_layout(const irs_config& c, int32_t n_lambda, irs_layout* L)
     L->win_len = take(E * 4); L->win_head = take(E * 4); L->err = take(E * 4);
     L->sorted = take(E * S);
     L->acc = take(E * IRS_NUM_METRICS * 8);
-    L->bank = take((size_t)c.n_scen * sizeof(irs_scenario));
+    // assoc_mode 2: the n_scen slice-type templates are followed by two private scenario rows per env
+    L->bank = take(((size_t)c.n_scen + (c.assoc_mode == 2 ? 2 * E : 0)) * sizeof(irs_scenario));
     L->cdf = take((size_t)(n_lambda > 0 ? n_lambda : 1) * IRS_POISSON_K * 8);
     L->in_a0 = take(E * S * 8); L->in_intra = take(E * S * 4);
     L->out_obs0 = take(E * IRS_OBS0 * 8);
@@ -130,7 +131,7 @@ int irs_create(const irs_config* cfg, int32_t n_lambda, irs_env** out)
         cfg->channel_mode < 0 || cfg->channel_mode > 3 || cfg->traffic_mode < 0 || cfg->traffic_mode > 1 ||
         cfg->policy < 0 || cfg->policy > 3 || cfg->fixed_intra < -1 || cfg->fixed_intra > 2 ||
         (cfg->assoc_mode == 0 && cfg->scen_mod <= 0) || (cfg->assoc_mode == 1 && cfg->scen_div <= 0) ||
-        cfg->assoc_mode < 0 || cfg->assoc_mode > 1 || !(cfg->bandwidth > 0) ||
+        cfg->assoc_mode < 0 || cfg->assoc_mode > 2 || (cfg->assoc_mode == 2 && (cfg->n_scen < S || cfg->n_scen > 32)) || !(cfg->bandwidth > 0) ||
         (cfg->traffic_mode == 1 && n_lambda <= 0) || (long long)cfg->num_envs * U >= (1ll << 31))
         return IRS_ERR_ARG;
     irs_env* env = new (std::nothrow) irs_env;
@@ -216,6 +217,8 @@ int irs_load_scenarios(irs_env* env, const irs_scenario* bank_host, int32_t n_sc
         for (int s = 0; s < S; ++s) {
             const irs_slice& sl = bank_host[i].sl[s];
             if (sl.n_ues > NS) return fail(env, IRS_ERR_ARG, "more than 5 UEs in a slice (agents/ib_sched.py:50)");
+            if (env->cfg.assoc_mode == 2 && s == 0 && (sl.pad < 1 || sl.pad > sl.n_ues))
+                return fail(env, IRS_ERR_ARG, "assoc_mode 2: template row needs 1 <= min UEs (sl[0].pad) <= max UEs (sl[0].n_ues)");
             if (sl.n_ues > 0 && ((int)sl.buffer_latency + 1 > env->cfg.depth_cap || sl.buffer_size < 1 || sl.message_size < 1))
                 return fail(env, IRS_ERR_ARG, "slice buffer parameters out of range (depth_cap too small?)");
             if ((sl.flags & IRS_F_REQ) && env->cfg.traffic_mode == 1 && (sl.lam_idx < 0 || sl.lam_idx >= n_lambda))

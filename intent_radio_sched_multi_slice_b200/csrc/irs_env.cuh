@@ -5,6 +5,60 @@
 
 #define ENV_WARPS 4 /* envs per block in k_env_tail / k_reset */
 
+// assoc_mode 2 - MultSliceAssociation in GENERATOR mode (associations/mult_slice.py:359-416, 454-466): a fresh
+// network scenario per (env, episode) instead of a replayed file: 3..5 slices, slice slots and slice types drawn
+// without replacement, UEs per slice uniform in the type's [min, max], random UE ids.  The first n_scen rows of the
+// bank are the slice-TYPE templates (sl[0] = the type's parameters, sl[0].n_ues = max UEs, sl[0].pad = min UEs);
+// the env's own rows follow (two per env, alternating with the episode's parity so that a row is never rewritten in
+// the launch that read it through the read-only cache).  Draws come from the counter-based generator, keyed by
+// (seed, global env id, episode): same distribution as the reference, not its PCG64 stream.  Serial, by one lane.
+struct ScenWords {
+    uint64_t seed;
+    int episode, gid, i;
+    uint4 cur;
+    __device__ uint32_t next()
+    {
+        if ((i & 3) == 0) cur = rng_quad(seed, K_SCEN, 0, i >> 2, 0, episode, gid);
+        const uint32_t w = (i & 3) == 0 ? cur.x : ((i & 3) == 1 ? cur.y : ((i & 3) == 2 ? cur.z : cur.w));
+        ++i;
+        return w;
+    }
+    __device__ int below(int n) { return (int)(((uint64_t)next() * (uint32_t)n) >> 32); } // uniform in [0, n)
+};
+__device__ __noinline__ void generate_scenario_row(const StepArgs& A, int e, int ep, irs_scenario* row)
+{
+    const irs_scenario* types = A.st.bank;
+    const int T = A.cfg.n_scen;
+    ScenWords g;
+    g.seed = A.cfg.seed; g.episode = ep; g.gid = A.cfg.env_id_base + e; g.i = 0;
+    int slots[S], tys[32], counts[S], ues[U];
+    const int k = 3 + g.below(S - 3 + 1);
+    for (int j = 0; j < S; ++j) slots[j] = j;
+    for (int j = 0; j < k; ++j) { const int r = j + g.below(S - j); const int t = slots[j]; slots[j] = slots[r]; slots[r] = t; }
+    for (int j = 0; j < T && j < 32; ++j) tys[j] = j;
+    for (int j = 0; j < k; ++j) { const int r = j + g.below(T - j); const int t = tys[j]; tys[j] = tys[r]; tys[r] = t; }
+    int total = 0;
+    for (int j = 0; j < k; ++j) {
+        const int mn = types[tys[j]].sl[0].pad, mx = types[tys[j]].sl[0].n_ues;
+        counts[j] = mn + g.below(mx - mn + 1);
+        total += counts[j];
+    }
+    for (int j = 0; j < U; ++j) ues[j] = j;
+    for (int j = 0; j < total; ++j) { const int r = j + g.below(U - j); const int t = ues[j]; ues[j] = ues[r]; ues[r] = t; }
+    irs_slice empty;
+    memset(&empty, 0, sizeof(empty));
+    for (int s = 0; s < S; ++s) row->sl[s] = empty;
+    for (int u = 0; u < 32; ++u) row->ue_slice[u] = -1;
+    int off = 0;
+    for (int j = 0; j < k; ++j) {
+        irs_slice sl = types[tys[j]].sl[0];
+        sl.n_ues = counts[j];
+        sl.pad = 0;
+        row->sl[slots[j]] = sl;
+        for (int c = 0; c < counts[j]; ++c) row->ue_slice[ues[off++]] = (int8_t)slots[j];
+    }
+}
+
 // CommunicationEnv.reset (comm_env.py:375-482) for env e, by the whole warp.  `se_row` is a
 // 136-double shared-memory scratch row owned by the warp.  The observation window is NOT
 // cleared (ib_sched.py:51,64: the deque lives in the agent) - the zero frame of the reset is
@@ -25,7 +79,14 @@ __device__ __noinline__ void reset_env_warp(const StepArgs& A, int e, int initia
         if (lane == 0) atomicOr(&st.err[e], ERR_EPISODE_RANGE); // :428-433
         return;
     }
-    const int scen = scen_of_episode(c, ep);
+    int scen;
+    if (c.assoc_mode == 2) {
+        scen = c.n_scen + 2 * e + (ep & 1);
+        if (lane == 0) generate_scenario_row(A, e, ep, const_cast<irs_scenario*>(st.bank) + scen);
+        __syncwarp();
+    } else {
+        scen = scen_of_episode(c, ep);
+    }
     const irs_scenario* sc = st.bank + scen;
     __syncwarp();
     if (lane == 0) { st.step[e] = 0; st.episode[e] = ep; st.scen[e] = scen; }

@@ -13,7 +13,7 @@
 #pragma once
 #include "irs_common.cuh"
 
-enum { K_SE = 0, K_TRAFFIC = 1, K_MU = 2, K_POLICY = 3 };
+enum { K_SE = 0, K_TRAFFIC = 1, K_MU = 2, K_POLICY = 3, K_SCEN = 4 };
 
 __device__ __noinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1)
 {

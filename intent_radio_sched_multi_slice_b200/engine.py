@@ -217,6 +217,14 @@ class BatchEngine:
         capi.check(self.h, rc)
         return None
 
+    def scenario_rows(self):
+        """The scenario row every env is playing, as a NumPy record array (scenario.SCENARIO_DTYPE).  With
+        assoc_mode 2 these are the rows generated on the device."""
+        from .scenario import SCENARIO_DTYPE
+        n = len(self.bank_array) + (2 * self.E if self.cfg.assoc_mode == 2 else 0)
+        raw = self.blob[self.layout.bank:self.layout.bank + n * SCENARIO_DTYPE.itemsize].cpu().numpy()
+        return raw.view(SCENARIO_DTYPE)[self.v["scen"].cpu().numpy()]
+
     def surface(self):
         """The env surface tensors (device views into the state blob)."""
         v = self.v

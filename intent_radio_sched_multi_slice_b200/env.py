@@ -79,7 +79,8 @@ class BatchedMARLCommEnv:
                 setattr(self, f"_host_{kind}", cls)
             self._modes.update(mode)
         if scenario_bank is None:
-            scenario_bank = plugins.MultSliceAssociation.scenario_bank(root_path)
+            acls = AssociationClass if hasattr(AssociationClass, "scenario_bank") else plugins.MultSliceAssociation
+            scenario_bank = acls.scenario_bank(root_path)
         self.bank = scenario_bank
         self.auto_reset = (self.num_envs > 1) if auto_reset is None else bool(auto_reset)
         self.env_id_base = env_id_base

@@ -211,7 +211,18 @@ class MultSliceAssociationSeq(MultSliceAssociation):
     device_mode = {"assoc_mode": 1, "scen_div": 100}
 
 
-BUILTIN = {c.__name__: c for c in (MimicQuadriga, FixedSE, QuadrigaChannel, QuadrigaChannelSeq, MultSliceTraffic, SimpleMobility, MultSliceAssociation,
+class MultSliceAssociationGen(MultSliceAssociation):
+    """associations/mult_slice.py in GENERATOR mode (:359-416): a new network scenario for every env and episode -
+    3..5 slices, slots and slice types without replacement, UEs per slice uniform in the type's [min, max], random
+    UE ids - drawn on the device by the counter-based generator at every reset (assoc_mode 2).  No ep_N.npz files."""
+    device_mode = {"assoc_mode": 2}
+
+    @classmethod
+    def scenario_bank(cls, root_path: str = "", n: int = 0, seed: int = 10) -> scn.ScenarioBank:
+        return scn.ScenarioBank.templates()
+
+
+BUILTIN = {c.__name__: c for c in (MultSliceAssociationGen, MimicQuadriga, FixedSE, QuadrigaChannel, QuadrigaChannelSeq, MultSliceTraffic, SimpleMobility, MultSliceAssociation,
                                    MultSliceAssociationSeq)}
 
 

@@ -145,6 +145,19 @@ class ScenarioBank:
                 sua[int(s), u] = 1
         return self.add(req, sua)
 
+    @classmethod
+    def templates(cls) -> "ScenarioBank":
+        """Bank for assoc_mode 2 (scenario generated on the device per env and episode): row t is the
+        TEMPLATE of slice type t - sl[0] holds the type's parameters, sl[0].n_ues its max and sl[0].pad
+        its min number of UEs (associations/mult_slice.py:58-347)."""
+        bank = cls()
+        for t in range(len(SLICE_TYPES)):
+            bank.add({"slice_0": slice_req_from_type(t)}, np.zeros((MAX_SLICES, MAX_UES)))
+            row = bank.rows[-1]
+            row["sl"][0]["n_ues"] = SLICE_TYPES[t][10]
+            row["sl"][0]["pad"] = SLICE_TYPES[t][9]
+        return bank
+
     def max_depth(self) -> int:
         arr = self.array()
         return int(arr["sl"]["buffer_latency"].max()) + 1
@@ -187,3 +200,54 @@ def generate_scenarios(n: int, seed: int = 10) -> tuple[np.ndarray, np.ndarray]:
             us[i, ues[off:off + c]] = slot
             off += c
     return st, us
+
+
+def decode_row(row) -> tuple[np.ndarray, np.ndarray]:
+    """One bank row -> (slice type id per slot, -1 = unused; slice of each UE) by matching the row's slice
+    parameters against the slice-type table."""
+    st = -np.ones(MAX_SLICES, np.int8)
+    for s in range(MAX_SLICES):
+        sl = row["sl"][s]
+        if not (int(sl["flags"]) & F_REQ):
+            continue
+        for t, ty in enumerate(SLICE_TYPES):
+            if (sl["priority"], sl["buffer_size"], sl["buffer_latency"], sl["message_size"], sl["traffic"]) == \
+                    (ty[1], ty[5], ty[6], ty[7], ty[8]) and \
+                    (ty[2] is None) == (not int(sl["flags"]) & F_REL) and (ty[4] is None) == (not int(sl["flags"]) & F_THR):
+                st[s] = t
+                break
+    return st, np.array(row["ue_slice"][:MAX_UES], np.int8)
+
+
+def export_reference_episode(directory: str, episode: int, slice_type, ue_slice, number_steps: int = 1000) -> str:
+    """Write `ep_<episode>.npz` in the format of gen_assoc_mult_slice.py:229-237, which
+    MultSliceAssociation.load_episode_data (associations/mult_slice.py:490-508) replays: per-step copies of the
+    association matrices and of the slice_req dict (operators as numpy ufuncs, like the reference)."""
+    import os
+
+    ops = {"at_least": np.greater_equal, "at_most": np.less_equal}
+    req = {}
+    for s, t in enumerate(slice_type):
+        r = slice_req_from_type(int(t)) if t >= 0 else {}
+        for par in (r.get("parameters", {}) if r else {}).values():
+            par["operator"] = ops[par["operator"]]
+        req[f"slice_{s}"] = r
+    sua = np.zeros((MAX_SLICES, MAX_UES))
+    for u, s in enumerate(ue_slice[:MAX_UES]):
+        if s >= 0:
+            sua[int(s), u] = 1
+    bsa = np.array([[1.0 if slice_type[s] >= 0 else 0.0 for s in range(MAX_SLICES)]])
+    bua = np.array([sua.sum(axis=0)])
+    rep = lambda a: np.repeat(np.asarray(a)[None], number_steps, axis=0)
+    hist_req = np.empty(number_steps, object)
+    to_use = np.empty(number_steps, object)
+    used = np.flatnonzero(np.asarray(slice_type) >= 0)
+    for k in range(number_steps):
+        hist_req[k] = req
+        to_use[k] = used
+    os.makedirs(directory, exist_ok=True)
+    path = os.path.join(directory, f"ep_{episode}.npz")
+    np.savez_compressed(path, hist_basestation_ue_assoc=rep(bua), hist_basestation_slice_assoc=rep(bsa),
+                        hist_slice_ue_assoc=rep(sua), hist_slice_req=hist_req,
+                        hist_slices_lifetime=np.zeros((number_steps, MAX_SLICES)), hist_slices_to_use=to_use)
+    return path

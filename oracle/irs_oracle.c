@@ -50,7 +50,8 @@ typedef struct {
     int32_t sort_slices;              /* IBSched enable_sort_slices (ib_sched.py:57) */
     int32_t fixed_intra;              /* -1 per-slice action, 0 rr, 1 pf, 2 mt */
     int32_t policy;                   /* 0 external, 1 MARR, 2 MAPF, 3 random (native RNG) */
-    int32_t assoc_mode;               /* 0 scen = episode % scen_mod, 1 scen = episode / scen_div */
+    int32_t assoc_mode;               /* 0 scen = episode % scen_mod, 1 scen = episode / scen_div,
+                                         2 generated per (env, episode): bank rows are slice-type templates */
     int32_t scen_mod, scen_div, n_scen;
     int32_t max_steps, max_episodes, initial_episode;
     int32_t auto_reset, env_id_base;
@@ -78,6 +79,7 @@ typedef struct {
     int32_t *buf; /* [E][U][depth_cap] age histograms (buffer.py:47) */
     const orc_scenario *bank;
     const double *poisson_cdf; /* [n_lambda][POISSON_K] */
+    orc_scenario *own_bank;    /* assoc_mode 2: templates + two generated rows per env */
     const double *se_bank;     /* channel_mode 3: [bank_eps][bank_steps][U][R] (channels/quadriga.py) */
     int32_t bank_eps, bank_steps;
 } orc_handle;
@@ -102,7 +104,7 @@ static void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1)
         k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
     }
 }
-enum { K_SE = 0, K_TRAFFIC = 1, K_MU = 2, K_POLICY = 3 };
+enum { K_SE = 0, K_TRAFFIC = 1, K_MU = 2, K_POLICY = 3, K_SCEN = 4 };
 static void rng_quad(const orc_config *cfg, int kind, int ue, int q, int frame, int episode, int gid,
                      uint32_t out[4])
 {
@@ -777,6 +779,46 @@ static void channel_frame(const orc_handle *h, int e, const orc_env *env, int fr
         }
     }
 }
+/* assoc_mode 2: MultSliceAssociation generator mode (associations/mult_slice.py:359-416, 454-466) with the
+ * counter-based generator: 3..5 slices, slots and types without replacement (partial Fisher-Yates), UEs per slice
+ * uniform in the type's [min, max] (template sl[0].pad .. sl[0].n_ues), random UE ids. */
+typedef struct { const orc_config *cfg; int episode, gid, i; uint32_t cur[4]; } scen_words;
+static uint32_t sw_next(scen_words *g)
+{
+    if ((g->i & 3) == 0) rng_quad(g->cfg, K_SCEN, 0, g->i >> 2, 0, g->episode, g->gid, g->cur);
+    return g->cur[g->i++ & 3];
+}
+static int sw_below(scen_words *g, int n) { return (int)(((uint64_t)sw_next(g) * (uint32_t)n) >> 32); }
+static void generate_scenario_row(const orc_handle *h, int e, int ep, orc_scenario *row)
+{
+    const orc_scenario *types = h->bank;
+    const int T = h->cfg.n_scen;
+    scen_words g = {&h->cfg, ep, h->cfg.env_id_base + e, 0, {0, 0, 0, 0}};
+    int slots[S], tys[32], counts[S], ues[U];
+    int k = 3 + sw_below(&g, S - 3 + 1);
+    for (int j = 0; j < S; ++j) slots[j] = j;
+    for (int j = 0; j < k; ++j) { int r = j + sw_below(&g, S - j), t = slots[j]; slots[j] = slots[r]; slots[r] = t; }
+    for (int j = 0; j < T && j < 32; ++j) tys[j] = j;
+    for (int j = 0; j < k; ++j) { int r = j + sw_below(&g, T - j), t = tys[j]; tys[j] = tys[r]; tys[r] = t; }
+    int total = 0;
+    for (int j = 0; j < k; ++j) {
+        int mn = types[tys[j]].sl[0].pad, mx = types[tys[j]].sl[0].n_ues;
+        counts[j] = mn + sw_below(&g, mx - mn + 1);
+        total += counts[j];
+    }
+    for (int j = 0; j < U; ++j) ues[j] = j;
+    for (int j = 0; j < total; ++j) { int r = j + sw_below(&g, U - j), t = ues[j]; ues[j] = ues[r]; ues[r] = t; }
+    memset(row, 0, sizeof(*row));
+    memset(row->ue_slice, -1, sizeof(row->ue_slice));
+    int off = 0;
+    for (int j = 0; j < k; ++j) {
+        orc_slice sl = types[tys[j]].sl[0];
+        sl.n_ues = counts[j];
+        sl.pad = 0;
+        row->sl[slots[j]] = sl;
+        for (int c = 0; c < counts[j]; ++c) row->ue_slice[ues[off++]] = (int8_t)slots[j];
+    }
+}
 /* comm_env.py:375-482 for env e.  initial_episode = -1: options {"initial_episode": -1} */
 static int reset_one(orc_handle *h, int e, int initial_episode, const double *se_in, const orc_io *io)
 {
@@ -790,7 +832,12 @@ static int reset_one(orc_handle *h, int e, int initial_episode, const double *se
     else if (env->episode < c->max_episodes - 1) env->episode += 1;   /* :426-427 */
     else return -2;                                            /* :428-433 */
     env->step = 0;
-    env->scen = scen_of_episode(c, env->episode);
+    if (c->assoc_mode == 2) {
+        env->scen = c->n_scen + 2 * e + (env->episode & 1);
+        generate_scenario_row(h, e, env->episode, &h->own_bank[env->scen]);
+    } else {
+        env->scen = scen_of_episode(c, env->episode);
+    }
     memset(h->buf + (size_t)e * U * c->depth_cap, 0, sizeof(int32_t) * U * c->depth_cap); /* :620-625 new UEs */
     double se[U * R];
     channel_frame(h, e, env, 0, se_in, se);
@@ -870,6 +917,11 @@ orc_handle *orc_create(const orc_config *cfg, const orc_scenario *bank, const do
     h->envs = (orc_env *)calloc(cfg->num_envs, sizeof(orc_env));
     h->buf = (int32_t *)calloc((size_t)cfg->num_envs * U * cfg->depth_cap, sizeof(int32_t));
     h->bank = bank; h->poisson_cdf = poisson_cdf;
+    if (cfg->assoc_mode == 2) {
+        h->own_bank = (orc_scenario *)calloc((size_t)cfg->n_scen + 2 * (size_t)cfg->num_envs, sizeof(orc_scenario));
+        memcpy(h->own_bank, bank, sizeof(orc_scenario) * cfg->n_scen);
+        h->bank = h->own_bank;
+    }
     for (int e = 0; e < cfg->num_envs; ++e) {
         h->envs[e].episode = cfg->initial_episode;
         for (int s = 0; s < S; ++s) h->envs[e].sorted_slices[s] = s; /* ib_sched.py:58 */
@@ -899,7 +951,9 @@ void orc_power_to_se(const double *power, double *se, int64_t n_frames, int layo
             else se[f * U * R + i] = v;
         }
 }
-void orc_destroy(orc_handle *h) { if (h) { free(h->envs); free(h->buf); free(h); } }
+void orc_destroy(orc_handle *h) { if (h) { free(h->envs); free(h->buf); free(h->own_bank); free(h); } }
+/* the scenario row env e is playing (tests: generated scenarios) */
+void orc_get_scenario(const orc_handle *h, int e, orc_scenario *out) { *out = h->bank[h->envs[e].scen]; }
 int orc_reset(orc_handle *h, const uint8_t *mask, int initial_episode, const double *se, const orc_io *io)
 {
     int rc = 0;

@@ -54,6 +54,7 @@ def lib():
         _lib.orc_create.restype = C.c_void_p
         _lib.orc_create.argtypes = [C.POINTER(Config), C.c_void_p, C.c_void_p]
         _lib.orc_destroy.argtypes = [C.c_void_p]
+        _lib.orc_get_scenario.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         _lib.orc_set_se_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32]
         _lib.orc_power_to_se.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_double, C.c_double]
         _lib.orc_reset.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.POINTER(IO)]
@@ -163,6 +164,13 @@ class OracleEnv:
         self._se_bank = np.ascontiguousarray(se_bank, np.float64)
         assert self._se_bank.ndim == 4 and self._se_bank.shape[2:] == (U, R)
         lib().orc_set_se_trace(self.h, _ptr(self._se_bank), self._se_bank.shape[0], self._se_bank.shape[1])
+
+    def scenario_rows(self):
+        """The scenario row every env is playing (432-byte records, dtype of the bank)."""
+        out = np.zeros(self.E, self.bank.dtype)
+        for e in range(self.E):
+            lib().orc_get_scenario(self.h, e, out[e:e + 1].ctypes.data)
+        return out
 
     def want_se(self):
         self.out["se_used"] = np.zeros((self.E, U, R))

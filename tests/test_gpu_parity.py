@@ -121,6 +121,30 @@ def test_batch_native_matches_oracle(bank, cfg):
     assert per_g[:, 15].min() >= 3  # every env went through >= 3 resets
 
 
+def test_generated_scenarios_match_oracle():
+    """assoc_mode 2: a new scenario per (env, episode) generated on the device at every reset
+    (associations/mult_slice.py:359-416 distribution): the rows and every step output equal the oracle's."""
+    from intent_radio_sched_multi_slice_b200 import scenario as scn
+    from oracle import oracle
+
+    tb = scn.ScenarioBank.templates()
+    E, steps = 200, 60
+    kw = dict(channel_mode=2, traffic_mode=1, policy=3, fixed_intra=-1, sort_slices=1, assoc_mode=2, max_steps=17,
+              auto_reset=1, env_id_base=40, seed=77, initial_episode=3)
+    orc = oracle.OracleEnv(tb.array(), tb.poisson_cdf(), E, depth_cap=404, **kw)
+    gpu = CudaEnv(tb, E, depth_cap=401, **kw)
+    want, got = orc.reset(initial_episode=3), gpu.reset(initial_episode=3)
+    compare_outputs(got, want, "reset", keys=["obs0", "obs_i", "mask0", "mask_i", "sorted_slices"])
+    assert np.array_equal(gpu.eng.scenario_rows(), orc.scenario_rows())
+    for k in range(steps):
+        want, got = orc.step(), gpu.step()
+        compare_outputs(got, want, f"step {k}")
+        if k % 17 == 16:
+            assert np.array_equal(gpu.eng.scenario_rows(), orc.scenario_rows()), k
+    assert np.array_equal(gpu.buffers()[:, :, :401], orc.buffers()[:, :, :401])
+    assert np.array_equal(gpu.state()["scen"], orc.state()["scen"])
+
+
 def test_native_se_statistics(bank):
     """Native mimic_quadriga / Poisson draws follow the reference's distributions
     (channels/mimic_quadriga.py:37-56: |N(mu_u, 1.5)|, mu_u = |N(10, 7.5)|;
