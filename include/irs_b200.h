@@ -53,7 +53,8 @@ typedef enum {
 } irs_status;
 
 /* slice flags */
-enum { IRS_F_ACTIVE = 1, IRS_F_REQ = 2, IRS_F_THR = 4, IRS_F_REL = 8, IRS_F_LAT = 16 };
+enum { IRS_F_ACTIVE = 1, IRS_F_REQ = 2, IRS_F_THR = 4, IRS_F_REL = 8, IRS_F_LAT = 16,
+       IRS_F_EMBB = 32, IRS_F_URLLC = 64 /* use case of the slice type, sched_colran.py:352-363 */ };
 
 /* One slice slot of a scenario: the dense form of one `slice_req["slice_s"]` entry
  * (associations/mult_slice.py:58-347) plus its UE count.  80 bytes. */
@@ -89,6 +90,13 @@ typedef struct {
     int32_t auto_reset;      /* step() resets a finished env in the same call (VecEnv style) */
     int32_t env_id_base;     /* global id of env 0 of this shard: RNG key, so results do not
                                 depend on how envs are sharded over GPUs */
+    int32_t surface;         /* agent surface written to obs0 / reward[0]:
+                                0 IBSched family (ib_sched.py:63-221; MARR, MAPF, SB3 adapters),
+                                1 SchedTWC (agents/sched_twc.py:166-413), 2 SchedColORAN (agents/sched_colran.py:166-417):
+                                  50-value per-slice metric vector, weighted-negative-drift / eMBB-URLLC reward, and
+                                  every frame pushed TWICE into the 10-entry window, as those agents do
+                                  (sched_twc.py:176-179) */
+    int32_t pad0;
     uint64_t seed;
     double bandwidth;        /* Hz, env_config/mult_slice.yml:3 */
 } irs_config;

@@ -71,6 +71,7 @@ DEVICE_POLICY = DevicePolicy()
 
 class _AgentBase:
     sort_slices, fixed_intra, policy, flat = 1, -1, 0, False
+    surface = 0  # irs_config.surface: which observation / reward kernel fills obs0 and reward[0]
     # ib_sched.py:49-58
     max_obs_memory, max_number_ues_slice, intent_overfulfillment_rate, rbs_per_rbg = 10, 5, 0.2, 5
 
@@ -147,7 +148,24 @@ class IBSchedSB3PF(IBSchedSB3):
     fixed_intra = 1
 
 
-_BY_NAME = {c.__name__: c for c in (IBSched, MARR, MAPF, IBSchedSB3, IBSchedSB3PF)}
+class SchedTWC(_AgentBase):
+    """agents/sched_twc.py:20-449 env adapters: 50-value per-slice metric vector (requirements, mean SE, served and
+    effective throughput, buffer occupancy and latency, packet-loss rate, requested throughput), reward = weighted
+    mean of the negative slice intent drifts, round-robin inside slices, slices not sorted, every frame pushed twice
+    into the observation window (:176-179)."""
+    sort_slices, fixed_intra, policy, flat, surface = 0, 0, 0, True, 1
+
+    def get_obs_space(self):  # sched_twc.py:425-428: declared with the fake agent's player_0 shape (50,)
+        return _box(-1, np.inf, (self.max_number_slices * 10,), np.float64)
+
+
+class SchedColORAN(SchedTWC):
+    """agents/sched_colran.py:20-455: the same observation; reward = sum over slices of +throughput / 200 Mbps for eMBB
+    slice types and -buffered Mbps / 2000 for URLLC ones (:347-417)."""
+    surface = 2
+
+
+_BY_NAME = {c.__name__: c for c in (IBSched, MARR, MAPF, IBSchedSB3, IBSchedSB3PF, SchedTWC, SchedColORAN)}
 
 
 def surface_of(callback):

@@ -26,7 +26,7 @@ class Config(C.Structure):
     _fields_ = [(n, C.c_int32) for n in (
         "num_envs", "depth_cap", "channel_mode", "traffic_mode", "sort_slices", "fixed_intra", "policy",
         "assoc_mode", "scen_mod", "scen_div", "n_scen", "max_steps", "max_episodes", "initial_episode",
-        "auto_reset", "env_id_base")] + [("seed", C.c_uint64), ("bandwidth", C.c_double)]
+        "auto_reset", "env_id_base", "surface", "pad0")] + [("seed", C.c_uint64), ("bandwidth", C.c_double)]
 
 
 _LAYOUT_ARRAYS = [

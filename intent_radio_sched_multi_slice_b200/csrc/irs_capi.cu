@@ -13,6 +13,7 @@
 #include "irs_ue.cuh"
 #include "irs_fused.cuh"
 #include "irs_serial.cuh"
+#include "irs_alt.cuh"
 
 #define IRS_MAX_HOST_CHUNKS 16
 
@@ -96,6 +97,9 @@ static StepArgs make_args(const irs_env* env)
     A.se_bank = env->se_bank;
     A.bank_eps = env->bank_eps;
     A.bank_steps = env->bank_steps;
+    A.win_cap = env->cfg.surface ? W / 2 : W;
+    A.win_mul = env->cfg.surface ? 2 : 1;
+    A.defer_rollover = 0;
     A.env_begin = 0;
     A.env_end = env->cfg.num_envs;
     return A;
@@ -129,7 +133,7 @@ int irs_create(const irs_config* cfg, int32_t n_lambda, irs_env** out)
     *out = nullptr;
     if (cfg->num_envs <= 0 || cfg->depth_cap <= 0 || cfg->n_scen <= 0 || cfg->max_steps <= 0 ||
         cfg->channel_mode < 0 || cfg->channel_mode > 3 || cfg->traffic_mode < 0 || cfg->traffic_mode > 1 ||
-        cfg->policy < 0 || cfg->policy > 3 || cfg->fixed_intra < -1 || cfg->fixed_intra > 2 ||
+        cfg->policy < 0 || cfg->policy > 3 || cfg->surface < 0 || cfg->surface > 2 || cfg->fixed_intra < -1 || cfg->fixed_intra > 2 ||
         (cfg->assoc_mode == 0 && cfg->scen_mod <= 0) || (cfg->assoc_mode == 1 && cfg->scen_div <= 0) ||
         cfg->assoc_mode < 0 || cfg->assoc_mode > 2 || (cfg->assoc_mode == 2 && (cfg->n_scen < S || cfg->n_scen > 32)) || !(cfg->bandwidth > 0) ||
         (cfg->traffic_mode == 1 && n_lambda <= 0) || (long long)cfg->num_envs * U >= (1ll << 31))
@@ -258,6 +262,7 @@ int irs_reset(irs_env* env, const uint8_t* mask_dev, int32_t initial_episode, co
     A.initial_episode_dev = initial_episode_dev;
     const int E = env->cfg.num_envs;
     k_reset<<<(E + ENV_WARPS - 1) / ENV_WARPS, ENV_WARPS * 32, 0, (cudaStream_t)stream>>>(A);
+    if (env->cfg.surface != 0) k_surface_alt<<<(E + ENV_WARPS - 1) / ENV_WARPS, ENV_WARPS * 32, 0, (cudaStream_t)stream>>>(A, 2);
     CK(cudaGetLastError());
     return IRS_OK;
 }
@@ -283,11 +288,20 @@ static int launch_step(irs_env* env, const StepArgs& A, cudaStream_t st, bool pr
     else if (A.raw.se_used) k_ue_env_raw<<<(E + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(A);
     else k_ue_env<<<(E + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(A);
     if (profile) CK(cudaEventRecord(env->ev[2], st));
+    const bool alt = env->cfg.surface != 0; // SchedTWC / SchedColORAN: their surface reads the step's records before
+                                            // finished envs roll over, then once more for the reset observation
+    const unsigned env_blocks = (E + ENV_WARPS - 1) / ENV_WARPS;
     if (serial) {
         k_env_tail_t<<<(E + SERIAL_THREADS - 1) / SERIAL_THREADS, SERIAL_THREADS, 0, st>>>(A);
-        if (env->cfg.auto_reset) k_rollover<<<(E + ENV_WARPS - 1) / ENV_WARPS, ENV_WARPS * 32, 0, st>>>(A);
     } else {
-        k_env_tail<<<(E + ENV_WARPS - 1) / ENV_WARPS, ENV_WARPS * 32, 0, st>>>(A);
+        StepArgs B = A;
+        B.defer_rollover = alt ? 1 : 0;
+        k_env_tail<<<env_blocks, ENV_WARPS * 32, 0, st>>>(B);
+    }
+    if (alt) k_surface_alt<<<env_blocks, ENV_WARPS * 32, 0, st>>>(A, 0);
+    if ((serial || alt) && env->cfg.auto_reset) {
+        k_rollover<<<env_blocks, ENV_WARPS * 32, 0, st>>>(A);
+        if (alt) k_surface_alt<<<env_blocks, ENV_WARPS * 32, 0, st>>>(A, 1);
     }
     if (profile) CK(cudaEventRecord(env->ev[3], st));
     CK(cudaGetLastError());

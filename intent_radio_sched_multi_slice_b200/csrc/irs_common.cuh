@@ -62,6 +62,11 @@ struct StepArgs {
     const uint8_t* reset_mask;
     const int32_t* initial_episode_dev;
     int32_t initial_episode;
+    int32_t win_cap;  // distinct frames the observation window keeps: 10 (ib_sched.py:49-51), or 5 when the surface
+                      // pushes every frame twice (sched_twc.py:176-179, sched_colran.py:176-179)
+    int32_t win_mul;  // how often each kept frame counts in window sums: 1, or 2 with the double push
+    int32_t defer_rollover; // k_env_tail leaves finished envs to k_rollover (the alternative surfaces read the
+                            // last step's records in between)
     int32_t env_begin, env_end; // env range of this launch (irs_step_host pipelines chunks of the batch)
 };
 

@@ -109,7 +109,7 @@ __device__ __noinline__ void reset_env_warp(const StepArgs& A, int e, int initia
     }
     // push the all-zero metrics frame (comm_env.py:474-478)
     const int win_len = st.win_len[e];
-    const int p = (st.win_head[e] + 1) % W;
+    const int p = (st.win_head[e] + 1) % A.win_cap;
     UeFrame f;
     f.occ = 0; f.lat = 0; f.sebar = sebar; f.sent = 0; f.rb_count = 0;
     f.sum_sent = 0; f.sum_drop = 0; f.occ1z = false;
@@ -118,7 +118,7 @@ __device__ __noinline__ void reset_env_warp(const StepArgs& A, int e, int initia
         int* ui = st.ue_i + eu * UI_N;
         double* ud = st.ue_d + eu * UD_N;
         int ss = ui[UI_SUM_SENT], sd = ui[UI_SUM_DROP];
-        if (win_len == W) { const int2 ev = st.ring[eu * W + p]; ss -= ev.x; sd -= ev.y; }
+        if (win_len == A.win_cap) { const int2 ev = st.ring[eu * W + p]; ss -= ev.x; sd -= ev.y; }
         st.ring[eu * W + p] = make_int2(0, 0);
         f.sum_sent = ss; f.sum_drop = sd;
         f.occ1z = isclose0(ud[UD_OCC]);
@@ -127,7 +127,7 @@ __device__ __noinline__ void reset_env_warp(const StepArgs& A, int e, int initia
         ud[UD_OCC] = 0; ud[UD_LAT] = 0; ud[UD_SEBAR] = sebar; ud[UD_THR] = 0;
         st.rb[eu] = make_short2(0, 0);
     }
-    const int win_len_new = win_len < W ? win_len + 1 : W;
+    const int win_len_new = win_len < A.win_cap ? win_len + 1 : A.win_cap;
     __syncwarp();
     if (lane == 0) { st.win_len[e] = win_len_new; st.win_head[e] = p; }
     format_obs_warp(A, e, sc, f, win_len_new);
@@ -144,8 +144,8 @@ __device__ __forceinline__ void env_tail_core(const StepArgs& A, int e, const ir
     const irs_config& c = A.cfg;
     const int lane = lane_id();
     if (lane >= U) { f.sent = 0; f.rb_count = 0; dropped = 0; inc = 0; }
-    const int win_len = win_len_old < W ? win_len_old + 1 : W;
-    const int head = (head_old + 1) % W;
+    const int win_len = win_len_old < A.win_cap ? win_len_old + 1 : A.win_cap;
+    const int head = (head_old + 1) % A.win_cap;
     const int step = step_old + 1; // comm_env.py:339
     __syncwarp();
     if (lane == 0) { st.win_len[e] = win_len; st.win_head[e] = head; st.step[e] = step; }
@@ -244,7 +244,7 @@ __device__ __forceinline__ void env_tail_core(const StepArgs& A, int e, const ir
         if (done) acc[15] += 1;
         st.out_done[e] = done ? 1 : 0;
     }
-    if (done && c.auto_reset) {
+    if (done && c.auto_reset && !A.defer_rollover) {
         __syncwarp();
         reset_env_warp(A, e, -1, se_row);
     }

@@ -56,7 +56,7 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
     // ---- phase 0: env scalars and this lane's UE record ------------------------------------
     const int step = st.step[e], episode = st.episode[e];
     const int win_len = st.win_len[e], head = st.win_head[e];
-    const int p = (head + 1) % W; // window slot of this frame (deque.appendleft)
+    const int p = (head + 1) % A.win_cap; // window slot of this frame (deque.appendleft)
     const irs_scenario* sc = st.bank + st.scen[e];
     const bool ue_lane = lane < U;
     const int s_mine = ue_lane ? (int)sc->ue_slice[lane] : -1;
@@ -67,7 +67,7 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
     const double2 rec_d0 = *reinterpret_cast<const double2*>(st.ue_d + eu * UD_N);     // occ, lat
     const double2 rec_d1 = *reinterpret_cast<const double2*>(st.ue_d + eu * UD_N + 2); // sebar, thr
     int2 evict = make_int2(0, 0);
-    if (ue_lane && win_len == W) evict = st.ring[eu * W + p];
+    if (ue_lane && win_len == A.win_cap) evict = st.ring[eu * W + p];
     const int tot_prev = ue_lane ? rec_a.x : 0;
     int* row = st.buf + eu * (size_t)st.row_stride;
     const int expired = (ue_lane && tot_prev != 0) ? row[up.depth - 1] : 0; // buffer.py:60, in flight early

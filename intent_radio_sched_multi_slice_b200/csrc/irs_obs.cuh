@@ -28,7 +28,9 @@ struct SliceView { // valid on lanes 0..4 (slice = lane)
 };
 
 // common.py:9-65 + 68-340 for one UE; r = intent_overfulfillment_rate 0.2 (ib_sched.py:53)
-__device__ __forceinline__ void intent_drift_ue(const irs_slice* sl, int flags, const UeFrame& f, int win_len,
+// `mul` = 2 when the agent pushes every frame twice into the window (win[1] is then the newest frame again and
+// every window sum counts each kept frame twice), else 1.
+__device__ __forceinline__ void intent_drift_ue(const irs_slice* sl, int flags, const UeFrame& f, int win_len, int mul,
                                                 double (&drift)[3])
 {
     const double r = 0.2;
@@ -37,7 +39,7 @@ __device__ __forceinline__ void intent_drift_ue(const irs_slice* sl, int flags, 
         const double v = __ldg(&sl->thr_value);
         double m = (double)((long long)f.sent * (long long)__ldg(&sl->message_size)) / 1e6; // :26-31
         bool zero = isclose0(f.occ);                                                        // :104-107
-        if (win_len > 1) zero = zero || f.occ1z;                                            // :108-116
+        if (win_len * mul > 1) zero = zero || (mul == 2 ? isclose0(f.occ) : f.occ1z);          // :108-116
         if (zero) m = v * (1.1 + r);                                                        // :117-119
         if (m >= v) {
             if (m > v * (1 + r)) drift[0] += 1;        // :164-168
@@ -48,8 +50,8 @@ __device__ __forceinline__ void intent_drift_ue(const irs_slice* sl, int flags, 
     }
     if (flags & IRS_F_REL) {
         const double v = __ldg(&sl->rel_value);
-        const double den = (f.occ * __ldg(&sl->buffer_size) + (double)f.sum_drop) + (double)f.sum_sent; // :40-47
-        const double m = den != 0 ? (double)f.sum_drop / den : 0.0;                                      // :48-53
+        const double den = (f.occ * __ldg(&sl->buffer_size) + (double)(f.sum_drop * mul)) + (double)(f.sum_sent * mul); // :40-47
+        const double m = den != 0 ? (double)(f.sum_drop * mul) / den : 0.0;                                      // :48-53
         const double t = (100 - v) / 100;
         if (100 * (1 - m) >= v) {                      // :124-126
             if (m < t * (1 - r)) drift[1] += 1;        // :188-220
@@ -91,7 +93,7 @@ __device__ __noinline__ SliceView format_obs_warp(const StepArgs& A, int e, cons
 
     // per-UE drift, then the slice means (common.py:371-373 np.mean over the slice's UEs)
     double drift[3] = {0, 0, 0};
-    if (member && (fl_u & IRS_F_REQ)) intent_drift_ue(sl_u, fl_u, f, win_len, drift);
+    if (member && (fl_u & IRS_F_REQ)) intent_drift_ue(sl_u, fl_u, f, win_len, A.win_mul, drift);
     double dsl_u[3];
     const int fbit[3] = {IRS_F_THR, IRS_F_REL, IRS_F_LAT};
 #pragma unroll

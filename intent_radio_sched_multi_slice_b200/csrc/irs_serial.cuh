@@ -286,9 +286,9 @@ __global__ void __launch_bounds__(SERIAL_THREADS, TAIL_T_MINB) k_env_tail_t(cons
     const size_t eu0 = (size_t)e * U;
     prefetch_env_records(st, eu0);
     const int win_len_old = st.win_len[e], head_old = st.win_head[e], step_old = st.step[e];
-    const int win_len = win_len_old < W ? win_len_old + 1 : W;
+    const int win_len = win_len_old < A.win_cap ? win_len_old + 1 : A.win_cap;
     const int step = step_old + 1; // comm_env.py:339
-    st.win_len[e] = win_len; st.win_head[e] = (head_old + 1) % W; st.step[e] = step;
+    st.win_len[e] = win_len; st.win_head[e] = (head_old + 1) % A.win_cap; st.step[e] = step;
 
     // ---- one pass over the UEs (ascending, so every per-slice sum runs in NumPy's order): totals for the
     //      metrics, per-UE drift (common.py:68-340) accumulated into the UE's slice, per-UE observation tail.
@@ -320,7 +320,7 @@ __global__ void __launch_bounds__(SERIAL_THREADS, TAIL_T_MINB) k_env_tail_t(cons
         f.occ = d0.x; f.lat = d0.y; f.sebar = sebar; f.sent = lo.w; f.sum_sent = lo.y; f.sum_drop = lo.z;
         f.rb_count = st.rb[eu].y; f.occ1z = hi.z != 0;
         double drift[3] = {0, 0, 0};
-        if (fl & IRS_F_REQ) intent_drift_ue(sl, fl, f, win_len, drift);
+        if (fl & IRS_F_REQ) intent_drift_ue(sl, fl, f, win_len, A.win_mul, drift);
         int j = 0;
 #pragma unroll
         for (int ss = 0; ss < S; ++ss) {

@@ -131,11 +131,11 @@ __global__ void __launch_bounds__(UE_WARPS * 32, 4) k_ue_step(const __grid_const
 
     // ---- prologue: every scalar the row needs, one lane each, issued before the generators --
     const int win_len = st.win_len[e];
-    const int p = (st.win_head[e] + 1) % W; // window slot this frame goes to (deque.appendleft)
+    const int p = (st.win_head[e] + 1) % A.win_cap; // window slot this frame goes to (deque.appendleft)
     const int pre_i = lane < UI_N ? st.ue_i[eu * UI_N + lane] : 0;
     const double occ_old_l = lane == 0 ? st.ue_d[eu * UD_N + UD_OCC] : 0.0;
     int2 evict = make_int2(0, 0);
-    if (lane == 0 && win_len == W) evict = st.ring[(eu * W) + p];
+    if (lane == 0 && win_len == A.win_cap) evict = st.ring[(eu * W) + p];
     const short2 run = st.rb[eu];
     const irs_scenario* sc = st.bank + st.scen[e];
     const int s = sc->ue_slice[u];

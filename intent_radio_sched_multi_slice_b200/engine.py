@@ -45,7 +45,7 @@ class BatchEngine:
     def __init__(self, bank: ScenarioBank, num_envs: int, *, device="cuda:0", depth_cap=None,
                  channel_mode=2, traffic_mode=1, sort_slices=1, fixed_intra=-1, policy=0, assoc_mode=0,
                  scen_mod=200, scen_div=100, max_steps=1000, max_episodes=10000, initial_episode=0,
-                 auto_reset=0, env_id_base=0, seed=10, bandwidth=1e8):
+                 auto_reset=0, env_id_base=0, seed=10, bandwidth=1e8, surface=0):
         if not torch.cuda.is_available():
             raise RuntimeError("intent_radio_sched_multi_slice_b200 needs a CUDA device (there is no CPU path)")
         self.lib = capi.load()
@@ -57,7 +57,7 @@ class BatchEngine:
             depth_cap = max(bank.max_depth(), 101)  # 101: default depth of unassociated UEs (comm_env.py:184-198)
         self.cfg = capi.Config(self.E, int(depth_cap), channel_mode, traffic_mode, sort_slices, fixed_intra, policy,
                                assoc_mode, scen_mod, scen_div, len(self.bank_array), max_steps, max_episodes,
-                               initial_episode, auto_reset, env_id_base, seed, bandwidth)
+                               initial_episode, auto_reset, env_id_base, surface, 0, seed, bandwidth)
         self.h = C.c_void_p()
         rc = self.lib.irs_create(C.byref(self.cfg), self.cdf.shape[0], C.byref(self.h))
         if rc:

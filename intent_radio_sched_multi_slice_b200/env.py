@@ -118,7 +118,7 @@ class BatchedMARLCommEnv:
             kw = dict(channel_mode=2, traffic_mode=1, assoc_mode=0, scen_mod=200, scen_div=100)
             kw.update(self._modes)
             self.eng = BatchEngine(self.bank, self.num_envs, device=self.device, sort_slices=s.sort_slices,
-                                   fixed_intra=s.fixed_intra, policy=s.policy, max_steps=self.max_number_steps,
+                                   fixed_intra=s.fixed_intra, policy=s.policy, surface=s.surface, max_steps=self.max_number_steps,
                                    max_episodes=self.max_number_episodes, initial_episode=self.initial_episode_number,
                                    auto_reset=int(self.auto_reset), env_id_base=self.env_id_base, seed=self.seed,
                                    bandwidth=float(self.bandwidths[0]), **kw)

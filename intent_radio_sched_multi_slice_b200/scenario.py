@@ -14,7 +14,15 @@ MAX_SLICES = 5  # env_config/mult_slice.yml:13
 NUM_RBS = 135  # env_config/mult_slice.yml:5
 POISSON_K = 256
 
-F_ACTIVE, F_REQ, F_THR, F_REL, F_LAT = 1, 2, 4, 8, 16
+F_ACTIVE, F_REQ, F_THR, F_REL, F_LAT, F_EMBB, F_URLLC = 1, 2, 4, 8, 16, 32, 64
+
+# agents/sched_colran.py:352-363: use case(s) of every slice type (SchedColORAN's reward)
+USE_CASES = {
+    "control_case_2": F_URLLC, "monitoring_case_1": F_EMBB, "robotic_surgery_case_1": F_EMBB | F_URLLC,
+    "robotic_diagnosis": F_URLLC, "medical_monitoring": F_EMBB, "uav_app_case_1": F_EMBB,
+    "uav_control_non_vlos": F_EMBB, "vr_gaming": F_EMBB | F_URLLC, "cloud_gaming": F_EMBB,
+    "video_streaming_4k": F_EMBB,
+}
 
 # Restated from associations/mult_slice.py:58-347.  Columns:
 # name, priority, reliability %, latency ms, throughput Mbps (None = intent not declared),
@@ -105,7 +113,7 @@ class ScenarioBank:
             if active:
                 flags |= F_ACTIVE
             if req != {}:
-                flags |= F_REQ
+                flags |= F_REQ | USE_CASES.get(req.get("name"), F_EMBB)
                 ue = req["ues"]
                 sl["priority"] = req["priority"]
                 sl["traffic"] = ue["traffic"]

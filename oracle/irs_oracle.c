@@ -32,7 +32,7 @@
 #define POISSON_K 256
 
 /* ---- scenario bank row (mirrors include/irs_b200.h; restated, not included) ---- */
-enum { F_ACTIVE = 1, F_REQ = 2, F_THR = 4, F_REL = 8, F_LAT = 16 };
+enum { F_ACTIVE = 1, F_REQ = 2, F_THR = 4, F_REL = 8, F_LAT = 16, F_EMBB = 32, F_URLLC = 64 };
 typedef struct {
     double priority, traffic, buffer_size, buffer_latency, message_size;
     double thr_value, rel_value, lat_value;
@@ -55,6 +55,7 @@ typedef struct {
     int32_t scen_mod, scen_div, n_scen;
     int32_t max_steps, max_episodes, initial_episode;
     int32_t auto_reset, env_id_base;
+    int32_t surface, pad0;            /* 0 IBSched family, 1 SchedTWC, 2 SchedColORAN (double window push) */
     uint64_t seed;
     double bandwidth;
 } orc_config;
@@ -62,6 +63,7 @@ typedef struct {
 typedef struct {
     double occ[U], lat[U], sebar[U];
     int32_t sent[U], dropped[U], rb_count[U];
+    double thr[U]; /* pkt_throughputs (SchedTWC / SchedColORAN observations) */
 } orc_frame;
 
 typedef struct {
@@ -325,6 +327,7 @@ static void ues_step(const orc_handle *h, int e, const orc_scenario *sc, const d
         fr->rb_count[u] = rb_count[u];
         aux->pkt_incoming[u] = inc;
         aux->pkt_throughputs[u] = thr;
+        fr->thr[u] = thr;
     }
 }
 
@@ -578,6 +581,88 @@ static void intent_drift_ue(const orc_env *env, const orc_slice *sl, int u, doub
         } else {
             drift[2] -= (m - v) / (sl->buffer_latency - v);                      /* :322-335 */
         }
+    }
+}
+/* SchedTWC / SchedColORAN (agents/sched_twc.py:166-413, agents/sched_colran.py:166-417): 50-value observation
+ * and scalar reward, evaluated on the window AFTER the agents' second push of the frame (sched_twc.py:176-179):
+ * env->win then holds every frame twice, exactly like the reference's deque. */
+static double np_mean_small(const double *a, int n) { return np_sum(a, n) / (double)n; }
+static void alt_surface(const orc_handle *h, const orc_env *env, const orc_scenario *sc, double *obs /*[50]*/,
+                        double *reward /* NULL at reset */)
+{
+    const orc_frame *f0 = &env->win[0];
+    double valid[15], weights[15];
+    int nv = 0;
+    double r_col = 0;
+    for (int s = 0; s < S; ++s) {
+        const orc_slice *sl = &sc->sl[s];
+        int ues[U], n = slice_ues(sc, s, ues);
+        double req[3] = {0, 0, 0};
+        if (n != 0) {                                           /* sched_twc.py:217-229 */
+            if (sl->flags & F_REL) req[0] = sl->rel_value;
+            if (sl->flags & F_LAT) req[1] = sl->lat_value;
+            if (sl->flags & F_THR) req[2] = sl->thr_value;
+        }
+        for (int k = 0; k < 3; ++k) obs[3 * s + k] = req[k];
+        double pkt = n != 0 ? sl->message_size : 0;             /* :234-240 */
+        double se[NS], thr[NS], eff[NS], occ[NS], lat[NS], loss[NS], thr_pk[NS];
+        for (int i = 0; i < n && i < NS; ++i) {
+            int u = ues[i];
+            se[i] = f0->sebar[u];
+            thr_pk[i] = f0->thr[u];
+            thr[i] = (f0->thr[u] * pkt) / 1e6;                  /* pkts_to_mbps :430-431 */
+            eff[i] = (double)((int64_t)f0->sent[u] * (int64_t)pkt) / 1e6;
+            occ[i] = f0->occ[u];
+            lat[i] = f0->lat[u];
+            int64_t snt = 0, drp = 0;                           /* get_metric_value "reliability", common.py:32-53 */
+            for (int k = 0; k < env->win_len; ++k) { snt += env->win[k].sent[u]; drp += env->win[k].dropped[u]; }
+            double den = (f0->occ[u] * sl->buffer_size + (double)drp) + (double)snt;
+            loss[i] = den != 0 ? (double)drp / den : 0.0;
+        }
+        obs[15 + s] = n ? np_mean_small(se, n) : 0.0;
+        obs[20 + s] = n ? np_mean_small(thr, n) : 0.0;
+        obs[25 + s] = n ? np_mean_small(eff, n) : 0.0;
+        obs[30 + s] = n ? np_mean_small(occ, n) : 0.0;
+        obs[35 + s] = n ? np_mean_small(lat, n) : 0.0;
+        obs[40 + s] = n ? np_mean_small(loss, n) : 0.0;
+        obs[45 + s] = (sl->flags & F_ACTIVE) ? sl->traffic : 0.0; /* :319-336 */
+        if (!reward || n == 0) continue;
+        /* TWC: slice drift per declared intent (calculate_slice_ue_obs, common.py:343-378) */
+        double dsum[3][NS];
+        for (int i = 0; i < n; ++i) {
+            double d[3] = {0, 0, 0};
+            if (sl->flags & F_REQ) intent_drift_ue(env, sl, ues[i], d);
+            for (int k = 0; k < 3; ++k) dsum[k][i] = d[k];
+        }
+        const int fbit[3] = {F_THR, F_REL, F_LAT};
+        for (int k = 0; k < 3; ++k) {
+            double d = ((sl->flags & F_REQ) && (sl->flags & fbit[k])) ? np_mean_small(dsum[k], n) : -2.0;
+            if (fabs(d - (-2.0)) <= 1e-8 + 1e-5 * 2.0) continue; /* np.isclose(x, -2) */
+            valid[nv] = d > 0 ? 0.0 : d;                          /* sched_twc.py:392-394 */
+            weights[nv] = sl->priority != 0 ? 2.0 : 1.0;          /* :382-390 */
+            ++nv;
+        }
+        /* ColORAN (sched_colran.py:364-415) */
+        if (sl->flags & F_ACTIVE) {
+            if (sl->flags & F_EMBB) r_col += ((np_mean_small(thr_pk, n) * sl->message_size) / 1e6) / 200.0;
+            if (sl->flags & F_URLLC) r_col -= (((np_mean_small(occ, n) * sl->buffer_size) * sl->message_size) / 1e6) / 2000.0;
+        }
+    }
+    if (!reward) return;
+    if (h->cfg.surface == 1) {
+        double neg[15], nw[15];
+        int m = 0;
+        for (int i = 0; i < nv; ++i) if (valid[i] < 0) { neg[m] = valid[i]; nw[m] = weights[i]; ++m; }
+        double wsum = np_sum(nw, m);
+        if (!np_isclose0(wsum)) {
+            double t[15];
+            for (int i = 0; i < m; ++i) t[i] = (neg[i] * nw[i]) / wsum;
+            *reward = np_sum(t, m);
+        } else {
+            *reward = 0.0;
+        }
+    } else {
+        *reward = r_col;
     }
 }
 /* ib_sched.py:351-370: stable ascending argsort of n_ues * traffic */
@@ -846,8 +931,10 @@ static int reset_one(orc_handle *h, int e, int initial_episode, const double *se
     memset(&fr, 0, sizeof(fr));                                /* :474-478 zero metrics */
     for (int u = 0; u < U; ++u) fr.sebar[u] = np_sum(se + u * R, R) / (double)R;
     window_push(env, &fr);                                     /* quirk Q1: window survives reset */
+    if (c->surface) window_push(env, &fr);
     orc_obs o;
     obs_space_format(h, env, &h->bank[env->scen], &o);
+    if (c->surface) alt_surface(h, env, &h->bank[env->scen], o.obs0, NULL);
     write_obs(io, e, &o);
     return 0;
 }
@@ -882,10 +969,12 @@ static int step_one(orc_handle *h, int e, const double *a0_in, const int32_t *in
     ues_step(h, e, sc, se, traffic, rb_start, rb_count, &fr, &aux); /* :320-326 */
     env->step += 1;                                            /* :339 */
     window_push(env, &fr);
+    if (c->surface) window_push(env, &fr);                     /* sched_twc.py:176-179: the frame is pushed twice */
     orc_obs o;
     obs_space_format(h, env, sc, &o);                          /* :340 */
     double reward[6];
     calculate_reward(env, sc, reward);                         /* :341 */
+    if (c->surface) alt_surface(h, env, sc, o.obs0, &reward[0]);
     accumulate_metrics(env, sc, &aux, reward);
     int done = env->step == c->max_steps;                      /* :370 */
     if (done) env->acc[15] += 1;

@@ -31,7 +31,7 @@ class Config(C.Structure):
     _fields_ = [(n, C.c_int32) for n in (
         "num_envs", "depth_cap", "channel_mode", "traffic_mode", "sort_slices", "fixed_intra", "policy",
         "assoc_mode", "scen_mod", "scen_div", "n_scen", "max_steps", "max_episodes", "initial_episode",
-        "auto_reset", "env_id_base")] + [("seed", C.c_uint64), ("bandwidth", C.c_double)]
+        "auto_reset", "env_id_base", "surface", "pad0")] + [("seed", C.c_uint64), ("bandwidth", C.c_double)]
 
 
 _IO_FIELDS = ["pkt_incoming", "pkt_throughputs", "sent", "dropped", "occ", "lat", "rb_start", "rb_count",
@@ -132,7 +132,7 @@ class OracleEnv:
 
     def __init__(self, bank_array, poisson_cdf, num_envs=1, depth_cap=None, channel_mode=0, traffic_mode=0,
                  sort_slices=1, fixed_intra=-1, policy=0, assoc_mode=0, scen_mod=200, scen_div=100,
-                 max_steps=1000, max_episodes=10000, initial_episode=0, auto_reset=0, env_id_base=0, seed=10,
+                 max_steps=1000, max_episodes=10000, initial_episode=0, auto_reset=0, env_id_base=0, seed=10, surface=0,
                  bandwidth=1e8):
         self.bank = np.ascontiguousarray(bank_array)
         assert self.bank.dtype.itemsize == 432
@@ -143,7 +143,7 @@ class OracleEnv:
         self.depth_cap = depth_cap
         self.cfg = Config(num_envs, depth_cap, channel_mode, traffic_mode, sort_slices, fixed_intra, policy,
                           assoc_mode, scen_mod, scen_div, len(self.bank), max_steps, max_episodes,
-                          initial_episode, auto_reset, env_id_base, seed, bandwidth)
+                          initial_episode, auto_reset, env_id_base, surface, 0, seed, bandwidth)
         self.h = lib().orc_create(C.byref(self.cfg), _ptr(self.bank), _ptr(self.cdf))
         E = num_envs
         self.out = {

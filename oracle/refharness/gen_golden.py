@@ -33,6 +33,11 @@ def rand_actions(seed):
     return f
 
 
+def rand_flat(seed):
+    rng = np.random.default_rng(seed)
+    return lambda k, obs, ag: rng.uniform(-1, 1, 5)
+
+
 def policy(k, obs, ag):
     return ag.step(obs)
 
@@ -49,6 +54,9 @@ TRACES = {
     # QuadrigaChannel / QuadrigaChannelSeq over synthetic power files (shims._install_h5py)
     "quadriga": ("ib_sched", "quadriga", "mult_slice", 17, 3, 100, 30, None, 6),
     "quadriga_seq": ("ib_sched", "quadriga_seq", "mult_slice_seq", 18, 99, 100, 30, None, 7),
+    # the baseline agents' surfaces (negative action seed: flat 5-vector actions)
+    "twc": ("sched_twc", "mimic", "mult_slice", 19, 4, 300, 100, None, -8),
+    "colran": ("sched_colran", "mimic", "mult_slice", 20, 8, 300, 100, None, -9),
 }
 
 
@@ -65,7 +73,7 @@ def record(name):
     shims.QUADRIGA_STEPS["n"] = max_steps
     env, ag = refenv.make_env(wd, agent=agent, channel=channel, assoc=assoc, seed=seed,
                               initial_episode=init_ep, max_episode_number=max_eps)
-    fn = policy if act_seed is None else rand_actions(act_seed)
+    fn = policy if act_seed is None else (rand_actions(act_seed) if act_seed > 0 else rand_flat(-act_seed))
     steps, resets, ckpt = refenv.run_trace(env, ag, n_steps, fn, seed, init_ep)
     from golden_inputs import bits_checksum
 

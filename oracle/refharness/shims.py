@@ -117,6 +117,7 @@ def install():
         m = _mod(name)
         m.__getattr__ = lambda k: _Any()  # type: ignore
     _install_h5py()
+    _install_sb3()
     for pkg in ("agents", "channels", "traffics", "associations", "mobilities"):
         m = types.ModuleType(pkg)
         m.__path__ = [f"{REF}/{pkg}"]
@@ -124,6 +125,29 @@ def install():
     for p in (REF, f"{REF}/sixg_radio_mgmt"):
         if p not in sys.path:
             sys.path.insert(0, p)
+
+
+def _install_sb3():
+    """stable_baselines3 is absent; agents/sched_twc.py and agents/sched_colran.py import PPO / SAC and callback
+    classes at module level but their env adapters (obs_space_format, action_format, calculate_reward) never touch
+    them: inert stand-ins."""
+    class _Inert:
+        def __init__(self, *a, **k):
+            pass
+
+    class _Event(_Inert):
+        pass
+
+    cb = _mod("stable_baselines3.common.callbacks", CheckpointCallback=_Inert, BaseCallback=_Inert, EvalCallback=_Inert,
+              EventCallback=_Event)
+    ev = _mod("stable_baselines3.common.evaluation", evaluate_policy=lambda *a, **k: None)
+    ve = _mod("stable_baselines3.common.vec_env", DummyVecEnv=_Inert, VecEnv=_Inert, sync_envs_normalization=lambda *a, **k: None)
+    common = _mod("stable_baselines3.common", callbacks=cb, evaluation=ev, vec_env=ve)
+    ppo = _mod("stable_baselines3.ppo.ppo", PPO=_Inert)
+    sac = _mod("stable_baselines3.sac.sac", SAC=_Inert)
+    _mod("stable_baselines3.ppo", ppo=ppo, PPO=_Inert)
+    _mod("stable_baselines3.sac", sac=sac, SAC=_Inert)
+    _mod("stable_baselines3", common=common, PPO=_Inert, SAC=_Inert)
 
 
 QUADRIGA_STEPS = {"n": 1000}  # frames per synthetic target_cell_power.mat

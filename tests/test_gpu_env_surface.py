@@ -40,7 +40,8 @@ def _trace_plugins(rse, sse, stf):
 
 @pytest.mark.parametrize("name,agent,n", [("ibsched_mimic", "IBSched", 150), ("seq_fixed", "IBSched", 100),
                                           ("cfg1_marr", "MARR", 120), ("mapf", "MAPF", 120),
-                                          ("quadriga", "IBSched", 100), ("quadriga_seq", "IBSched", 100)])
+                                          ("quadriga", "IBSched", 100), ("quadriga_seq", "IBSched", 100),
+                                          ("twc", "SchedTWC", 220), ("colran", "SchedColORAN", 220)])
 def test_env_api_replays_reference_trace(name, agent, n, bank):
     from intent_radio_sched_multi_slice_b200 import agents, plugins
     from intent_radio_sched_multi_slice_b200.env import MARLCommEnv
@@ -74,6 +75,8 @@ def test_env_api_replays_reference_trace(name, agent, n, bank):
             np.testing.assert_allclose(obs[f"player_{s + 1}"]["observations"], oi[s], rtol=1e-5, atol=0, err_msg=tag)
             assert np.array_equal(obs[f"player_{s + 1}"]["action_mask"], mi[s])
 
+    if "agent_obs" in d:  # SchedTWC / SchedColORAN return their own 50-vector
+        d["obs0"], d["reset_obs0"] = d["agent_obs"], d["reset_agent_obs"]
     check_obs(obs, d["reset_obs0"][0], d["reset_mask0"][0], d["reset_obs_i"][0], d["reset_mask_i"][0],
               d["reset_order"][0], "reset")
     ri = 0
@@ -83,7 +86,7 @@ def test_env_api_replays_reference_trace(name, agent, n, bank):
             action = {"player_0": d["a0"][k]}
             action.update({f"player_{i + 1}": int(d["intra"][k][i]) for i in range(5)})
         else:
-            action = ag.step(obs)  # DEVICE_POLICY: MARR / MAPF scores are computed on the device
+            action = d["a0"][k] if agent.startswith("Sched") else ag.step(obs)  # DEVICE_POLICY: MARR / MAPF on the device
         obs, reward, term, trunc, info = env.step(action)
         check_obs(obs, d["obs0"][k], d["mask0"][k], d["obs_i"][k], d["mask_i"][k], d["order"][k], f"step {k}")
         done = bool(d["done"][k])

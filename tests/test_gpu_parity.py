@@ -23,13 +23,14 @@ def per_env_kernels(request, monkeypatch):
     8,192 envs per launch; irs_serial.cuh)."""
     monkeypatch.setenv("IRS_SERIAL_MIN_ENVS", "1" if request.param == "thread_per_env" else str(1 << 30))
 
-TRACES = ["cfg1_marr", "mapf", "ibsched_mimic", "ibsched_fixed", "seq_mimic", "seq_fixed", "sweep_scen"]
+TRACES = ["cfg1_marr", "mapf", "ibsched_mimic", "ibsched_fixed", "seq_mimic", "seq_fixed", "sweep_scen", "twc", "colran"]
 
 
 def _cuda_env_factory(bank):
     def make(meta):
         sort, fixed = trace_replay.agent_config(meta)
         return CudaEnv(bank, 1, channel_mode=0, traffic_mode=0, sort_slices=sort, fixed_intra=fixed,
+                       surface=trace_replay.agent_surface(meta),
                        assoc_mode=0 if meta["assoc"] == "mult_slice" else 1, max_steps=int(meta["max_steps"]),
                        max_episodes=int(meta["max_episodes"]), initial_episode=int(meta["initial_episode"]))
     return make
@@ -84,6 +85,8 @@ def test_buffer_main_known_answer():
     dict(policy=1, fixed_intra=0, sort_slices=0, channel_mode=2, assoc_mode=0),
     dict(policy=2, fixed_intra=1, sort_slices=0, channel_mode=2, assoc_mode=0),
     dict(policy=3, fixed_intra=-1, sort_slices=1, channel_mode=1, assoc_mode=1),
+    dict(policy=3, fixed_intra=0, sort_slices=0, channel_mode=2, assoc_mode=0, surface=1),  # SchedTWC surface
+    dict(policy=3, fixed_intra=0, sort_slices=0, channel_mode=2, assoc_mode=0, surface=2),  # SchedColORAN surface
 ])
 def test_batch_native_matches_oracle(bank, cfg):
     """256 envs, native counter-based generators, on-device policy, auto-reset across several

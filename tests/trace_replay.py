@@ -16,7 +16,12 @@ GOLD_KEY = {"sent": "pkt_effective_thr", "dropped": "dropped_pkts", "occ": "buff
 
 def agent_config(meta):
     """(sort_slices, fixed_intra) of the reference agent (ib_sched.py:57; marr.py:66; mapf.py:130)."""
-    return {"ib_sched": (1, -1), "marr": (0, 0), "mapf": (0, 1)}[meta["agent"]]
+    return {"ib_sched": (1, -1), "marr": (0, 0), "mapf": (0, 1), "sched_twc": (0, 0), "sched_colran": (0, 0)}[meta["agent"]]
+
+
+def agent_surface(meta):
+    """cfg.surface of the reference agent: 0 IBSched family, 1 SchedTWC, 2 SchedColORAN."""
+    return {"sched_twc": 1, "sched_colran": 2}.get(meta["agent"], 0)
 
 
 def replay(name, make_env, tight=False):
@@ -34,8 +39,13 @@ def replay(name, make_env, tight=False):
         else:
             np.testing.assert_allclose(got, want, rtol=rtol, atol=1e-300, err_msg=f"{name}: {tag} at step {k}")
 
+    alt = "agent_obs" in d  # SchedTWC / SchedColORAN: the surface is the agent's own 50-vector; the IBSched dict of
+    #                         their internal fake agent (computed before the frame's second push) is not observable
+
     def cmp_reset(out, ri, k):
-        for key in ("obs0", "obs_i"):
+        if alt:
+            cmp("reset agent obs", out["obs0"][0], d["reset_agent_obs"][ri], k, False)
+        for key in (() if alt else ("obs0", "obs_i")):
             cmp("reset " + key, out[key][0], d["reset_" + key][ri], k, False)
         for key in ("mask0", "mask_i", "sorted_slices"):
             cmp("reset " + key, out[key][0], d["reset_" + key][ri], k, True)
@@ -49,7 +59,11 @@ def replay(name, make_env, tight=False):
         for key in EXACT:
             cmp(key, out[key][0], d[GOLD_KEY.get(key, key)][k], k, True)
         for key in CLOSE:
+            if alt and key in ("obs0", "obs_i"):
+                continue
             cmp(key, out[key][0], d[GOLD_KEY.get(key, key)][k], k, False)
+        if alt:
+            cmp("agent obs", out["obs0"][0], d["agent_obs"][k], k, False)
         r = d["reward"][k]
         if np.isnan(r[1]):
             cmp("reward", out["reward"][0, 0], r[0], k, False)
