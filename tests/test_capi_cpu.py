@@ -32,7 +32,7 @@ def test_library_builds_and_exports_every_declared_symbol():
 
 
 def test_struct_sizes_match_the_header():
-    assert C.sizeof(capi.Config) == 16 * 4 + 8 + 8
+    assert C.sizeof(capi.Config) == 18 * 4 + 8 + 8
     assert scenario.SCENARIO_DTYPE.itemsize == 432 and scenario.SLICE_DTYPE.itemsize == 80
     assert C.sizeof(capi.RawOutputs) == 13 * 8 and C.sizeof(capi.HostSurface) == 9 * 8
 
