@@ -30,7 +30,8 @@ struct irs_env {
 
     cudaEvent_t chunk_ev[IRS_MAX_HOST_CHUNKS];
     bool have_copy;
-    int host_chunks;               // IRS_HOST_CHUNKS (0 = choose from the batch size)
+    int host_chunks;               // IRS_HOST_CHUNKS (0 = whole waves of the row kernel, about five chunks)
+    size_t wave_envs;              // envs one full wave of k_ue_env covers on this device (0 = not queried yet)
     int serial_min;                // IRS_SERIAL_MIN_ENVS (default 49,152): launches covering at least this many envs
                                    // use the thread-per-env action / tail kernels (irs_serial.cuh); below that one
                                    // thread per env leaves the SMs too empty to hide its serial latency
@@ -442,16 +443,38 @@ static int copy_surface(irs_env* env, const irs_host_surface* o, bool with_rewar
     return IRS_OK;
 }
 
-// How many chunks irs_step_host splits the batch into: the surface of a finished chunk crosses
-// PCIe while the next chunk computes.  Small batches stay whole (launch latency dominates).
-static int host_chunk_count(const irs_env* env)
+// How irs_step_host splits the batch: the surface of a finished chunk crosses PCIe while the next chunk computes.
+// Chunks are whole WAVES of the row kernel (resident blocks per SM x SMs x envs per block), so that chunking does not
+// add a partly filled last wave to every chunk; about five chunks per step.  Small batches stay whole (launch latency
+// dominates).  IRS_HOST_CHUNKS=n forces n equal chunks.
+static int host_chunk_plan(irs_env* env, size_t* bounds /* [IRS_MAX_HOST_CHUNKS + 1] */)
 {
-    int c = env->host_chunks;
-    if (c <= 0) c = env->cfg.num_envs / 8192;
-    if (c < 1) c = 1;
-    if (c > 8 && env->host_chunks <= 0) c = 8;
-    if (c > IRS_MAX_HOST_CHUNKS) c = IRS_MAX_HOST_CHUNKS;
-    return c;
+    const size_t E = (size_t)env->cfg.num_envs;
+    int chunks;
+    size_t per;
+    if (env->host_chunks > 0) {
+        chunks = env->host_chunks > IRS_MAX_HOST_CHUNKS ? IRS_MAX_HOST_CHUNKS : env->host_chunks;
+        per = (E + chunks - 1) / chunks;
+    } else if (E < 16384) {
+        chunks = 1;
+        per = E;
+    } else {
+        if (env->wave_envs == 0) {
+            int dev = 0, sms = 0, nb = 0;
+            if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
+                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_ue_env, FUSED_WARPS * 32, 0) != cudaSuccess || sms <= 0 || nb <= 0) {
+                sms = 148; nb = UE_ENV_MINB;
+            }
+            env->wave_envs = (size_t)sms * nb * FUSED_WARPS;
+        }
+        const size_t waves = (E + env->wave_envs - 1) / env->wave_envs;
+        const size_t wpc = (waves + 4) / 5; // waves per chunk: about five chunks
+        per = wpc * env->wave_envs;
+        chunks = (int)((E + per - 1) / per);
+        if (chunks > IRS_MAX_HOST_CHUNKS) { chunks = IRS_MAX_HOST_CHUNKS; per = (E + chunks - 1) / chunks; }
+    }
+    for (int c = 0; c <= chunks; ++c) bounds[c] = (size_t)c * per < E ? (size_t)c * per : E;
+    return chunks;
 }
 
 int irs_step_host(irs_env* env, const irs_actions* actions_host, const irs_host_surface* out_host, void* stream)
@@ -474,7 +497,8 @@ int irs_step_host(irs_env* env, const irs_actions* actions_host, const irs_host_
             A.intra = env->st.in_intra;
         } else if (env->cfg.fixed_intra < 0) return fail(env, IRS_ERR_ARG, "fixed_intra -1 needs actions.intra");
     }
-    const int chunks = host_chunk_count(env);
+    size_t bounds[IRS_MAX_HOST_CHUNKS + 1];
+    const int chunks = host_chunk_plan(env, bounds);
     if (chunks == 1) {
         rc = launch_step(env, A, st);
         if (rc) return rc;
@@ -487,9 +511,8 @@ int irs_step_host(irs_env* env, const irs_actions* actions_host, const irs_host_
     }
     // One compute stream: a chunk must FINISH early for its copy to start early (two alternating compute
     // streams were measured slower - both chunks then finish late, profiles/r1_notes.md).
-    const size_t per = (E + chunks - 1) / chunks;
     for (int c = 0; c < chunks; ++c) {
-        const size_t e0 = c * per, e1 = e0 + per < E ? e0 + per : E;
+        const size_t e0 = bounds[c], e1 = bounds[c + 1];
         if (e0 >= e1) break;
         A.env_begin = (int32_t)e0;
         A.env_end = (int32_t)e1;
