@@ -34,6 +34,9 @@ def parse():
     p.add_argument("--warmup", type=int, default=20)
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
     p.add_argument("--envs", type=int, default=65536, help="env instances per GPU (weak scaling)")
+    p.add_argument("--fill", type=int, default=-1,
+                   help="untimed steps before the warm-up that fill the packet buffers to their steady state "
+                        "(default: the deepest row of the workload)")
     p.add_argument("--depth", type=int, default=0,
                    help="buffer depth of the sweep workload (BASELINE config 5: 401, 1024, 4096); default 1024")
     p.add_argument("--workload", default="sweep", choices=["sweep", "mix", "cfg2", "trace"],
@@ -41,7 +44,9 @@ def parse():
                         "configuration the metric is quoted on at 1/2/4/8 GPUs; mix: the 200-scenario mult_slice mix "
                         "(D 21..401); cfg2: BASELINE config 2 (1,024 envs); trace: QuadrigaChannel-shaped SE bank in HBM")
     p.add_argument("--trace-steps", type=int, default=16, help="frames per episode of the SE bank (wraps around)")
-    p.add_argument("--cpu-envs", type=int, default=2048, help="env instances of the CPU baseline sample")
+    p.add_argument("--cpu-envs", type=int, default=0,
+                   help="env instances of the CPU baseline sample (default 512 for the sweep, whose buffers take "
+                        "thousands of steps to fill, else 2048)")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
     a = p.parse_args()
@@ -77,8 +82,37 @@ def make_bank(depth: int):
 
 def engine_kwargs(args, rank):
     return dict(channel_mode=3 if args.workload == "trace" else 2, traffic_mode=1, sort_slices=1, fixed_intra=-1, policy=0, assoc_mode=0,
-                scen_mod=200, max_steps=1000, max_episodes=10000, auto_reset=1, seed=10,
+                scen_mod=200, max_steps=episode_steps(args), max_episodes=10000, auto_reset=1, seed=10,
                 env_id_base=rank * args.envs)
+
+
+def episode_steps(args):
+    """mult_slice.yml's 1000-step episodes; the depth sweep never rolls over, so that its rows stay
+    fully live (aged across the whole row, expiring at the old end) for the whole measurement."""
+    return 1_000_000 if args.workload == "sweep" else 1000
+
+
+def fill_to_steady_state(args, bank, eng, pool):
+    """Untimed steps that bring the packet buffers to their steady state before anything is measured.
+    The row kernel only touches a row's live extent (slots up to the oldest packet), which keeps growing
+    for about 1.7 x depth steps in the sweep profile (backlog grows, the capacity clip sets in, then the
+    oldest packets reach the expiry age).  Steps in blocks of 128 until the mean live extent moves by
+    less than 0.5 % per block (or --fill steps exactly, when given)."""
+    if args.fill >= 0:
+        for k in range(args.fill):
+            eng.step(*pool[k % 4])
+        return args.fill
+    cap = min(4 * bank.max_depth(), episode_steps(args) // 2)  # mult_slice episodes: stay clear of the rollover
+    n, prev = 0, -1.0
+    while n < cap:
+        for k in range(128):
+            eng.step(*pool[k % 4])
+        n += 128
+        live = float(((eng.v["path"] >> 2) & 0x3FFF).float().mean().item())
+        if prev >= 0 and abs(live - prev) <= 0.005 * max(live, 1.0):
+            break
+        prev = live
+    return n
 
 
 class ClockSampler:
@@ -126,9 +160,20 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def cpu_oracle_run(args, bank, n_envs, warmup, steps=None, budget_s=12.0):
+def cpu_fill_steps(args, bank):
+    """Steps the GPU arm's plateau detection settles on (config.fill_steps of its bench lines): the CPU
+    sample is brought to the same steady state before it is timed (its drain loop is FASTER on full rows)."""
+    if args.fill >= 0:
+        return args.fill
+    if args.workload != "sweep":
+        return 512
+    return {401: 1664, 1024: 2944, 4096: 4736}.get(bank.max_depth(), 3 * bank.max_depth())
+
+
+def cpu_oracle_run(args, bank, n_envs, warmup, steps=None, budget_s=12.0, fill=0):
     """The oracle port (oracle/irs_oracle.c, OpenMP over envs) on the host cores: same scenario
     bank, generators, agent surface and action distribution as the GPU arm."""
+    n_envs = n_envs or (512 if args.workload == "sweep" else 2048)
     from oracle import oracle
 
     kw = engine_kwargs(args, 0)
@@ -148,7 +193,7 @@ def cpu_oracle_run(args, bank, n_envs, warmup, steps=None, budget_s=12.0):
         m[:] = (np.arange(n_envs) % 200) == e0
         if m.any():
             env.reset(mask=m, initial_episode=e0)
-    for k in range(warmup):
+    for k in range(fill + warmup):
         env.step(*pool[k % 4])
     if steps is None:
         t = time.perf_counter()
@@ -162,7 +207,8 @@ def cpu_oracle_run(args, bank, n_envs, warmup, steps=None, budget_s=12.0):
     dt = time.perf_counter() - t
     env.close()
     return {"value": n_envs * U * steps / dt, "unit": "UE-steps/s", "cores": cores, "kind": "port",
-            "sample": f"{n_envs} envs x {steps} steps of the same workload, oracle/irs_oracle.c with OpenMP on {cores} threads",
+            "sample": f"{n_envs} envs x {steps} steps of the same workload after {fill} untimed fill steps, "
+                      f"oracle/irs_oracle.c with OpenMP on {cores} threads", "envs": n_envs,
             "seconds": dt, "ms_per_step": dt / steps * 1e3, "steps": steps}
 
 
@@ -175,7 +221,8 @@ def run_reference(args):
         return
     bank, wl = make_bank(args.depth)
     n_envs = args.cpu_envs
-    r = cpu_oracle_run(args, bank, n_envs, args.warmup, steps=args.steps)
+    r = cpu_oracle_run(args, bank, n_envs, args.warmup, steps=args.steps, fill=cpu_fill_steps(args, bank))
+    n_envs = r["envs"]
     line = {
         "impl": "reference", "metric": "UE-steps/sec (env-steps/sec x UEs)", "value": r["value"], "unit": "UE-steps/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
@@ -246,6 +293,7 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
+    n_fill = fill_to_steady_state(args, bank, eng, pool)
     for k in range(Wm):
         eng.step(*pool[k % 4])
     barrier()
@@ -289,15 +337,17 @@ def run_b200(args):
     kms = np.zeros(3)
     ue_bytes = 0.0
     path_frac = np.zeros(3)
+    live_frac = 0.0
     for k in range(P):
         if flush is not None:
             flush.fill_(k & 255)
         kms += np.array(eng.step_profiled(*pool[k % 4]))
         # bytes the row kernel had to move in THIS launch: per-UE records for every row, plus the
         # buffer row by the path the kernel took (DESIGN.md "Algorithmic bytes")
-        path = eng.v["path"].long()
-        dep = depth_tab_t[eng.v["scen"].long()]
-        row_b = torch.where(path == 2, 8 * dep, torch.where(path == 1, 4 * dep, torch.full_like(dep, 4)))
+        word = eng.v["path"].long()  # path | live extent << 2 | slots touched << 16 (irs_common.cuh)
+        path, dep = word & 3, word >> 16
+        live_frac += float(((word >> 2) & 0x3fff).float().sum().item() / depth_tab_t[eng.v["scen"].long()].sum().item())
+        row_b = torch.where(path == 2, 8 * dep, torch.where(path == 1, 4 * dep, 4 * dep))
         if args.workload == "trace":  # + the 135 float64 SE values of every associated UE's row
             row_b = row_b + 1080 * assoc_tab_t[eng.v["scen"].long()]
         ue_bytes += float((row_b + FIXED_ROW_BYTES).sum().item())
@@ -305,6 +355,7 @@ def run_b200(args):
     kms /= P
     ue_bytes /= P
     path_frac /= P
+    live_frac /= P
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -324,9 +375,10 @@ def run_b200(args):
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650 GB/s",
                 "algorithmic_bytes_per_launch": ue_bytes, "kernel_ms": kms[1],
                 "kernel_ms_all": {"k_action": kms[0], "k_ue_env": kms[1], "k_env_tail": kms[2]},
-                "bytes_per_ue_row": ("%d (per-UE records) + buffer row: 8*D_u streamed, 4*D_u zero-filled, 4 empty" % FIXED_ROW_BYTES)
+                "bytes_per_ue_row": ("%d (per-UE records) + buffer row: 8*L streamed, 4*L zero-filled (L = the row's live extent), 4 when an empty row receives packets" % FIXED_ROW_BYTES)
                 + (" + 1080 (SE row) per associated UE" if args.workload == "trace" else ""),
-                "row_paths": {"empty": path_frac[0], "zero_fill": path_frac[1], "stream": path_frac[2]}}
+                "row_paths": {"empty": path_frac[0], "zero_fill": path_frac[1], "stream": path_frac[2]},
+                "live_slot_fraction": live_frac}
 
     # ---- e2e: host actions in, host surface out, through irs_step_host ------------------------
     e2e = e2e_f32 = None
@@ -381,7 +433,7 @@ def run_b200(args):
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu = cpu_oracle_run(args, bank, args.cpu_envs, warmup=5)
+        cpu = cpu_oracle_run(args, bank, args.cpu_envs, warmup=5, fill=n_fill)
         cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
     if rank == 0:
         value = world * E * U * K / (ms_total * 1e-3)
@@ -393,7 +445,7 @@ def run_b200(args):
                        "surface": "IBSched dict obs + action masks + 6 rewards, random actions supplied on device",
                        "channel": "SE trace bank in HBM (channel_mode 3)" if args.workload == "trace" else "native mimic_quadriga",
                        "trace_bank_bytes": trace_bytes, "traffic": "native Poisson",
-                       "state_bytes_per_gpu": state_bytes,
+                       "state_bytes_per_gpu": state_bytes, "fill_steps": n_fill, "episode_steps": episode_steps(args),
                        "l2": "state larger than L2" if flush is None else "L2 flushed (256 MB fill) between timed steps"},
             "e2e": e2e, "e2e_f32_surface": e2e_f32, "roofline": roofline, "cpu_baseline": cpu, "gpu_launches": 3 * K, "clocks": clocks,
             "env_errors": err, "episode_metrics": metrics_named,

@@ -110,7 +110,9 @@ typedef struct {
     size_t buf;              /* i32 [E][25][row_stride]  age histograms (buffer.py:47) */
     size_t ue_i;             /* i32 [E][25][8]  per-UE record: packets in buffer, window sums of
                                 sent / dropped, newest frame's sent / dropped / incoming,
-                                isclose(win[1].occ, 0), row path taken (0 empty, 1 zero-fill, 2 stream) */
+                                isclose(win[1].occ, 0), row word = path taken (0 empty, 1 zero-fill,
+                                2 stream) | live extent << 2 (14 bits: oldest non-empty slot + 1; every
+                                slot of the row at or beyond it is zero) | slots touched << 16 */
     size_t ue_d;             /* f64 [E][25][4]  newest window frame: occupancy, mean delay, mean SE,
                                 pkt_throughputs */
     size_t ring;             /* i32 [E][25][10][2] (sent, dropped) of the last 10 frames */

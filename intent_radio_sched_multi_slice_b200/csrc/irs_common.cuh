@@ -25,6 +25,11 @@ enum { ERR_INTRA_ACTION = 1, ERR_EPISODE_RANGE = 2, ERR_RB_SUM = 4 };
 //   ring[E][25][10] int2 : (sent, dropped) of the last 10 frames (agents/ib_sched.py:49-51)
 //   rb[E][25]       short2: (rb_start, rb_count) contiguous RB run of the UE
 enum { UI_TOT = 0, UI_SUM_SENT, UI_SUM_DROP, UI_SENT, UI_DROP, UI_INC, UI_OCC1Z, UI_PATH, UI_N };
+// UI_PATH word: row path of the step (2 bits) | live extent << 2 (14 bits) | slots the step touched
+// << 16 (bench.py's byte accounting reads the last).  Invariant: every slot of a buffer row at or
+// beyond its live extent is zero, so the row kernels never read or write past it.
+#define ROW_LIVE(word) (((word) >> 2) & 0x3fff)
+#define ROW_WORD(path, live, slots) ((path) | ((live) << 2) | ((slots) << 16))
 enum { UD_OCC = 0, UD_LAT, UD_SEBAR, UD_THR, UD_N };
 
 // Pointers into the caller-owned state blob (see irs_layout).

@@ -91,11 +91,13 @@ __device__ __noinline__ void reset_env_warp(const StepArgs& A, int e, int initia
     __syncwarp();
     if (lane == 0) { st.step[e] = 0; st.episode[e] = ep; st.scen[e] = scen; }
     // fresh UEs: empty buffers (comm_env.py:620-625, associations/mult_slice.py:468-488)
-    {
-        int4* rows = reinterpret_cast<int4*>(st.buf + (size_t)e * U * st.row_stride);
-        const int n4 = U * st.row_stride / 4;
-        for (int i = lane; i < n4; i += 32) rows[i] = make_int4(0, 0, 0, 0);
+    for (int u = 0; u < U; ++u) { // only a row's live extent can hold packets
+        const size_t eu = (size_t)e * U + u;
+        const int live = ROW_LIVE(st.ue_i[eu * UI_N + UI_PATH]);
+        int4* row4 = reinterpret_cast<int4*>(st.buf + eu * st.row_stride);
+        for (int i = lane; 4 * i < live; i += 32) row4[i] = make_int4(0, 0, 0, 0);
     }
+    __syncwarp();
     // channel frame 0 of the new episode -> mean SE per UE (comm_env.py:449-451)
     double sebar = 0;
     for (int u = 0; u < U; ++u) {

@@ -70,7 +70,8 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
     if (ue_lane && win_len == A.win_cap) evict = st.ring[eu * W + p];
     const int tot_prev = ue_lane ? rec_a.x : 0;
     int* row = st.buf + eu * (size_t)st.row_stride;
-    const int expired = (ue_lane && tot_prev != 0) ? row[up.depth - 1] : 0; // buffer.py:60, in flight early
+    const int live_prev = ue_lane ? ROW_LIVE(st.ue_i[eu * UI_N + UI_PATH]) : 0; // slots [0, live_prev) may hold packets
+    const int expired = (ue_lane && live_prev == up.depth) ? row[up.depth - 1] : 0; // buffer.py:60, in flight early
     const int frame = step + 1, gid = cfg.env_id_base + e;
 
     // ---- phase 1: action -> RB runs (ib_sched.py:223-349) ---------------------------------
@@ -343,8 +344,11 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
     const int a_left = kept - min(kept, thr_i - sent_old);
     const int sent = sent_old + (kept - a_left);
     const int rem = total + kept - sent;
-    int path = ROW_EMPTY;
-    if (ue_lane && tot_prev != 0) path = (sent_old == total) ? ROW_ZERO_FILL : ROW_STREAM;
+    int path = ROW_EMPTY, live = a_left != 0, slots = live; // live extent after / slots touched by the step
+    if (ue_lane && tot_prev != 0) {
+        path = (sent_old == total) ? ROW_ZERO_FILL : ROW_STREAM;
+        slots = (sent_old == total) ? live_prev : min(live_prev + 1, up.depth);
+    }
 
     // ---- phase 4: the rows -------------------------------------------------------------------
     if (ue_lane && tot_prev == 0 && a_left != 0) row[0] = a_left; // empty row: only slot 0 changes
@@ -354,16 +358,16 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
     while (zf) {
         const int u = __ffs(zf) - 1;
         zf &= zf - 1;
-        buffer_row_zero_fill(st.buf + ((size_t)e * U + u) * st.row_stride, __shfl_sync(FULL, up.depth, u),
+        buffer_row_zero_fill(st.buf + ((size_t)e * U + u) * st.row_stride, __shfl_sync(FULL, slots, u),
                              __shfl_sync(FULL, a_left, u));
     }
     while (stm) {
         const int u = __ffs(stm) - 1;
         stm &= stm - 1;
         const long long w = buffer_row_stream(st.buf + ((size_t)e * U + u) * st.row_stride,
-                                              __shfl_sync(FULL, up.depth, u), __shfl_sync(FULL, thr_i, u),
+                                              __shfl_sync(FULL, slots, u), __shfl_sync(FULL, thr_i, u),
                                               __shfl_sync(FULL, a_left, u));
-        if (lane == u) wsum = w;
+        if (lane == u) { wsum = w & ((1LL << ROW_WSUM_BITS) - 1); live = (int)(w >> ROW_WSUM_BITS); }
     }
 
     // ---- phase 5: occupancy, mean delay, window push, record stores ---------------------------
@@ -374,7 +378,7 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
     const bool occ1z = isclose0(rec_d0.x); // win[1].occ of the new window
     if (ue_lane) {
         *reinterpret_cast<int4*>(st.ue_i + eu * UI_N) = make_int4(rem, sum_sent, sum_drop, sent);
-        *reinterpret_cast<int4*>(st.ue_i + eu * UI_N + 4) = make_int4(dropped, (int)inc, occ1z ? 1 : 0, path);
+        *reinterpret_cast<int4*>(st.ue_i + eu * UI_N + 4) = make_int4(dropped, (int)inc, occ1z ? 1 : 0, ROW_WORD(path, live, slots));
         *reinterpret_cast<double2*>(st.ue_d + eu * UD_N) = make_double2(occ, lat);
         *reinterpret_cast<double2*>(st.ue_d + eu * UD_N + 2) = make_double2(sebar, thr);
         st.ring[eu * W + p] = make_int2(sent, dropped);

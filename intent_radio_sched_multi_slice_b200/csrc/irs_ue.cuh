@@ -31,12 +31,17 @@ enum { ROW_EMPTY = 0, ROW_ZERO_FILL = 1, ROW_STREAM = 2 };
 
 // General case: stream the row once.  `total` = packets in slots >= 1 after the shift,
 // `thr_i` = packets that may leave (thr_i < total here), `a_left` = what stays in slot 0.
-// Returns sum(age * packets left), reduced over the warp.
+// `depth` is the row's live extent after the shift (min(live + 1, configured depth)): slots at
+// and beyond it are zero and are neither read nor written.
+// Returns sum(age * packets left) in the low 48 bits (age < 2^12, packets < 2^31) and the new
+// live extent (index of the oldest non-empty slot + 1) above them, both reduced over the warp.
+#define ROW_WSUM_BITS 48
 __device__ __noinline__ long long buffer_row_stream(int* __restrict__ row, int depth, int thr_i, int a_left)
 {
     const int lane = lane_id();
     const int nch = (depth + 127) >> 7;
     int sfx = 0;        // packets in slots older than the chunk being processed (warp-uniform)
+    int hi = 0;         // this lane's oldest non-empty slot + 1 (the walk starts at the old end)
     long long wsum = 0; // sum age * packets left (this lane's slots)
     for (int g = (nch + GC - 1) / GC - 1; g >= 0; --g) {
         const int cb = g * GC;
@@ -80,15 +85,18 @@ __device__ __noinline__ long long buffer_row_stream(int* __restrict__ row, int d
             }
             if (i0 == 0) n0 = a_left; // slot 0: the new arrivals (already net of what was sent)
             wsum += (long long)i0 * (n0 + n1 + n2 + n3) + (n1 + 2 * n2 + 3 * n3);
+            if (hi == 0 && (n0 | n1 | n2 | n3) != 0) hi = i0 + (n3 ? 4 : (n2 ? 3 : (n1 ? 2 : 1)));
             if (i0 < depth) *reinterpret_cast<int4*>(row + i0) = make_int4(n0, n1, n2, n3);
         }
     }
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) wsum += __shfl_xor_sync(FULL, wsum, d);
-    return wsum;
+    return wsum | ((long long)__reduce_max_sync(FULL, hi) << ROW_WSUM_BITS);
 }
 
-// Everything older than the new arrivals was sent: the row becomes [a_left, 0, 0, ...].
+
+// Everything older than the new arrivals was sent: the row becomes [a_left, 0, 0, ...]
+// (`depth` = the live extent before the shift; nothing beyond it needs clearing).
 __device__ __noinline__ void buffer_row_zero_fill(int* __restrict__ row, int depth, int a_left)
 {
     const int lane = lane_id();
@@ -180,7 +188,8 @@ __global__ void __launch_bounds__(UE_WARPS * 32, 4) k_ue_step(const __grid_const
     // ---- Buffer.receive_packets + send_packets (buffer.py:53-104) ---------------------------
     int* row = st.buf + eu * (size_t)st.row_stride;
     int expired = 0, path = ROW_EMPTY;
-    if (tot_prev != 0) expired = row[up.depth - 1];   // buffer.py:60 dropped = buffer[-1]
+    const int live_prev = ROW_LIVE(__shfl_sync(FULL, pre_i, UI_PATH)); // slots [0, live_prev) may hold packets
+    if (live_prev == up.depth) expired = row[up.depth - 1]; // buffer.py:60 dropped = buffer[-1]
     const int total = tot_prev - expired;             // occupancy after the age shift
     int dropped = expired, kept;
     if ((double)total + inc <= (double)up.max_pkts) { // buffer.py:62-80
@@ -194,13 +203,18 @@ __global__ void __launch_bounds__(UE_WARPS * 32, 4) k_ue_step(const __grid_const
     const int sent = sent_old + (kept - a_left);
     const int rem = total + kept - sent;
     long long wsum = 0;
+    int live = a_left != 0, slots = live;
     if (tot_prev == 0) {                              // row is all zero: only slot 0 changes
         if (lane == 0 && a_left != 0) row[0] = a_left;
     } else if (sent_old == total) {                   // all older packets left: zero-fill
-        buffer_row_zero_fill(row, up.depth, a_left);
+        slots = live_prev;
+        buffer_row_zero_fill(row, slots, a_left);
         path = ROW_ZERO_FILL;
     } else {
-        wsum = buffer_row_stream(row, up.depth, thr_i, a_left);
+        slots = min(live_prev + 1, up.depth);
+        wsum = buffer_row_stream(row, slots, thr_i, a_left);
+        live = (int)(wsum >> ROW_WSUM_BITS);
+        wsum &= (1LL << ROW_WSUM_BITS) - 1;
         path = ROW_STREAM;
     }
     // occupancy and mean delay: two divisions in one stream (buffer.py:106-130)
@@ -222,7 +236,7 @@ __global__ void __launch_bounds__(UE_WARPS * 32, 4) k_ue_step(const __grid_const
     out_i = lane == UI_DROP ? dropped : out_i;
     out_i = lane == UI_INC ? (int)inc : out_i;
     out_i = lane == UI_OCC1Z ? (isclose0(occ_old) ? 1 : 0) : out_i; // win[1].occ of the new window
-    out_i = lane == UI_PATH ? path : out_i;
+    out_i = lane == UI_PATH ? ROW_WORD(path, live, slots) : out_i;
     if (lane < UI_N) st.ue_i[eu * UI_N + lane] = out_i;
     double out_d = occ;                               // UD_OCC
     out_d = lane == UD_LAT ? lat : out_d;

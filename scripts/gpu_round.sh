@@ -11,14 +11,16 @@ python bench.py --workload trace > gpurun_out/bench_trace.json 2> gpurun_out/ben
 python bench.py --workload cfg2 --no-cpu-baseline > gpurun_out/bench_cfg2.json 2> gpurun_out/bench_cfg2.err
 python bench.py --depth 401 --steps 100 --no-cpu-baseline > gpurun_out/bench_d401.json 2> gpurun_out/bench_d401.err
 python bench.py --depth 4096 --envs 16384 --steps 50 --no-cpu-baseline > gpurun_out/bench_d4096.json 2> gpurun_out/bench_d4096.err
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv \
-    python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu_launches.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:k_ue_env -s 10 -c 1 -f -o gpurun_out/k_ue_env_sweep \
-    python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu_full_sweep.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:k_ue_env -s 10 -c 1 -f -o gpurun_out/k_ue_env_mix \
-    python bench.py --workload mix --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu_full_mix.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:k_ue_env -s 10 -c 1 -f -o gpurun_out/k_ue_env_trace \
-    python bench.py --workload trace --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu_full_trace.log 2>&1
+# ncu passes: the buffers are first filled to their steady state (the fill lengths are what bench.py's plateau detection
+# settles on, see config.fill_steps of the bench lines); unprofiled launches are skipped with -s (counts matching kernels)
+ncu --metrics gpu__time_duration.sum --clock-control none -k regex:^k_ -s 8843 -c 15 --csv --log-file gpurun_out/launches.csv \
+    python bench.py --fill 2944 --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu_launches.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:k_ue_env -s 2950 -c 1 -f -o gpurun_out/k_ue_env_sweep \
+    python bench.py --fill 2944 --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu_full_sweep.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:k_ue_env -s 518 -c 1 -f -o gpurun_out/k_ue_env_mix \
+    python bench.py --workload mix --fill 512 --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu_full_mix.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:k_ue_env -s 518 -c 1 -f -o gpurun_out/k_ue_env_trace \
+    python bench.py --workload trace --fill 512 --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu_full_trace.log 2>&1
 # a history file written by the recorder, for a read-back with the reference's own Metrics.read in the build container
 python - > gpurun_out/hist.log 2>&1 <<'PY'
 import sys, numpy as np
