@@ -361,9 +361,17 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
         buffer_row_zero_fill(st.buf + ((size_t)e * U + u) * st.row_stride, __shfl_sync(FULL, slots, u),
                              __shfl_sync(FULL, a_left, u));
     }
+    if (stm) { // the first group of the first streamed row; each row then prefetches its successor's
+        const int u = __ffs(stm) - 1, ext = __shfl_sync(FULL, slots, u);
+        prefetch_row_group(st.buf + ((size_t)e * U + u) * st.row_stride, ext, row_oldest_group(ext));
+    }
     while (stm) {
         const int u = __ffs(stm) - 1;
         stm &= stm - 1;
+        if (stm) {
+            const int un = __ffs(stm) - 1, ext = __shfl_sync(FULL, slots, un);
+            prefetch_row_group(st.buf + ((size_t)e * U + un) * st.row_stride, ext, row_oldest_group(ext));
+        }
         const long long w = buffer_row_stream(st.buf + ((size_t)e * U + u) * st.row_stride,
                                               __shfl_sync(FULL, slots, u), __shfl_sync(FULL, thr_i, u),
                                               __shfl_sync(FULL, a_left, u));

@@ -25,7 +25,9 @@
 
 
 #define UE_WARPS 8 /* warps (rows) per block */
+#ifndef GC
 #define GC 4       /* 128-slot chunks per group */
+#endif
 
 enum { ROW_EMPTY = 0, ROW_ZERO_FILL = 1, ROW_STREAM = 2 };
 
@@ -36,6 +38,17 @@ enum { ROW_EMPTY = 0, ROW_ZERO_FILL = 1, ROW_STREAM = 2 };
 // Returns sum(age * packets left) in the low 48 bits (age < 2^12, packets < 2^31) and the new
 // live extent (index of the oldest non-empty slot + 1) above them, both reduced over the warp.
 #define ROW_WSUM_BITS 48
+#ifndef ROW_PREFETCH
+#define ROW_PREFETCH 1 /* L2 prefetch distance in groups within a row (0 = off); the next row's first group too */
+#endif
+// The 16 128-byte lines of group `g` (GC x 128 slots) of a row, one per lane 0..15, into L2.
+__device__ __forceinline__ void prefetch_row_group(const int* row, int depth, int g)
+{
+    const int i0 = g * (GC << 7) + 32 * lane_id();
+    if (ROW_PREFETCH && lane_id() < 4 * GC && i0 < depth) asm volatile("prefetch.global.L2 [%0];" ::"l"(row + i0));
+}
+__device__ __forceinline__ int row_oldest_group(int depth) { return (((depth + 127) >> 7) + GC - 1) / GC - 1; }
+
 __device__ __noinline__ long long buffer_row_stream(int* __restrict__ row, int depth, int thr_i, int a_left)
 {
     const int lane = lane_id();
@@ -43,8 +56,15 @@ __device__ __noinline__ long long buffer_row_stream(int* __restrict__ row, int d
     int sfx = 0;        // packets in slots older than the chunk being processed (warp-uniform)
     int hi = 0;         // this lane's oldest non-empty slot + 1 (the walk starts at the old end)
     long long wsum = 0; // sum age * packets left (this lane's slots)
-    for (int g = (nch + GC - 1) / GC - 1; g >= 0; --g) {
+    const int top = (nch + GC - 1) / GC - 1;
+    for (int g = top; g >= 0; --g) {
         const int cb = g * GC;
+        if (g == top) {
+#pragma unroll
+            for (int d = 1; d < ROW_PREFETCH; ++d)
+                if (g >= d) prefetch_row_group(row, depth, g - d);
+        }
+        if (g >= ROW_PREFETCH) prefetch_row_group(row, depth, g - ROW_PREFETCH);
         int4 v[GC];
 #pragma unroll
         for (int k = 0; k < GC; ++k) {
