@@ -431,6 +431,9 @@ def run_b200(args):
     from intent_radio_sched_multi_slice_b200 import distributed as D
     metrics_named = D.all_reduce_metrics(eng.episode_metrics(), dev)  # the path's one collective (NCCL when N > 1)
 
+    # kernels per irs_step (irs_capi.cu launch_step): k_action[_t], k_ue_env, k_env_tail[_t], and k_rollover after the
+    # thread-per-env tail (launches of >= IRS_SERIAL_MIN_ENVS envs, default 49,152)
+    launches_per_step = 4 if E >= int(os.environ.get("IRS_SERIAL_MIN_ENVS", "49152")) else 3
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_oracle_run(args, bank, args.cpu_envs, warmup=5, fill=n_fill)
@@ -447,7 +450,7 @@ def run_b200(args):
                        "trace_bank_bytes": trace_bytes, "traffic": "native Poisson",
                        "state_bytes_per_gpu": state_bytes, "fill_steps": n_fill, "episode_steps": episode_steps(args),
                        "l2": "state larger than L2" if flush is None else "L2 flushed (256 MB fill) between timed steps"},
-            "e2e": e2e, "e2e_f32_surface": e2e_f32, "roofline": roofline, "cpu_baseline": cpu, "gpu_launches": 3 * K, "clocks": clocks,
+            "e2e": e2e, "e2e_f32_surface": e2e_f32, "roofline": roofline, "cpu_baseline": cpu, "gpu_launches": launches_per_step * K, "clocks": clocks,
             "env_errors": err, "episode_metrics": metrics_named,
         }
         print(json.dumps(line))
