@@ -82,3 +82,50 @@ def test_fuzzed_scenarios_match_oracle(seed, family, monkeypatch):
     per_g, tot_g = gpu.episode_metrics()
     per_o, tot_o = orc.episode_metrics()
     np.testing.assert_allclose(per_g, per_o, rtol=1e-12, atol=1e-300)
+
+
+@pytest.mark.parametrize("depth,size", [(140, 90_000), (530, 1_024_000), (530, 250_000)])
+def test_rows_age_to_the_expiry_slot_like_oracle(depth, size):
+    """Rows that grow slot by slot to their full depth (across the 128-slot chunk and the 512-slot group boundaries of the
+    row walk), hit the capacity clip on the way and then expire at the old end every step: the live-extent bookkeeping of
+    the row kernel (irs_common.cuh ROW_LIVE) against the dense oracle - every output of every step, buffers at checkpoints."""
+    from intent_radio_sched_multi_slice_b200 import scenario as scn
+    from oracle import oracle
+
+    rng = np.random.default_rng(depth + size)
+    bank = scn.ScenarioBank()
+    for i in range(4):
+        req, sua = {}, np.zeros((5, 25))
+        for s in range(5):
+            r = scn.slice_req_from_type(5)  # 100 Mbit/s of 65,536-bit packets per UE against ~40 Mbit/s of service
+            r["ues"]["buffer_latency"] = depth - 1 - (s if i else 0)
+            r["ues"]["buffer_size"] = size
+            req[f"slice_{s}"] = r
+            sua[s, 5 * s:5 * s + (5 if i != 3 else 3)] = 1
+        bank.add(req, sua)
+    E, steps = 12, int(2.2 * depth)
+    kw = dict(channel_mode=2, traffic_mode=1, policy=0, fixed_intra=-1, sort_slices=1, assoc_mode=0, scen_mod=4,
+              max_steps=1_000_000, auto_reset=1, env_id_base=3, seed=77, initial_episode=0)
+    stride = (depth + 3) // 4 * 4
+    orc = oracle.OracleEnv(bank.array(), bank.poisson_cdf(), E, depth_cap=stride, **kw)
+    gpu = CudaEnv(bank, E, depth_cap=depth, **kw)
+    ie = (np.arange(E) % 4).astype(np.int32)
+    for e in range(E):
+        m = np.zeros(E, np.uint8)
+        m[e] = 1
+        orc.reset(mask=m, initial_episode=int(ie[e]))
+    gpu.reset(initial_episodes=ie, initial_episode=0)
+    expired = 0
+    for k in range(steps):
+        a0 = rng.uniform(-1, 1, (E, 5))
+        intra = rng.integers(0, 3, (E, 5)).astype(np.int32)
+        want, got = orc.step(a0, intra), gpu.step(a0, intra)
+        compare_outputs(got, want, f"depth {depth} step {k}")
+        expired += int(np.asarray(want["dropped"]).sum() > 0)
+        if k % 97 == 0 or k == steps - 1:
+            assert np.array_equal(gpu.buffers()[:, :, :depth], orc.buffers()[:, :, :depth]), k
+    word = gpu.eng.v["path"].cpu().numpy()
+    live = (word >> 2) & 0x3FFF
+    buf = gpu.buffers()
+    oldest = ((buf != 0) * (np.arange(buf.shape[2]) + 1)).max(2)
+    assert (oldest <= live).all() and (live.max() >= depth - 5) and expired > depth // 2
