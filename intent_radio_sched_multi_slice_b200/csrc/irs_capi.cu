@@ -445,8 +445,8 @@ static int copy_surface(irs_env* env, const irs_host_surface* o, bool with_rewar
 
 // How irs_step_host splits the batch: the surface of a finished chunk crosses PCIe while the next chunk computes.
 // Chunks are whole WAVES of the row kernel (resident blocks per SM x SMs x envs per block), so that chunking does not
-// add a partly filled last wave to every chunk; about five chunks per step.  Small batches stay whole (launch latency
-// dominates).  IRS_HOST_CHUNKS=n forces n equal chunks.
+// add a partly filled last wave to every chunk; about five chunks per step.
+// Small batches stay whole (launch latency dominates).  IRS_HOST_CHUNKS=n forces n equal chunks.
 static int host_chunk_plan(irs_env* env, size_t* bounds /* [IRS_MAX_HOST_CHUNKS + 1] */)
 {
     const size_t E = (size_t)env->cfg.num_envs;
@@ -467,6 +467,9 @@ static int host_chunk_plan(irs_env* env, size_t* bounds /* [IRS_MAX_HOST_CHUNKS 
             }
             env->wave_envs = (size_t)sms * nb * FUSED_WARPS;
         }
+        // Equal chunks: measured timelines (IRS_HOST_TRACE=1, profiles/r1_notes.md) show the sweep compute-bound with only the
+        // last chunk's copy exposed, the mix balanced between chunked kernels and PCIe; a one-wave first chunk and a
+        // partial-wave last chunk (1 + 4 + 4 + 4 + rest) measured 4-10 % slower on both.
         const size_t waves = (E + env->wave_envs - 1) / env->wave_envs;
         const size_t wpc = (waves + 4) / 5; // waves per chunk: about five chunks
         per = wpc * env->wave_envs;
@@ -511,6 +514,14 @@ int irs_step_host(irs_env* env, const irs_actions* actions_host, const irs_host_
     }
     // One compute stream: a chunk must FINISH early for its copy to start early (two alternating compute
     // streams were measured slower - both chunks then finish late, profiles/r1_notes.md).
+    // IRS_HOST_TRACE=1: timeline of one call on stderr (ms since the call's first enqueue) - a debugging aid
+    static const bool trace = getenv("IRS_HOST_TRACE") != nullptr;
+    cudaEvent_t t0 = nullptr, tk[IRS_MAX_HOST_CHUNKS] = {}, tc[IRS_MAX_HOST_CHUNKS] = {};
+    if (trace) {
+        CK(cudaEventCreate(&t0));
+        for (int c = 0; c < chunks; ++c) { CK(cudaEventCreate(&tk[c])); CK(cudaEventCreate(&tc[c])); }
+        CK(cudaEventRecord(t0, st));
+    }
     for (int c = 0; c < chunks; ++c) {
         const size_t e0 = bounds[c], e1 = bounds[c + 1];
         if (e0 >= e1) break;
@@ -519,11 +530,25 @@ int irs_step_host(irs_env* env, const irs_actions* actions_host, const irs_host_
         rc = launch_step(env, A, st);
         if (rc) return rc;
         CK(cudaEventRecord(env->chunk_ev[c], st));
+        if (trace) CK(cudaEventRecord(tk[c], st));
         CK(cudaStreamWaitEvent(env->copy_stream, env->chunk_ev[c], 0));
         rc = copy_surface_range(env, out_host, true, e0, e1, env->copy_stream);
         if (rc) return rc;
+        if (trace) CK(cudaEventRecord(tc[c], env->copy_stream));
     }
     CK(cudaStreamSynchronize(env->copy_stream));
+    if (trace) {
+        fprintf(stderr, "irs_step_host trace:");
+        for (int c = 0; c < chunks; ++c) {
+            float a = 0, b = 0;
+            cudaEventElapsedTime(&a, t0, tk[c]);
+            cudaEventElapsedTime(&b, t0, tc[c]);
+            fprintf(stderr, " [%zu envs: kernels done %.3f, copied %.3f]", bounds[c + 1] - bounds[c], a, b);
+            cudaEventDestroy(tk[c]); cudaEventDestroy(tc[c]);
+        }
+        fprintf(stderr, "\n");
+        cudaEventDestroy(t0);
+    }
     return IRS_OK;
 }
 
