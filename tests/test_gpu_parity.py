@@ -11,7 +11,7 @@ import pytest
 
 import golden_inputs
 import trace_replay
-from gpu_adapter import CudaEnv, compare_outputs
+from gpu_adapter import OUT_KEYS, CudaEnv, compare_outputs
 
 pytestmark = pytest.mark.gpu
 
@@ -122,6 +122,178 @@ def test_batch_native_matches_oracle(bank, cfg):
     np.testing.assert_allclose(per_g, per_o, rtol=1e-12, atol=1e-300)
     np.testing.assert_allclose(tot_g, tot_o, rtol=1e-12, atol=1e-300)
     assert per_g[:, 15].min() >= 3  # every env went through >= 3 resets
+
+
+def test_config2_1024_envs_full_episode(bank):
+    """BASELINE config 2: 1,024 batched mult_slice envs, env e on association episode e mod 200, actions pre-drawn per env
+    with default_rng(1234 + e) (player_0 ~ U(-1,1)^5, player_1..5 ~ integers{0,1,2}), one whole 1000-step episode plus the
+    rollover into the next: bit-exact buffers / RB runs / packet counts / masks and <= 1e-12 observations and rewards
+    against the oracle at every step (native generators: the reference's own RNG stream cannot be batched)."""
+    from oracle import oracle
+
+    E, steps = 1024, 1012
+    kw = dict(channel_mode=2, traffic_mode=1, policy=0, fixed_intra=-1, sort_slices=1, assoc_mode=0, scen_mod=200,
+              max_steps=1000, max_episodes=10000, initial_episode=0, auto_reset=1, env_id_base=0, seed=10)
+    orc = oracle.OracleEnv(bank.array(), bank.poisson_cdf(), E, depth_cap=404, **kw)
+    gpu = CudaEnv(bank, E, depth_cap=401, **kw)
+    ie = (np.arange(E) % 200).astype(np.int32)
+    for e0 in range(200):
+        m = ((np.arange(E) % 200) == e0).astype(np.uint8)
+        want = orc.reset(mask=m, initial_episode=e0)
+    got = gpu.reset(initial_episodes=ie, initial_episode=0)
+    compare_outputs(got, want, "reset", keys=["obs0", "obs_i", "mask0", "mask_i", "sorted_slices"])
+    gens = [np.random.default_rng(1234 + e) for e in range(E)]
+    a0_all = np.stack([g.uniform(-1, 1, (steps, 5)) for g in gens], 1)                       # [steps, E, 5]
+    intra_all = np.stack([g.integers(0, 3, (steps, 5)) for g in gens], 1).astype(np.int32)
+    dones = 0
+    for k in range(steps):
+        want, got = orc.step(a0_all[k], intra_all[k]), gpu.step(a0_all[k], intra_all[k])
+        compare_outputs(got, want, f"config 2 step {k}")
+        dones += int(np.asarray(want["done"]).sum())
+        if k % 250 == 249 or k == steps - 1:
+            assert np.array_equal(gpu.buffers()[:, :, :401], orc.buffers()[:, :, :401]), k
+    assert dones == E
+    st_g, st_o = gpu.state(), orc.state()
+    for key in st_o:
+        assert np.array_equal(st_g[key], st_o[key]), key
+    per_g, tot_g = gpu.episode_metrics()
+    per_o, tot_o = orc.episode_metrics()
+    np.testing.assert_allclose(per_g, per_o, rtol=1e-12, atol=1e-300)
+    np.testing.assert_allclose(tot_g, tot_o, rtol=1e-12, atol=1e-300)
+
+
+@pytest.mark.parametrize("channel_mode", [1, 2])
+def test_config4_seq_scenarios_across_resets(bank, channel_mode):
+    """BASELINE config 4: MultSliceAssociationSeq (scenario = episode // 100) with the fixed_se and mimic_quadriga channels;
+    envs start at episode 98 or 99 and run four episodes, so every env crosses a scenario boundary (new slice set, new
+    per-UE depth / buffer size / packet size) with the observation window carried over the reset (quirk Q1); a third of the
+    envs is reset once more in mid-episode, so resets are out of phase inside the batch."""
+    from oracle import oracle
+
+    E, T, steps = 384, 150, 640
+    kw = dict(channel_mode=channel_mode, traffic_mode=1, policy=3, fixed_intra=-1, sort_slices=1, assoc_mode=1, scen_div=100,
+              max_steps=T, max_episodes=10000, initial_episode=98, auto_reset=1, env_id_base=50, seed=4)
+    orc = oracle.OracleEnv(bank.array(), bank.poisson_cdf(), E, depth_cap=404, **kw)
+    gpu = CudaEnv(bank, E, depth_cap=401, **kw)
+    ie = (98 + np.arange(E) % 2).astype(np.int32)
+    for ep in (98, 99):
+        want = orc.reset(mask=(ie == ep).astype(np.uint8), initial_episode=ep)
+    got = gpu.reset(initial_episodes=ie, initial_episode=0)
+    compare_outputs(got, want, "reset", keys=["obs0", "obs_i", "mask0", "mask_i", "sorted_slices"])
+    third = (np.arange(E) % 3 == 0).astype(np.uint8)
+    for k in range(steps):
+        if k == 61:  # explicit reset of a third of the batch: those envs move on to their next episode now
+            want, got = orc.reset(mask=third), gpu.reset(mask=third)
+            compare_outputs(got, want, "masked reset", keys=["obs0", "obs_i", "mask0", "mask_i", "sorted_slices"])
+        want, got = orc.step(), gpu.step()
+        compare_outputs(got, want, f"config 4 step {k}")
+    st_g, st_o = gpu.state(), orc.state()
+    for key in st_o:
+        assert np.array_equal(st_g[key], st_o[key]), key
+    assert len(np.unique(st_o["step"])) >= 2 and st_o["scen"].min() >= 1  # out of phase; every env left scenario 0
+    assert np.array_equal(gpu.buffers()[:, :, :401], orc.buffers()[:, :, :401])
+    per_g, tot_g = gpu.episode_metrics()
+    per_o, tot_o = orc.episode_metrics()
+    np.testing.assert_allclose(per_g, per_o, rtol=1e-12, atol=1e-300)
+
+
+def test_config3_results_do_not_depend_on_the_sharding(bank):
+    """BASELINE config 3: 16,384 envs with the IBSched dict surface, native generators keyed by the GLOBAL env id.  The batch
+    run whole and run as 8 shards of 2,048 envs (env_id_base = rank * 2048, as distributed.shard hands them out) gives
+    bit-identical per-env results, identical integer episode counters and float sums equal to rounding; a 64-env sample of
+    every shard is checked against the oracle."""
+    from oracle import oracle
+
+    E, G, steps = 16384, 8, 40
+    kw = dict(channel_mode=2, traffic_mode=1, policy=3, fixed_intra=-1, sort_slices=1, assoc_mode=0, scen_mod=200,
+              max_steps=25, max_episodes=10000, initial_episode=0, auto_reset=1, seed=10)
+    whole = CudaEnv(bank, E, depth_cap=401, env_id_base=0, **kw)
+    ie = (np.arange(E) % 200).astype(np.int32)
+    whole.reset(initial_episodes=ie, initial_episode=0)
+    for k in range(steps):
+        out_w = whole.step()
+    per_w, tot_w = whole.episode_metrics()
+    buf_w = whole.buffers()
+    tot_s = np.zeros_like(np.asarray(tot_w))
+    n = E // G
+    for r in range(G):
+        sl = slice(r * n, (r + 1) * n)
+        shard = CudaEnv(bank, n, depth_cap=401, env_id_base=r * n, **kw)
+        shard.reset(initial_episodes=ie[sl], initial_episode=0)
+        sample = np.arange(r * n, r * n + 64)
+        orc = oracle.OracleEnv(bank.array(), bank.poisson_cdf(), 64, depth_cap=404, env_id_base=r * n, **kw)
+        for e in range(64):
+            m = np.zeros(64, np.uint8)
+            m[e] = 1
+            orc.reset(mask=m, initial_episode=int(ie[sample[e]]))
+        for k in range(steps):
+            out_s = shard.step()
+            want = orc.step()
+            compare_outputs({key: np.asarray(v)[:64] for key, v in out_s.items()}, want, f"shard {r} step {k}")
+        for key, v in out_s.items():
+            assert np.array_equal(np.asarray(v), np.asarray(out_w[key])[sl]), (r, key)
+        assert np.array_equal(shard.buffers(), buf_w[sl])
+        per_s, t = shard.episode_metrics()
+        assert np.array_equal(per_s, per_w[sl])
+        tot_s += np.asarray(t)
+        del shard
+    from intent_radio_sched_multi_slice_b200 import capi
+    for i, name in enumerate(capi.METRIC_NAMES):
+        np.testing.assert_allclose(tot_s[i], np.asarray(tot_w)[i], rtol=1e-12, err_msg=name)
+
+
+def test_config5_full_size_properties():
+    """BASELINE config 5 at its full size: 65,536 envs x 25 UEs x depth 1024 (every UE on the deep uav_app_case_1 profile,
+    7 GB of state).  Size-independent properties over the whole batch - packet conservation, the per-UE packet count and
+    the live extent against the rows themselves, sent <= throughput, 135 RBs per env - and the first 48 envs against the
+    oracle at every step."""
+    import torch
+    from intent_radio_sched_multi_slice_b200 import scenario as scn
+    from oracle import oracle
+
+    D = 1024
+    bank = scn.ScenarioBank()
+    for i in range(8):
+        req, sua = {}, np.zeros((5, 25))
+        for s in range(5):
+            r = scn.slice_req_from_type(5)
+            r["ues"]["buffer_latency"] = D - 1
+            r["parameters"]["par1"]["value"] = D // 2
+            req[f"slice_{s}"] = r
+            sua[s, 5 * s:5 * s + 5] = 1
+        bank.add(req, sua)
+    E, steps, n_orc = 65536, 24, 48
+    kw = dict(channel_mode=2, traffic_mode=1, policy=3, fixed_intra=-1, sort_slices=1, assoc_mode=0, scen_mod=8,
+              max_steps=1_000_000, max_episodes=10000, initial_episode=0, auto_reset=1, seed=10, env_id_base=0)
+    gpu = CudaEnv(bank, E, depth_cap=D, **kw)
+    orc = oracle.OracleEnv(bank.array(), bank.poisson_cdf(), n_orc, depth_cap=D, **kw)
+    orc.reset(initial_episode=0)
+    gpu.eng.reset(initial_episode=0)
+    inc = torch.zeros(E, 25, dtype=torch.int64, device="cuda")
+    out = torch.zeros_like(inc)
+    for k in range(steps):
+        gpu.eng.step()
+        raw = gpu.raw
+        want = orc.step()
+        surf = gpu.eng.surface()
+        got = {key: (surf[key] if key in surf else raw[key])[:n_orc].cpu().numpy() for key in OUT_KEYS}
+        compare_outputs(got, want, f"config 5 step {k}")
+        inc += raw["pkt_incoming"].long()
+        out += raw["sent"].long() + raw["dropped"].long()
+        assert bool((raw["sent"].double() <= raw["pkt_throughputs"]).all())
+        assert bool((raw["rb_count"].long().sum(1) == 135).all())
+    assert gpu.eng.check_errors() is None
+    buf = gpu.eng.buf
+    in_buf = buf.sum(2, dtype=torch.int64)
+    assert bool((inc == out + in_buf).all()) and bool((in_buf == gpu.eng.v["tot"].long()).all())
+    word = gpu.eng.v["path"].long()
+    live = (word >> 2) & 0x3FFF
+    idx = torch.arange(buf.shape[2], device="cuda", dtype=torch.int32) + 1
+    oldest = torch.zeros(E, 25, dtype=torch.int32, device="cuda")
+    for c0 in range(0, E, 8192):  # chunked: the mask of the whole state would be another 7 GB
+        oldest[c0:c0 + 8192] = ((buf[c0:c0 + 8192] != 0).int() * idx).amax(2)
+    assert bool((oldest.long() <= live).all()) and bool((oldest.long() == live)[(word & 3) == 2].all())
+    assert np.array_equal(buf[:n_orc].cpu().numpy()[:, :, :D], orc.buffers()[:, :, :D])
 
 
 def test_generated_scenarios_match_oracle():
