@@ -248,8 +248,12 @@ def run_b200(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa_pinned = False
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+        if os.environ.get("IRS_BENCH_NUMA", "1") != "0":  # host buffers next to the GPU (see distributed.pin_to_device_numa)
+            from intent_radio_sched_multi_slice_b200 import distributed as D0
+            numa_pinned = D0.pin_to_device_numa(local)
     if args.workload == "cfg2":
         args.envs = 1024
     E, K, Wm = args.envs, args.steps, max(args.warmup, 3)
@@ -449,6 +453,7 @@ def run_b200(args):
                        "channel": "SE trace bank in HBM (channel_mode 3)" if args.workload == "trace" else "native mimic_quadriga",
                        "trace_bank_bytes": trace_bytes, "traffic": "native Poisson",
                        "state_bytes_per_gpu": state_bytes, "fill_steps": n_fill, "episode_steps": episode_steps(args),
+                       "host_numa_pinned": numa_pinned,
                        "l2": "state larger than L2" if flush is None else "L2 flushed (256 MB fill) between timed steps"},
             "e2e": e2e, "e2e_f32_surface": e2e_f32, "roofline": roofline, "cpu_baseline": cpu, "gpu_launches": launches_per_step * K, "clocks": clocks,
             "env_errors": err, "episode_metrics": metrics_named,
