@@ -1,8 +1,7 @@
 #!/bin/bash
-# the bench workloads at their steady state (live-extent rows)
+# GPU suite + the main bench workloads (no CPU arm)
 mkdir -p gpurun_out
+python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
 for w in sweep mix trace cfg2; do
-  python bench.py --workload $w > gpurun_out/live_$w.json 2> gpurun_out/live_$w.err
+  python bench.py --workload $w --no-cpu-baseline > gpurun_out/live_$w.json 2> gpurun_out/live_$w.err
 done
-python bench.py --workload sweep --depth 401 --no-cpu-baseline > gpurun_out/live_sweep401.json 2> gpurun_out/live_sweep401.err
-python bench.py --workload sweep --depth 4096 --envs 16384 --no-cpu-baseline > gpurun_out/live_sweep4096.json 2> gpurun_out/live_sweep4096.err
