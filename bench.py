@@ -456,6 +456,7 @@ def run_b200(args):
                        "host_numa_pinned": numa_pinned,
                        "l2": "state larger than L2" if flush is None else "L2 flushed (256 MB fill) between timed steps"},
             "e2e": e2e, "e2e_f32_surface": e2e_f32, "roofline": roofline, "cpu_baseline": cpu, "gpu_launches": launches_per_step * K, "clocks": clocks,
+            "active_ue_steps_per_s": value * active / U,  # SURVEY 8(d) secondary figure: only UEs associated to a slice
             "env_errors": err, "episode_metrics": metrics_named,
         }
         print(json.dumps(line))
