@@ -30,6 +30,7 @@ struct irs_env {
 
     cudaEvent_t chunk_ev[IRS_MAX_HOST_CHUNKS];
     bool have_copy;
+    int ue_split;                  // IRS_UE_SPLIT: log2 of the warps per env in k_ue_env (-1 = by batch size)
     int host_chunks;               // IRS_HOST_CHUNKS (0 = whole waves of the row kernel, about five chunks)
     size_t wave_envs;              // envs one full wave of k_ue_env covers on this device (0 = not queried yet)
     int serial_min;                // IRS_SERIAL_MIN_ENVS (default 49,152): launches covering at least this many envs
@@ -101,6 +102,7 @@ static StepArgs make_args(const irs_env* env)
     A.win_cap = env->cfg.surface ? W / 2 : W;
     A.win_mul = env->cfg.surface ? 2 : 1;
     A.defer_rollover = 0;
+    A.ue_split_log2 = 0;
     A.env_begin = 0;
     A.env_end = env->cfg.num_envs;
     return A;
@@ -146,6 +148,9 @@ int irs_create(const irs_config* cfg, int32_t n_lambda, irs_env** out)
     env->n_lambda = n_lambda;
     const char* sp = getenv("IRS_STEP_MODE");
     env->mode = sp ? atoi(sp) : 2;
+    const char* us_ = getenv("IRS_UE_SPLIT");
+    env->ue_split = us_ ? atoi(us_) : -1;
+    if (env->ue_split > 2) env->ue_split = 2;
     const char* hc = getenv("IRS_HOST_CHUNKS");
     env->host_chunks = hc ? atoi(hc) : 0;
     const char* sm_ = getenv("IRS_SERIAL_MIN_ENVS");
@@ -285,9 +290,12 @@ static int launch_step(irs_env* env, const StepArgs& A, cudaStream_t st, bool pr
     else k_action<<<(E + 7) / 8, 256, 0, st>>>(A);
     if (profile) CK(cudaEventRecord(env->ev[1], st));
     const long long rows = (long long)E * U;
+    StepArgs B2 = A; // small batches: 2 or 4 warps per env, so that the launch still puts ~32 warps on every SM
+    B2.ue_split_log2 = env->ue_split >= 0 ? env->ue_split : (E <= 1184 ? 2 : (E <= 2368 ? 1 : 0));
+    const unsigned env_warps = (unsigned)E << B2.ue_split_log2;
     if (env->mode == 1) k_ue_step<<<(unsigned)((rows + UE_WARPS - 1) / UE_WARPS), UE_WARPS * 32, 0, st>>>(A);
-    else if (A.raw.se_used) k_ue_env_raw<<<(E + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(A);
-    else k_ue_env<<<(E + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(A);
+    else if (A.raw.se_used) k_ue_env_raw<<<(env_warps + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(B2);
+    else k_ue_env<<<(env_warps + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(B2);
     if (profile) CK(cudaEventRecord(env->ev[2], st));
     const bool alt = env->cfg.surface != 0; // SchedTWC / SchedColORAN: their surface reads the step's records before
                                             // finished envs roll over, then once more for the reset observation

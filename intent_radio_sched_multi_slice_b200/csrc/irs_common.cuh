@@ -73,6 +73,9 @@ struct StepArgs {
     int32_t defer_rollover; // k_env_tail leaves finished envs to k_rollover (the alternative surfaces read the
                             // last step's records in between)
     int32_t env_begin, env_end; // env range of this launch (irs_step_host pipelines chunks of the batch)
+    int32_t ue_split_log2;      // k_ue_env: 2^this warps share an env (UE u belongs to warp u mod 2^this).  Small batches
+                                // cannot fill the GPU with one warp per env, and a warp's serial walk over its UEs is
+                                // the step's critical path; nothing in the row kernel couples the UEs of an env
 };
 
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }

@@ -50,7 +50,9 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
     const irs_config& cfg = A.cfg;
     const int lane = lane_id();
     const int wib = threadIdx.x >> 5;
-    const int e = A.env_begin + blockIdx.x * FUSED_WARPS + wib;
+    const int split = FULL_STEP ? 0 : A.ue_split_log2, gmask = (1 << split) - 1;
+    const int wglob = blockIdx.x * FUSED_WARPS + wib;
+    const int e = A.env_begin + (wglob >> split), grp = wglob & gmask; // this warp serves the UEs u with (u & gmask) == grp
     if (e >= A.env_end) return;
 
     // ---- phase 0: env scalars and this lane's UE record ------------------------------------
@@ -58,7 +60,7 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
     const int win_len = st.win_len[e], head = st.win_head[e];
     const int p = (head + 1) % A.win_cap; // window slot of this frame (deque.appendleft)
     const irs_scenario* sc = st.bank + st.scen[e];
-    const bool ue_lane = lane < U;
+    const bool ue_lane = lane < U && (lane & gmask) == grp;
     const int s_mine = ue_lane ? (int)sc->ue_slice[lane] : -1;
     UeParams up = ue_params(sc, s_mine);
     if (up.depth > st.row_stride) up.depth = st.row_stride;
@@ -321,7 +323,7 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
     }
     if (RAWSE && native && A.raw.se_used) { // unassociated UEs have SE 0 in native mode
         for (int u = 0; u < U; ++u) {
-            if (__shfl_sync(FULL, s_mine, u) >= 0) continue;
+            if ((u & gmask) != grp || __shfl_sync(FULL, s_mine, u) >= 0) continue;
             for (int r = lane; r < R; r += 32) A.raw.se_used[((size_t)e * U + u) * R + r] = 0.0;
         }
     }
