@@ -9,8 +9,9 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("chunks", [1, 3, 8])
-def test_step_host_equals_device_step(bank, chunks, monkeypatch):
+@pytest.mark.parametrize("chunks,extra", [(1, {}), (3, {}), (8, {}), (3, dict(surface=1, fixed_intra=0, sort_slices=0)),
+                                          (5, dict(surface=2, fixed_intra=0, sort_slices=0, assoc_mode=2))])
+def test_step_host_equals_device_step(bank, chunks, extra, monkeypatch):
     import torch
 
     from intent_radio_sched_multi_slice_b200 import capi
@@ -19,6 +20,11 @@ def test_step_host_equals_device_step(bank, chunks, monkeypatch):
     E = 1000  # not a multiple of 3 or 8
     kw = dict(channel_mode=2, traffic_mode=1, sort_slices=1, fixed_intra=-1, policy=0, scen_mod=200, max_steps=9,
               auto_reset=1, seed=21, env_id_base=3, depth_cap=401)
+    kw.update(extra)  # the SchedTWC / SchedColORAN surfaces (extra kernels around the rollover) and generated scenarios
+    if kw.get("assoc_mode") == 2:  # scenarios drawn on the device from the 10 slice-type templates
+        from intent_radio_sched_multi_slice_b200 import scenario as scn
+        bank = scn.ScenarioBank.templates()
+        kw.pop("scen_mod")
     monkeypatch.setenv("IRS_HOST_CHUNKS", str(chunks))
     host = BatchEngine(bank, E, **kw)
     monkeypatch.delenv("IRS_HOST_CHUNKS")
