@@ -309,7 +309,7 @@ static int launch_step(irs_env* env, const StepArgs& A, cudaStream_t st, bool pr
     }
     if (alt) k_surface_alt<<<env_blocks, ENV_WARPS * 32, 0, st>>>(A, 0);
     if ((serial || alt) && env->cfg.auto_reset) {
-        k_rollover<<<env_blocks, ENV_WARPS * 32, 0, st>>>(A);
+        k_rollover<<<(E + ENV_WARPS * ROLL_ENVS - 1) / (ENV_WARPS * ROLL_ENVS), ENV_WARPS * 32, 0, st>>>(A);
         if (alt) k_surface_alt<<<env_blocks, ENV_WARPS * 32, 0, st>>>(A, 1);
     }
     if (profile) CK(cudaEventRecord(env->ev[3], st));

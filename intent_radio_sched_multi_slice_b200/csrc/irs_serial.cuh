@@ -471,12 +471,22 @@ __global__ void __launch_bounds__(SERIAL_THREADS, TAIL_T_MINB) k_env_tail_t(cons
     st.out_done[e] = done ? 1 : 0;
 }
 
-// Rollover of the envs that finished in this step (CommunicationEnv.reset, comm_env.py:375-482), one warp
-// per env; every other warp leaves at once.
+// Rollover of the envs that finished in this step (CommunicationEnv.reset, comm_env.py:375-482) by a whole warp per
+// finished env.  A warp looks at ROLL_ENVS envs (in all but one step of an episode none of them is done, so the kernel
+// is launched with 1/8 of the warps a warp-per-env grid would need) and resets the finished ones one after the other.
+#define ROLL_ENVS 8
 __global__ void __launch_bounds__(ENV_WARPS * 32) k_rollover(const __grid_constant__ StepArgs A)
 {
     __shared__ double sm[ENV_WARPS][136];
-    const int e = A.env_begin + blockIdx.x * ENV_WARPS + (threadIdx.x >> 5);
-    if (e >= A.env_end || !A.st.out_done[e]) return;
-    reset_env_warp(A, e, -1, sm[threadIdx.x >> 5]);
+    const int lane = lane_id();
+    const int e0 = A.env_begin + (blockIdx.x * ENV_WARPS + (threadIdx.x >> 5)) * ROLL_ENVS;
+    if (e0 >= A.env_end) return;
+    const bool done = lane < ROLL_ENVS && e0 + lane < A.env_end && A.st.out_done[e0 + lane];
+    uint32_t todo = __ballot_sync(FULL, done);
+    while (todo) {
+        const int e = e0 + __ffs(todo) - 1;
+        todo &= todo - 1;
+        reset_env_warp(A, e, -1, sm[threadIdx.x >> 5]);
+        __syncwarp();
+    }
 }
