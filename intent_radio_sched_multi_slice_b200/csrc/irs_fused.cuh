@@ -235,10 +235,13 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
                 if (pl < row0 + R * 8) asm volatile("prefetch.global.L2 [%0];" ::"l"(pl));
             }
         };
-        prefetch_pair(todo, 0);
-        prefetch_pair(todo, 1);
+#ifndef SE_PREFETCH_AHEAD
+#define SE_PREFETCH_AHEAD 2 /* pairs of rows requested ahead of the pass that sums them */
+#endif
+#pragma unroll
+        for (int k = 0; k < SE_PREFETCH_AHEAD; ++k) prefetch_pair(todo, k);
         while (FUSED_SYNC >= 2 ? __syncthreads_or(todo != 0) : (todo != 0)) {
-            prefetch_pair(todo, 2);
+            prefetch_pair(todo, SE_PREFETCH_AHEAD);
             const int u0 = __ffs(todo) - 1;
             todo &= todo - 1;
             const bool live1 = todo != 0;
