@@ -24,7 +24,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 U = 25
-FIXED_ROW_BYTES = 124  # per UE row besides the buffer: int/f64 records R+W, ring slot R+W, RB run
+FIXED_ROW_BYTES = 140  # per UE row besides the buffer: int/f64 records R+W, window-ring slot R+W, RB run, sum(age*n) R+W
 
 
 def parse():
@@ -340,7 +340,7 @@ def run_b200(args):
     P = max(3, min(K, 20))
     kms = np.zeros(3)
     ue_bytes = 0.0
-    path_frac = np.zeros(3)
+    path_frac = np.zeros(4)
     live_frac = 0.0
     for k in range(P):
         if flush is not None:
@@ -351,11 +351,11 @@ def run_b200(args):
         word = eng.v["path"].long()  # path | live extent << 2 | slots touched << 16 (irs_common.cuh)
         path, dep = word & 3, word >> 16
         live_frac += float(((word >> 2) & 0x3fff).float().sum().item() / depth_tab_t[eng.v["scen"].long()].sum().item())
-        row_b = torch.where(path == 2, 8 * dep, torch.where(path == 1, 4 * dep, 4 * dep))
+        row_b = 4 * dep  # every 4-byte ring-slot access the step made (expiring slot, look-ahead, drain, new arrivals)
         if args.workload == "trace":  # + the 135 float64 SE values of every associated UE's row
             row_b = row_b + 1080 * assoc_tab_t[eng.v["scen"].long()]
         ue_bytes += float((row_b + FIXED_ROW_BYTES).sum().item())
-        path_frac += np.array([(path == i).float().mean().item() for i in range(3)])
+        path_frac += np.array([(path == i).float().mean().item() for i in range(4)])
     kms /= P
     ue_bytes /= P
     path_frac /= P
@@ -379,9 +379,10 @@ def run_b200(args):
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650 GB/s",
                 "algorithmic_bytes_per_launch": ue_bytes, "kernel_ms": kms[1],
                 "kernel_ms_all": {"k_action": kms[0], "k_ue_env": kms[1], "k_env_tail": kms[2]},
-                "bytes_per_ue_row": ("%d (per-UE records) + buffer row: 8*L streamed, 4*L zero-filled (L = the row's live extent), 4 when an empty row receives packets" % FIXED_ROW_BYTES)
+                "bytes_per_ue_row": ("%d (per-UE records) + ring row: 4 per slot access (expiring slot, the 4-slot look-ahead at the old end, slots the drain changes, the arrivals slot)" % FIXED_ROW_BYTES)
                 + (" + 1080 (SE row) per associated UE" if args.workload == "trace" else ""),
-                "row_paths": {"empty": path_frac[0], "zero_fill": path_frac[1], "stream": path_frac[2]},
+                "row_paths": {"no_old_packets": path_frac[0], "window_cleared": path_frac[1], "lane_drain": path_frac[2],
+                              "warp_drain": path_frac[3]},
                 "live_slot_fraction": live_frac}
 
     # ---- e2e: host actions in, host surface out, through irs_step_host ------------------------

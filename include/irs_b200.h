@@ -72,7 +72,8 @@ typedef struct {
 
 typedef struct {
     int32_t num_envs;
-    int32_t depth_cap;       /* max buffer depth (buffer_latency + 1) of any scenario row */
+    int32_t depth_cap;       /* max buffer depth (buffer_latency + 1) of any scenario row; <= 16383 (the live extent of a
+                                row is kept in 14 bits of the per-UE record) */
     int32_t channel_mode;    /* 0 SE injected per call, 1 fixed_se (2.0), 2 native mimic_quadriga,
                                 3 device-resident SE trace bank (irs_set_se_trace; channels/quadriga.py) */
     int32_t traffic_mode;    /* 0 traffic (bits) injected per call, 1 native Poisson */
@@ -96,7 +97,10 @@ typedef struct {
                                   50-value per-slice metric vector, weighted-negative-drift / eMBB-URLLC reward, and
                                   every frame pushed TWICE into the 10-entry window, as those agents do
                                   (sched_twc.py:176-179) */
-    int32_t pad0;
+    int32_t random_episodes; /* enable_random_episodes (comm_env.py:219-226, 434-444): each env plays a shuffled cycle
+                                of [initial_episode, max_episodes) instead of counting up; the order is a counter-based
+                                pseudo-random permutation keyed by (seed, global env id, permutation number), or the
+                                table given to irs_set_episode_order */
     uint64_t seed;
     double bandwidth;        /* Hz, env_config/mult_slice.yml:3 */
 } irs_config;
@@ -107,17 +111,28 @@ typedef struct {
     size_t total_bytes;
     int32_t row_stride;      /* ints per buffer row: depth_cap rounded up to 4 */
     int32_t reserved;
-    size_t buf;              /* i32 [E][25][row_stride]  age histograms (buffer.py:47) */
+    size_t buf;              /* i32 [E][25][row_stride]  age histograms (buffer.py:47) kept as RINGS: the packets of age a
+                                of UE u (depth D_u = its slice's buffer_latency + 1) live in slot (k - a) mod D_u, k = the
+                                env's step counter, so a step moves no packets: it reads the expiring slot, the oldest
+                                slots the drain reaches, and writes slot k mod D_u.  irs_read_buffers returns the
+                                age-indexed view of buffer.py */
     size_t ue_i;             /* i32 [E][25][8]  per-UE record: packets in buffer, window sums of
                                 sent / dropped, newest frame's sent / dropped / incoming,
-                                isclose(win[1].occ, 0), row word = path taken (0 empty, 1 zero-fill,
-                                2 stream) | live extent << 2 (14 bits: oldest non-empty slot + 1; every
-                                slot of the row at or beyond it is zero) | slots touched << 16 */
+                                isclose(win[1].occ, 0), row word = path taken (0 no older packets, 1 all older packets
+                                left: window cleared, 2 drain inside the lane's 4-slot look-ahead, 3 longer drain by the
+                                warp) | live extent << 2 (14 bits: every age at or beyond it is empty) | 4-byte slot
+                                accesses of the step << 16 */
     size_t ue_d;             /* f64 [E][25][4]  newest window frame: occupancy, mean delay, mean SE,
                                 pkt_throughputs */
     size_t ring;             /* i32 [E][25][10][2] (sent, dropped) of the last 10 frames */
     size_t rb;               /* i16 [E][25][2] (rb_start, rb_count): contiguous RB run of each UE */
     size_t step, episode, scen, win_len, win_head, err; /* i32 [E] */
+    size_t visit;            /* i32 [E] resets this env has seen: part of the generators' key, so that an episode NUMBER
+                                played again draws fresh channel / traffic noise (the reference keeps ONE np_random stream
+                                running across episodes, comm_env.py:631-679) */
+    size_t ep_pos, ep_gen, ep_base; /* i32 [E] random_episodes: position in the current permutation, permutations drawn so
+                                far, first episode of the permuted range (comm_env.py:219-226, 434-444) */
+    size_t wsum;             /* i64 [E][25] sum(age * packets) of each buffer, updated incrementally (buffer.py:116-130) */
     size_t sorted;           /* i8  [E][5] IBSched.sorted_slices */
     size_t acc;              /* f64 [E][16] episode-metric accumulators */
     size_t bank;             /* irs_scenario [n_scen] */
@@ -242,6 +257,15 @@ int irs_episode_metrics(irs_env* env, double* host_out, void* stream);
 /* debug=True of the reference (comm_env.py:313-319): synchronises, returns IRS_ERR_ENV and the
  * index of the first env with a non-zero error word. */
 int irs_check_errors(irs_env* env, int32_t* first_env, int32_t* code, void* stream);
+/* random_episodes with a GIVEN order (parity runs replay the permutation the reference drew from its np_random):
+ * order_dev is i32 [E][n], caller-owned device memory kept alive while in use; env e plays order_dev[e][pos % n].
+ * The call also moves every env to the table's entry at its current position (position 0 right after irs_bind:
+ * comm_env.py:225).  A reset with initial_episode != -1 restarts at position 0 (the reference draws a new
+ * permutation there, comm_env.py:435-442: upload it before that reset).  NULL returns to the built-in permutation. */
+int irs_set_episode_order(irs_env* env, const int32_t* order_dev, int32_t n, void* stream);
+/* Buffer.buffer of every UE as the reference indexes it (buffer.py:47: index = age in steps): i32
+ * [E][25][row_stride] into caller-owned device memory, de-rotating the ring rows.  Asynchronous on `stream`. */
+int irs_read_buffers(irs_env* env, int32_t* out_dev, void* stream);
 const char* irs_last_error(const irs_env* env);
 int irs_version(void);
 

@@ -18,8 +18,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "_lib")
 LIB = os.environ.get("IRS_LIB_PATH") or os.path.join(LIB_DIR, "libirs_b200.so")
 SOURCES = ["irs_capi.cu"]
-HEADERS = ["irs_common.cuh", "irs_rng.cuh", "irs_action.cuh", "irs_ue.cuh", "irs_obs.cuh", "irs_env.cuh", "irs_fused.cuh",
-           os.path.join("..", "..", "include", "irs_b200.h")]
+HEADERS = sorted(f for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))) + [os.path.join("..", "..", "include", "irs_b200.h")]
 
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-fmad=false",

@@ -26,12 +26,12 @@ class Config(C.Structure):
     _fields_ = [(n, C.c_int32) for n in (
         "num_envs", "depth_cap", "channel_mode", "traffic_mode", "sort_slices", "fixed_intra", "policy",
         "assoc_mode", "scen_mod", "scen_div", "n_scen", "max_steps", "max_episodes", "initial_episode",
-        "auto_reset", "env_id_base", "surface", "pad0")] + [("seed", C.c_uint64), ("bandwidth", C.c_double)]
+        "auto_reset", "env_id_base", "surface", "random_episodes")] + [("seed", C.c_uint64), ("bandwidth", C.c_double)]
 
 
 _LAYOUT_ARRAYS = [
     "buf", "ue_i", "ue_d", "ring", "rb", "step", "episode", "scen", "win_len",
-    "win_head", "err", "sorted", "acc", "bank", "cdf", "in_a0", "in_intra", "out_obs0", "out_obsi",
+    "win_head", "err", "visit", "ep_pos", "ep_gen", "ep_base", "wsum", "sorted", "acc", "bank", "cdf", "in_a0", "in_intra", "out_obs0", "out_obsi",
     "out_mask0", "out_maski", "out_reward", "out_done", "metrics_total", "out32",
 ]
 UI_FIELDS = ["tot", "sum_sent", "sum_drop", "last_sent", "last_drop", "last_inc", "occ1z", "path"]
@@ -88,6 +88,8 @@ SYMBOLS = {
     "irs_reset_host": (C.c_int, [_P, C.c_int32, C.POINTER(HostSurface), _P]),
     "irs_episode_metrics": (C.c_int, [_P, _P, _P]),
     "irs_check_errors": (C.c_int, [_P, C.POINTER(C.c_int32), C.POINTER(C.c_int32), _P]),
+    "irs_set_episode_order": (C.c_int, [_P, _P, C.c_int32, _P]),
+    "irs_read_buffers": (C.c_int, [_P, _P, _P]),
     "irs_last_error": (C.c_char_p, [_P]),
 }
 

@@ -38,8 +38,8 @@ struct irs_env {
                                    // thread per env leaves the SMs too empty to hide its serial latency
     const double* se_bank;         // channel_mode 3 (irs_set_se_trace)
     int32_t bank_eps, bank_steps;
-    int mode; // IRS_STEP_MODE: 0 fused k_env_step, 1 k_action + k_ue_step (warp per row) + k_env_tail,
-              //                2 k_action + k_ue_env (warp per env) + k_env_tail
+    const int32_t* ep_order;       // random_episodes with a given order (irs_set_episode_order)
+    int32_t ep_order_n;
     char err[256];
 };
 
@@ -59,6 +59,8 @@ static void compute_layout(const irs_config& c, int32_t n_lambda, irs_layout* L)
     L->rb = take(E * U * 4);
     L->step = take(E * 4); L->episode = take(E * 4); L->scen = take(E * 4);
     L->win_len = take(E * 4); L->win_head = take(E * 4); L->err = take(E * 4);
+    L->visit = take(E * 4); L->ep_pos = take(E * 4); L->ep_gen = take(E * 4); L->ep_base = take(E * 4);
+    L->wsum = take(E * U * 8);
     L->sorted = take(E * S);
     L->acc = take(E * IRS_NUM_METRICS * 8);
     // assoc_mode 2: the n_scen slice-type templates are followed by two private scenario rows per env
@@ -99,6 +101,8 @@ static StepArgs make_args(const irs_env* env)
     A.se_bank = env->se_bank;
     A.bank_eps = env->bank_eps;
     A.bank_steps = env->bank_steps;
+    A.ep_order = env->ep_order;
+    A.ep_order_n = env->ep_order_n;
     A.win_cap = env->cfg.surface ? W / 2 : W;
     A.win_mul = env->cfg.surface ? 2 : 1;
     A.defer_rollover = 0;
@@ -134,7 +138,8 @@ int irs_create(const irs_config* cfg, int32_t n_lambda, irs_env** out)
 {
     if (!cfg || !out) return IRS_ERR_ARG;
     *out = nullptr;
-    if (cfg->num_envs <= 0 || cfg->depth_cap <= 0 || cfg->n_scen <= 0 || cfg->max_steps <= 0 ||
+    if (cfg->num_envs <= 0 || cfg->depth_cap <= 0 || cfg->depth_cap > 16383 /* ROW_LIVE: 14 bits */ ||
+        cfg->random_episodes < 0 || cfg->random_episodes > 1 || cfg->n_scen <= 0 || cfg->max_steps <= 0 ||
         cfg->channel_mode < 0 || cfg->channel_mode > 3 || cfg->traffic_mode < 0 || cfg->traffic_mode > 1 ||
         cfg->policy < 0 || cfg->policy > 3 || cfg->surface < 0 || cfg->surface > 2 || cfg->fixed_intra < -1 || cfg->fixed_intra > 2 ||
         (cfg->assoc_mode == 0 && cfg->scen_mod <= 0) || (cfg->assoc_mode == 1 && cfg->scen_div <= 0) ||
@@ -146,8 +151,6 @@ int irs_create(const irs_config* cfg, int32_t n_lambda, irs_env** out)
     memset(env, 0, sizeof(*env));
     env->cfg = *cfg;
     env->n_lambda = n_lambda;
-    const char* sp = getenv("IRS_STEP_MODE");
-    env->mode = sp ? atoi(sp) : 2;
     const char* us_ = getenv("IRS_UE_SPLIT");
     env->ue_split = us_ ? atoi(us_) : -1;
     if (env->ue_split > 2) env->ue_split = 2;
@@ -197,6 +200,9 @@ int irs_bind(irs_env* env, void* state_dev, size_t bytes, void* stream)
     s.rb = (short2*)(b + L.rb);
     s.step = (int32_t*)(b + L.step); s.episode = (int32_t*)(b + L.episode); s.scen = (int32_t*)(b + L.scen);
     s.win_len = (int32_t*)(b + L.win_len); s.win_head = (int32_t*)(b + L.win_head); s.err = (int32_t*)(b + L.err);
+    s.visit = (int32_t*)(b + L.visit); s.ep_pos = (int32_t*)(b + L.ep_pos); s.ep_gen = (int32_t*)(b + L.ep_gen);
+    s.ep_base = (int32_t*)(b + L.ep_base);
+    s.wsum = (long long*)(b + L.wsum);
     s.sorted = (int8_t*)(b + L.sorted);
     s.acc = (double*)(b + L.acc);
     s.bank = (const irs_scenario*)(b + L.bank);
@@ -278,23 +284,14 @@ static int launch_step(irs_env* env, const StepArgs& A, cudaStream_t st, bool pr
     const int E = A.env_end - A.env_begin;
     if (E <= 0) return IRS_OK;
     if (profile) CK(cudaEventRecord(env->ev[0], st));
-    if (env->mode == 0) {
-        if (profile) CK(cudaEventRecord(env->ev[1], st));
-        k_env_step<<<(E + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(A);
-        if (profile) { CK(cudaEventRecord(env->ev[2], st)); CK(cudaEventRecord(env->ev[3], st)); }
-        CK(cudaGetLastError());
-        return IRS_OK;
-    }
     const bool serial = E >= env->serial_min;
     if (serial) k_action_t<<<(E + SERIAL_THREADS - 1) / SERIAL_THREADS, SERIAL_THREADS, 0, st>>>(A);
     else k_action<<<(E + 7) / 8, 256, 0, st>>>(A);
     if (profile) CK(cudaEventRecord(env->ev[1], st));
-    const long long rows = (long long)E * U;
     StepArgs B2 = A; // small batches: 2 or 4 warps per env, so that the launch still puts ~32 warps on every SM
     B2.ue_split_log2 = env->ue_split >= 0 ? env->ue_split : (E <= 1184 ? 2 : (E <= 2368 ? 1 : 0));
     const unsigned env_warps = (unsigned)E << B2.ue_split_log2;
-    if (env->mode == 1) k_ue_step<<<(unsigned)((rows + UE_WARPS - 1) / UE_WARPS), UE_WARPS * 32, 0, st>>>(A);
-    else if (A.raw.se_used) k_ue_env_raw<<<(env_warps + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(B2);
+    if (A.raw.se_used) k_ue_env_raw<<<(env_warps + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(B2);
     else k_ue_env<<<(env_warps + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(B2);
     if (profile) CK(cudaEventRecord(env->ev[2], st));
     const bool alt = env->cfg.surface != 0; // SchedTWC / SchedColORAN: their surface reads the step's records before
@@ -373,6 +370,33 @@ int irs_set_se_trace(irs_env* env, const double* se_bank_dev, int32_t n_episodes
     env->se_bank = se_bank_dev;
     env->bank_eps = n_episodes;
     env->bank_steps = n_steps;
+    return IRS_OK;
+}
+
+int irs_set_episode_order(irs_env* env, const int32_t* order_dev, int32_t n, void* stream)
+{
+    if (!env) return IRS_ERR_ARG;
+    if (!env->bound) return fail(env, IRS_ERR_UNBOUND, "irs_bind first");
+    if (!env->cfg.random_episodes) return fail(env, IRS_ERR_ARG, "irs_set_episode_order needs cfg.random_episodes");
+    if (order_dev && n <= 0) return fail(env, IRS_ERR_ARG, "irs_set_episode_order: empty order");
+    env->ep_order = order_dev;
+    env->ep_order_n = order_dev ? n : 0;
+    if (order_dev) {
+        StepArgs A = make_args(env);
+        k_apply_order<<<(env->cfg.num_envs + 255) / 256, 256, 0, (cudaStream_t)stream>>>(A);
+        CK(cudaGetLastError());
+    }
+    return IRS_OK;
+}
+
+int irs_read_buffers(irs_env* env, int32_t* out_dev, void* stream)
+{
+    if (!env || !out_dev) return IRS_ERR_ARG;
+    if (!env->bound || !env->loaded) return fail(env, IRS_ERR_UNBOUND, "irs_bind and irs_load_scenarios first");
+    StepArgs A = make_args(env);
+    const size_t rows = (size_t)env->cfg.num_envs * U;
+    k_read_buffers<<<(unsigned)((rows + 7) / 8), 256, 0, (cudaStream_t)stream>>>(A, out_dev);
+    CK(cudaGetLastError());
     return IRS_OK;
 }
 

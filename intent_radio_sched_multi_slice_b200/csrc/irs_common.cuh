@@ -25,9 +25,9 @@ enum { ERR_INTRA_ACTION = 1, ERR_EPISODE_RANGE = 2, ERR_RB_SUM = 4 };
 //   ring[E][25][10] int2 : (sent, dropped) of the last 10 frames (agents/ib_sched.py:49-51)
 //   rb[E][25]       short2: (rb_start, rb_count) contiguous RB run of the UE
 enum { UI_TOT = 0, UI_SUM_SENT, UI_SUM_DROP, UI_SENT, UI_DROP, UI_INC, UI_OCC1Z, UI_PATH, UI_N };
-// UI_PATH word: row path of the step (2 bits) | live extent << 2 (14 bits) | slots the step touched
-// << 16 (bench.py's byte accounting reads the last).  Invariant: every slot of a buffer row at or
-// beyond its live extent is zero, so the row kernels never read or write past it.
+// UI_PATH word: row path of the step (2 bits) | live extent << 2 (14 bits) | 4-byte slot accesses of
+// the step << 16 (bench.py's byte accounting reads the last).  Invariant: every AGE of a buffer row at
+// or beyond its live extent is empty, so the row code never reads or writes past it.
 #define ROW_LIVE(word) (((word) >> 2) & 0x3fff)
 #define ROW_WORD(path, live, slots) ((path) | ((live) << 2) | ((slots) << 16))
 enum { UD_OCC = 0, UD_LAT, UD_SEBAR, UD_THR, UD_N };
@@ -40,6 +40,8 @@ struct DevState {
     int2* ring;
     short2* rb;
     int32_t *step, *episode, *scen, *win_len, *win_head, *err;
+    int32_t *visit, *ep_pos, *ep_gen, *ep_base;
+    long long* wsum;
     int8_t* sorted;
     double* acc;
     const irs_scenario* bank;
@@ -63,6 +65,8 @@ struct StepArgs {
     const double* traffic; // injected traffic or NULL
     const double* se_bank; // channel_mode 3: [bank_eps][bank_steps][U][R] SE trace (irs_set_se_trace)
     int32_t bank_eps, bank_steps;
+    const int32_t* ep_order; // random_episodes with a given order: [E][ep_order_n] (irs_set_episode_order), else NULL
+    int32_t ep_order_n;
     irs_raw_outputs raw;   // optional extra outputs (all may be NULL)
     const uint8_t* reset_mask;
     const int32_t* initial_episode_dev;
@@ -79,6 +83,9 @@ struct StepArgs {
 };
 
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
+// Key of env state for the counter-based generators: the seed with the env's reset count in the upper word, so an
+// episode number that is visited again does not replay its noise (the reference's np_random stream runs on).
+__host__ __device__ __forceinline__ uint64_t env_key(uint64_t seed, int visit) { return seed + ((uint64_t)(uint32_t)visit << 32); }
 __device__ __forceinline__ bool isclose0(double x) { return fabs(x) <= 1e-8; } // np.isclose(x, 0)
 
 // ---- ordered reductions over a group of lanes --------------------------------------------

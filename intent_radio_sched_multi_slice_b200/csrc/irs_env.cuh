@@ -25,12 +25,12 @@ struct ScenWords {
     }
     __device__ int below(int n) { return (int)(((uint64_t)next() * (uint32_t)n) >> 32); } // uniform in [0, n)
 };
-__device__ __noinline__ void generate_scenario_row(const StepArgs& A, int e, int ep, irs_scenario* row)
+__device__ __noinline__ void generate_scenario_row(const StepArgs& A, uint64_t key, int e, int ep, irs_scenario* row)
 {
     const irs_scenario* types = A.st.bank;
     const int T = A.cfg.n_scen;
     ScenWords g;
-    g.seed = A.cfg.seed; g.episode = ep; g.gid = A.cfg.env_id_base + e; g.i = 0;
+    g.seed = key; g.episode = ep; g.gid = A.cfg.env_id_base + e; g.i = 0;
     int slots[S], tys[32], counts[S], ues[U];
     const int k = 3 + g.below(S - 3 + 1);
     for (int j = 0; j < S; ++j) slots[j] = j;
@@ -68,40 +68,69 @@ __device__ __noinline__ void reset_env_warp(const StepArgs& A, int e, int initia
     const DevState& st = A.st;
     const irs_config& c = A.cfg;
     const int lane = lane_id();
+    const int gid = c.env_id_base + e;
     int step = st.step[e], ep = st.episode[e];
-    const int init = initial_episode != -1 ? initial_episode : c.initial_episode;
-    if ((step == 0 && ep == 0) || (step == c.max_steps && ep == c.max_episodes - 1) || initial_episode != -1) {
-        ep = init;                                              // comm_env.py:416-421
-    } else if (step == 0 && ep <= c.max_episodes - 1) {         // :422-425
-    } else if (ep < c.max_episodes - 1) {
-        ep += 1;                                                // :426-427
+    if (c.random_episodes) { // comm_env.py:434-444: a shuffled cycle over [initial_episode, max_episodes)
+        int pos = st.ep_pos[e], gen = st.ep_gen[e], base = st.ep_base[e];
+        bool moved = false;
+        if (initial_episode != -1) { base = initial_episode; gen += 1; pos = 0; moved = true; } // :435-442 new permutation
+        if (step == c.max_steps) { pos += 1; moved = true; }                                    // :443-444 next(cycle)
+        const int n = A.ep_order ? A.ep_order_n : c.max_episodes - base;
+        if (n <= 0) {
+            if (lane == 0) atomicOr(&st.err[e], ERR_EPISODE_RANGE);
+            return;
+        }
+        pos %= n;
+        if (moved) ep = A.ep_order ? A.ep_order[(size_t)e * n + pos] : shuffled_episode(c.seed, gid, gen, base, n, pos);
+        __syncwarp();
+        if (lane == 0) { st.ep_pos[e] = pos; st.ep_gen[e] = gen; st.ep_base[e] = base; }
     } else {
-        if (lane == 0) atomicOr(&st.err[e], ERR_EPISODE_RANGE); // :428-433
-        return;
+        const int init = initial_episode != -1 ? initial_episode : c.initial_episode;
+        if ((step == 0 && ep == 0) || (step == c.max_steps && ep == c.max_episodes - 1) || initial_episode != -1) {
+            ep = init;                                              // comm_env.py:416-421
+        } else if (step == 0 && ep <= c.max_episodes - 1) {         // :422-425
+        } else if (ep < c.max_episodes - 1) {
+            ep += 1;                                                // :426-427
+        } else {
+            if (lane == 0) atomicOr(&st.err[e], ERR_EPISODE_RANGE); // :428-433
+            return;
+        }
     }
+    const int visit = st.visit[e] + 1;
+    const uint64_t key = env_key(c.seed, visit);
+    // fresh UEs: empty buffers (comm_env.py:620-625, associations/mult_slice.py:468-488).  Only the live window of a
+    // ring row can hold packets: ages [0, live) = slots (step - age) mod depth, with the depths of the OLD scenario.
+    {
+        const irs_scenario* old = st.bank + st.scen[e];
+        for (int u = 0; u < U; ++u) {
+            const size_t eu = (size_t)e * U + u;
+            const int live = ROW_LIVE(st.ue_i[eu * UI_N + UI_PATH]);
+            const int sl = ((const volatile int8_t*)old->ue_slice)[u];
+            int depth = sl < 0 ? 101 : (int)((const volatile double*)&old->sl[sl].buffer_latency)[0] + 1;
+            if (depth > st.row_stride) depth = st.row_stride;
+            int* row = st.buf + eu * st.row_stride;
+            const int head = step % depth;
+            for (int a = lane; a < live; a += 32) row[head - a + (head < a ? depth : 0)] = 0;
+        }
+    }
+    __syncwarp();
     int scen;
-    if (c.assoc_mode == 2) {
-        scen = c.n_scen + 2 * e + (ep & 1);
-        if (lane == 0) generate_scenario_row(A, e, ep, const_cast<irs_scenario*>(st.bank) + scen);
+    if (c.assoc_mode == 2) { // the env's other private row: the one in use was read through the read-only cache
+        const int row0 = c.n_scen + 2 * e;
+        scen = st.scen[e] == row0 ? row0 + 1 : row0;
+        if (lane == 0) generate_scenario_row(A, key, e, ep, const_cast<irs_scenario*>(st.bank) + scen);
         __syncwarp();
     } else {
         scen = scen_of_episode(c, ep);
     }
     const irs_scenario* sc = st.bank + scen;
     __syncwarp();
-    if (lane == 0) { st.step[e] = 0; st.episode[e] = ep; st.scen[e] = scen; }
-    // fresh UEs: empty buffers (comm_env.py:620-625, associations/mult_slice.py:468-488)
-    for (int u = 0; u < U; ++u) { // only a row's live extent can hold packets
-        const size_t eu = (size_t)e * U + u;
-        const int live = ROW_LIVE(st.ue_i[eu * UI_N + UI_PATH]);
-        int4* row4 = reinterpret_cast<int4*>(st.buf + eu * st.row_stride);
-        for (int i = lane; 4 * i < live; i += 32) row4[i] = make_int4(0, 0, 0, 0);
-    }
+    if (lane == 0) { st.step[e] = 0; st.episode[e] = ep; st.scen[e] = scen; st.visit[e] = visit; }
     __syncwarp();
     // channel frame 0 of the new episode -> mean SE per UE (comm_env.py:449-451)
     double sebar = 0;
     for (int u = 0; u < U; ++u) {
-        channel_row(A, e, u, sc->ue_slice[u] >= 0, 0, ep, se_row);
+        channel_row(A, key, e, u, sc->ue_slice[u] >= 0, 0, ep, se_row);
         __syncwarp();
         if (A.raw.se_used)
             for (int r = lane; r < R; r += 32) A.raw.se_used[((size_t)e * U + u) * R + r] = se_row[r];
@@ -128,6 +157,7 @@ __device__ __noinline__ void reset_env_warp(const StepArgs& A, int e, int initia
         ui[UI_INC] = 0; ui[UI_OCC1Z] = f.occ1z ? 1 : 0; ui[UI_PATH] = 0;
         ud[UD_OCC] = 0; ud[UD_LAT] = 0; ud[UD_SEBAR] = sebar; ud[UD_THR] = 0;
         st.rb[eu] = make_short2(0, 0);
+        st.wsum[eu] = 0;
     }
     const int win_len_new = win_len < A.win_cap ? win_len + 1 : A.win_cap;
     __syncwarp();
@@ -292,8 +322,39 @@ __global__ void k_init(const __grid_constant__ StepArgs A)
 {
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= A.cfg.num_envs) return;
-    A.st.episode[e] = A.cfg.initial_episode;
+    int ep = A.cfg.initial_episode;
+    if (A.cfg.random_episodes) { // comm_env.py:219-226: the first permutation is drawn at construction
+        const int n = A.cfg.max_episodes - ep;
+        A.st.ep_base[e] = ep;
+        if (n > 0) ep = shuffled_episode(A.cfg.seed, A.cfg.env_id_base + e, 0, ep, n, 0);
+    }
+    A.st.episode[e] = ep;
     for (int s = 0; s < S; ++s) A.st.sorted[(size_t)e * S + s] = (int8_t)s;
+}
+
+// irs_set_episode_order: every env moves to the given table's entry at its current position
+__global__ void k_apply_order(const __grid_constant__ StepArgs A)
+{
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= A.cfg.num_envs || !A.ep_order) return;
+    A.st.episode[e] = A.ep_order[(size_t)e * A.ep_order_n + A.st.ep_pos[e] % A.ep_order_n];
+}
+
+// irs_read_buffers: the age-indexed view of the ring rows (buffer.py:47), one warp per (env, UE) row.
+__global__ void __launch_bounds__(256) k_read_buffers(const __grid_constant__ StepArgs A, int32_t* __restrict__ out)
+{
+    const DevState& st = A.st;
+    const size_t row_id = (size_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (row_id >= (size_t)A.cfg.num_envs * U) return;
+    const int e = (int)(row_id / U), u = (int)(row_id - (size_t)e * U);
+    const irs_scenario* sc = st.bank + st.scen[e];
+    UeParams up = ue_params(sc, sc->ue_slice[u]);
+    if (up.depth > st.row_stride) up.depth = st.row_stride;
+    const int head = st.step[e] % up.depth;
+    const int* row = st.buf + row_id * st.row_stride;
+    int32_t* dst = out + row_id * st.row_stride;
+    for (int a = lane_id(); a < st.row_stride; a += 32)
+        dst[a] = a < up.depth ? row[head - a + (head < a ? up.depth : 0)] : 0;
 }
 
 // Sum of the per-env accumulators in a FIXED order (reproducible bits for a given batch size): block k sums

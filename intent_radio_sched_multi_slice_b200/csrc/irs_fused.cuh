@@ -1,32 +1,23 @@
-// irs_fused.cuh - k_env_step: the whole CommunicationEnv.step of one env in ONE warp.
+// irs_fused.cuh - k_ue_env: the per-UE middle of CommunicationEnv.step (channel, traffic, throughput,
+// buffers, per-UE window push; comm_env.py:302-326, ues.py:149-243) of one env in ONE warp, between k_action
+// and k_env_tail.
 //
-// Lane u = UE u for everything that is per-UE scalar work (RB allocation, closed-form buffer
-// arithmetic, intent drift, window push) - the same mapping k_action and k_env_tail use, so
-// their cores are reused on register inputs and nothing makes a round trip through HBM between
-// the stages.  The two warp-wide stages are
-//   * the generators: (UE, Philox quad) tasks of up to 4 associated UEs are packed over the 32
-//     lanes - 4 main passes (lane l = SE quad l of one UE) + 1 auxiliary pass that serves all 4
-//     UEs at once (6 lanes per UE: 4 half-quads for RBs 128..134, the per-episode mean, the
-//     Poisson arrival) - and the 135-term NumPy-order sums of each generated row;
-//   * the buffer rows that need touching (zero-fill / stream paths), one row after the other
-//     with 128-bit accesses (irs_ue.cuh).
-// Compared with one warp per UE row this removes the per-row scalar prologue/epilogue (done
-// once per env, 25 UEs wide), skips unassociated UEs entirely, and replaces three launches by
-// one.  Same reference symbols as irs_action.cuh / irs_ue.cuh / irs_obs.cuh / irs_env.cuh.
+// Lane u = UE u for everything that is per-UE scalar work (closed-form buffer arithmetic, ring-row
+// update, window push).  The one warp-wide stage is the generators: (UE, Philox quad) tasks of up to 4
+// associated UEs are packed over the 32 lanes - pair passes (lanes 0..15 one UE, lanes 16..31 another;
+// a lane adds up the 8 elements of one accumulator of NumPy's pairwise sum in registers) + 1 auxiliary
+// pass that serves all 4 UEs at once (6 lanes per UE: 4 half-quads for RBs 128..134, the per-episode
+// mean, the Poisson arrival).  Unassociated UEs are skipped entirely.  Buffer rows are rings
+// (irs_ue.cuh): a UE lane loads the expiring slot and its 4 oldest slots in the prologue, before the
+// generators run, and resolves the step's drain on them after the closed form; only a drain that
+// reaches further, or a window of more than 4 slots that empties, is handed to the whole warp.
 #pragma once
 #include "irs_action.cuh"
 #include "irs_env.cuh"
 #include "irs_ue.cuh"
 
 #ifndef FUSED_WARPS
-#define FUSED_WARPS 4 /* envs per block */
-#endif
-#ifndef FUSED_SYNC
-#define FUSED_SYNC 0 /* 1: block-wide barriers between phases keep the SM's warps in the same code region */
-#endif
-#define PHASE_SYNC() do { if (FUSED_SYNC) __syncthreads(); } while (0)
-#ifndef FUSED_MINB
-#define FUSED_MINB 4 /* resident blocks per SM the register budget is set for */
+#define FUSED_WARPS 4 /* warps per block */
 #endif
 #define GRP 4         /* UE rows generated per group */
 
@@ -39,26 +30,23 @@ __device__ __forceinline__ T sel4(const T (&a)[GRP], int j)
     return v;
 }
 
-// FULL_STEP = true : the whole step (action -> rows -> observation/reward/rollover) in one kernel.
-// FULL_STEP = false: only the per-UE middle of the step (what k_ue_step does per row), between
-//                    k_action and k_env_tail; every warp of the GPU then runs the same, much
-//                    smaller code region, which the instruction cache holds.
-template <bool FULL_STEP, bool RAWSE>
-__device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GRP][136])
+template <bool RAWSE>
+__device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP][136])
 {
     const DevState& st = A.st;
     const irs_config& cfg = A.cfg;
     const int lane = lane_id();
     const int wib = threadIdx.x >> 5;
-    const int split = FULL_STEP ? 0 : A.ue_split_log2, gmask = (1 << split) - 1;
+    const int split = A.ue_split_log2, gmask = (1 << split) - 1;
     const int wglob = blockIdx.x * FUSED_WARPS + wib;
     const int e = A.env_begin + (wglob >> split), grp = wglob & gmask; // this warp serves the UEs u with (u & gmask) == grp
     if (e >= A.env_end) return;
 
-    // ---- phase 0: env scalars and this lane's UE record ------------------------------------
+    // ---- phase 0: env scalars, this lane's UE record, and the ring slots the step can touch -------
     const int step = st.step[e], episode = st.episode[e];
-    const int win_len = st.win_len[e], head = st.win_head[e];
-    const int p = (head + 1) % A.win_cap; // window slot of this frame (deque.appendleft)
+    const int win_len = st.win_len[e], head_w = st.win_head[e];
+    const int p = (head_w + 1) % A.win_cap; // window slot of this frame (deque.appendleft)
+    const uint64_t key = env_key(cfg.seed, st.visit[e]);
     const irs_scenario* sc = st.bank + st.scen[e];
     const bool ue_lane = lane < U && (lane & gmask) == grp;
     const int s_mine = ue_lane ? (int)sc->ue_slice[lane] : -1;
@@ -66,26 +54,28 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
     if (up.depth > st.row_stride) up.depth = st.row_stride;
     const size_t eu = (size_t)e * U + (ue_lane ? lane : 0);
     const int4 rec_a = *reinterpret_cast<const int4*>(st.ue_i + eu * UI_N); // tot, sum_sent, sum_drop, sent
-    const double2 rec_d0 = *reinterpret_cast<const double2*>(st.ue_d + eu * UD_N);     // occ, lat
-    const double2 rec_d1 = *reinterpret_cast<const double2*>(st.ue_d + eu * UD_N + 2); // sebar, thr
+    const double2 rec_d0 = *reinterpret_cast<const double2*>(st.ue_d + eu * UD_N); // occ, lat
     int2 evict = make_int2(0, 0);
     if (ue_lane && win_len == A.win_cap) evict = st.ring[eu * W + p];
     const int tot_prev = ue_lane ? rec_a.x : 0;
     int* row = st.buf + eu * (size_t)st.row_stride;
-    const int live_prev = ue_lane ? ROW_LIVE(st.ue_i[eu * UI_N + UI_PATH]) : 0; // slots [0, live_prev) may hold packets
-    const int expired = (ue_lane && live_prev == up.depth) ? row[up.depth - 1] : 0; // buffer.py:60, in flight early
+    const int live_prev = ue_lane ? ROW_LIVE(st.ue_i[eu * UI_N + UI_PATH]) : 0; // ages [0, live_prev) may hold packets
+    const long long wsum_prev = ue_lane ? st.wsum[eu] : 0;
     const int frame = step + 1, gid = cfg.env_id_base + e;
-
-    // ---- phase 1: action -> RB runs (ib_sched.py:223-349) ---------------------------------
-    int rb_s, rb_c;
-    if (FULL_STEP) {
-        action_to_rb_core(A, e, sc, rec_d0.x, rec_d1.x, rec_a.y, win_len, step, episode, rb_s, rb_c);
-    } else {
-        const short2 run = st.rb[eu];
-        rb_s = run.x; rb_c = run.y;
+    const int head = frame % up.depth;                 // slot of age 0 after this step
+    const int a_old = min(live_prev, up.depth - 1);    // oldest age that may hold packets after the shift (0: none)
+    // buffer.py:60: the packets that reach age `depth` now sit in the slot the new arrivals will take
+    const int expired = (ue_lane && live_prev == up.depth) ? row[head] : 0;
+    int look[RING_LOOK]; // ages a_old, a_old - 1, ...: consecutive slots from ring_slot(head, a_old)
+    const int p_old = ring_slot(head, a_old, up.depth);
+#pragma unroll
+    for (int k = 0; k < RING_LOOK; ++k) {
+        const int q = p_old + k;
+        look[k] = (ue_lane && a_old - k >= 1) ? row[q >= up.depth ? q - up.depth : q] : 0;
     }
+    const short2 run = st.rb[eu];
+    const int rb_s = run.x, rb_c = run.y;
 
-    PHASE_SYNC();
     // ---- phase 2: channel + traffic of this frame, and the two row sums per UE --------------
     const bool native = cfg.channel_mode == 2 && cfg.traffic_mode == 1;
     const int fl_mine = s_mine >= 0 ? __ldg(&sc->sl[s_mine].flags) : 0;
@@ -94,14 +84,14 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
     double sum_t = 0.0, sum_se = 0.0, traffic = 0.0, mu_l = 0.0;
     if (!native) {
         if (cfg.traffic_mode == 0) traffic = ue_lane ? A.traffic[eu] : 0.0;
-        else if (has_traffic) traffic = native_traffic(cfg.seed, st.cdf, lane, lam_idx, frame, episode, gid);
+        else if (has_traffic) traffic = native_traffic(key, st.cdf, lane, lam_idx, frame, episode, gid);
     }
     if (native) {
         // Per-warp scratch in shared memory: tail (SE, throughput term) pairs of the group's rows at
         // ws[16 j .. 16 j + 13], per-UE results (sum_t, sum_se, traffic) at ws[64 + 4 u ..].
         double* ws = &sm[wib][0][0];
         uint32_t todo = __ballot_sync(FULL, ue_lane && s_mine >= 0);
-        while (FUSED_SYNC >= 2 ? __syncthreads_or(todo != 0) : (todo != 0)) { // warp-uniform (block-uniform when synced)
+        while (todo != 0) { // warp-uniform
             uint32_t ulp = 0; // lane ids of the group's UEs, one byte each
             int n = 0;
 #pragma unroll
@@ -115,7 +105,7 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
                 const int ue_j = (ulp >> (8 * (j & 3))) & 31;
                 const int kind = k < 4 ? K_SE : (k == 4 ? K_MU : K_TRAFFIC);
                 const int q = k < 2 ? 32 : (k < 4 ? 33 : 0);
-                const uint4 w = rng_quad(cfg.seed, kind, ue_j, q, k == 4 ? 0 : frame, episode, gid);
+                const uint4 w = rng_quad(key, kind, ue_j, q, k == 4 ? 0 : frame, episode, gid);
                 const bool hi_pair = k < 4 && (k & 1);
                 float z0, z1;
                 normal_pair(hi_pair ? w.z : w.x, hi_pair ? w.w : w.y, z0, z1);
@@ -167,7 +157,7 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
                 double* se_out = (RAWSE && A.raw.se_used) ? A.raw.se_used + ((size_t)e * U + uj) * R : nullptr;
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
-                    const uint4 wb = rng_quad(cfg.seed, K_SE, uj, 2 * l16 + h, frame, episode, gid);
+                    const uint4 wb = rng_quad(key, K_SE, uj, 2 * l16 + h, frame, episode, gid);
                     float y[4];
                     normal_pair(wb.x, wb.y, y[0], y[1]);
                     normal_pair(wb.z, wb.w, y[2], y[3]);
@@ -240,7 +230,7 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
 #endif
 #pragma unroll
         for (int k = 0; k < SE_PREFETCH_AHEAD; ++k) prefetch_pair(todo, k);
-        while (FUSED_SYNC >= 2 ? __syncthreads_or(todo != 0) : (todo != 0)) {
+        while (todo != 0) {
             prefetch_pair(todo, SE_PREFETCH_AHEAD);
             const int u0 = __ffs(todo) - 1;
             todo &= todo - 1;
@@ -297,7 +287,7 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
         }
     } else {
     uint32_t todo = __ballot_sync(FULL, ue_lane);
-    while (FUSED_SYNC >= 2 ? __syncthreads_or(todo != 0) : (todo != 0)) { // warp-uniform (block-uniform when synced)
+    while (todo != 0) { // warp-uniform
         int ul[GRP], n = 0;
 #pragma unroll
         for (int j = 0; j < GRP; ++j) {
@@ -308,7 +298,7 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
         for (int jj = 0; jj < n; ++jj) {
             const int uj = sel4(ul, jj);
             const int assoc = __shfl_sync(FULL, (int)(s_mine >= 0), uj);
-            channel_row(A, e, uj, assoc != 0, frame, episode, sm[wib][jj]);
+            channel_row(A, key, e, uj, assoc != 0, frame, episode, sm[wib][jj]);
         }
         __syncwarp();
 #pragma unroll 1
@@ -331,7 +321,7 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
         }
     }
 
-    PHASE_SYNC();
+
     // ---- phase 3: throughput, arrivals, closed-form buffer arithmetic - one UE per lane -------
     const double thr = floor(sum_t / up.pkt_bits);   // ues.py:108-116
     const double inc = floor(traffic / up.pkt_bits); // ues.py:199
@@ -349,39 +339,69 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
     const int a_left = kept - min(kept, thr_i - sent_old);
     const int sent = sent_old + (kept - a_left);
     const int rem = total + kept - sent;
-    int path = ROW_EMPTY, live = a_left != 0, slots = live; // live extent after / slots touched by the step
-    if (ue_lane && tot_prev != 0) {
-        path = (sent_old == total) ? ROW_ZERO_FILL : ROW_STREAM;
-        slots = (sent_old == total) ? live_prev : min(live_prev + 1, up.depth);
-    }
 
-    // ---- phase 4: the rows -------------------------------------------------------------------
-    if (ue_lane && tot_prev == 0 && a_left != 0) row[0] = a_left; // empty row: only slot 0 changes
-    long long wsum = 0;
-    uint32_t zf = __ballot_sync(FULL, path == ROW_ZERO_FILL);
-    uint32_t stm = __ballot_sync(FULL, path == ROW_STREAM);
-    while (zf) {
-        const int u = __ffs(zf) - 1;
-        zf &= zf - 1;
-        buffer_row_zero_fill(st.buf + ((size_t)e * U + u) * st.row_stride, __shfl_sync(FULL, slots, u),
-                             __shfl_sync(FULL, a_left, u));
-    }
-    if (stm) { // the first group of the first streamed row; each row then prefetches its successor's
-        const int u = __ffs(stm) - 1, ext = __shfl_sync(FULL, slots, u);
-        prefetch_row_group(st.buf + ((size_t)e * U + u) * st.row_stride, ext, row_oldest_group(ext));
-    }
-    while (stm) {
-        const int u = __ffs(stm) - 1;
-        stm &= stm - 1;
-        if (stm) {
-            const int un = __ffs(stm) - 1, ext = __shfl_sync(FULL, slots, un);
-            prefetch_row_group(st.buf + ((size_t)e * U + un) * st.row_stride, ext, row_oldest_group(ext));
+    // ---- phase 4: the ring rows (buffer.py:53-104) --------------------------------------------
+    int path = ROW_NONE, live = a_left != 0;
+    int acc = (live_prev == up.depth) + min(RING_LOOK, a_old); // 4-byte slot accesses (reads so far)
+    long long wdec = 0;
+    int want = sent_old;
+    int a_next = a_old; // first age the warp has to continue from (ROW_WARP)
+    if (ue_lane && total > 0) {
+        if (sent_old == total) { // all older packets leave: ages [1, a_old] become empty
+            path = ROW_CLEAR;
+            if (a_old <= RING_LOOK) {
+#pragma unroll
+                for (int k = 0; k < RING_LOOK; ++k)
+                    if (look[k] != 0) { const int q = p_old + k; row[q >= up.depth ? q - up.depth : q] = 0; ++acc; }
+            }
+        } else { // the oldest `sent_old` packets leave; some older packet stays
+            path = ROW_LANE;
+            live = 0;
+#pragma unroll
+            for (int k = 0; k < RING_LOOK; ++k) {
+                const int a = a_old - k;
+                if (live == 0 && a >= 1) {
+                    const int n = look[k], take = min(n, want);
+                    if (take) {
+                        const int q = p_old + k;
+                        row[q >= up.depth ? q - up.depth : q] = n - take;
+                        wdec += (long long)a * take;
+                        want -= take;
+                        ++acc;
+                    }
+                    if (n - take > 0) live = a + 1;
+                    a_next = a - 1;
+                }
+            }
+            if (live == 0) {
+                if (want > 0 && a_next >= 1) path = ROW_WARP;
+                else live = max(a_next, 0) + 1; // ages above a_next are empty
+            }
         }
-        const long long w = buffer_row_stream(st.buf + ((size_t)e * U + u) * st.row_stride,
-                                              __shfl_sync(FULL, slots, u), __shfl_sync(FULL, thr_i, u),
-                                              __shfl_sync(FULL, a_left, u));
-        if (lane == u) { wsum = w & ((1LL << ROW_WSUM_BITS) - 1); live = (int)(w >> ROW_WSUM_BITS); }
     }
+    if (ue_lane && (a_left != 0 || expired != 0)) { row[head] = a_left; ++acc; }
+    uint32_t clr = __ballot_sync(FULL, path == ROW_CLEAR && a_old > RING_LOOK);
+    uint32_t wrp = __ballot_sync(FULL, path == ROW_WARP);
+    while (clr) {
+        const int u = __ffs(clr) - 1;
+        clr &= clr - 1;
+        const int ao = __shfl_sync(FULL, a_old, u);
+        ring_clear_warp(st.buf + ((size_t)e * U + u) * st.row_stride, __shfl_sync(FULL, up.depth, u),
+                        __shfl_sync(FULL, head, u), ao);
+        if (lane == u) acc += ao;
+    }
+    while (wrp) {
+        const int u = __ffs(wrp) - 1;
+        wrp &= wrp - 1;
+        int lv = 0, ac = 0;
+        const long long w = ring_drain_warp(st.buf + ((size_t)e * U + u) * st.row_stride, __shfl_sync(FULL, up.depth, u),
+                                            __shfl_sync(FULL, head, u), __shfl_sync(FULL, a_next, u),
+                                            __shfl_sync(FULL, want, u), lv, ac);
+        if (lane == u) { wdec += w; live = lv; acc += ac; }
+    }
+    // sum(age * packets) after the step: every remaining packet one step older, the drained ones gone
+    const long long wsum = (rem == 0 || path == ROW_CLEAR || path == ROW_NONE)
+                               ? 0 : wsum_prev + (long long)tot_prev - (long long)up.depth * expired - wdec;
 
     // ---- phase 5: occupancy, mean delay, window push, record stores ---------------------------
     const double occ = (double)rem / (double)up.max_pkts;               // buffer.py:106-114
@@ -391,11 +411,11 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
     const bool occ1z = isclose0(rec_d0.x); // win[1].occ of the new window
     if (ue_lane) {
         *reinterpret_cast<int4*>(st.ue_i + eu * UI_N) = make_int4(rem, sum_sent, sum_drop, sent);
-        *reinterpret_cast<int4*>(st.ue_i + eu * UI_N + 4) = make_int4(dropped, (int)inc, occ1z ? 1 : 0, ROW_WORD(path, live, slots));
+        *reinterpret_cast<int4*>(st.ue_i + eu * UI_N + 4) = make_int4(dropped, (int)inc, occ1z ? 1 : 0, ROW_WORD(path, live, min(acc, 0xffff)));
         *reinterpret_cast<double2*>(st.ue_d + eu * UD_N) = make_double2(occ, lat);
         *reinterpret_cast<double2*>(st.ue_d + eu * UD_N + 2) = make_double2(sebar, thr);
         st.ring[eu * W + p] = make_int2(sent, dropped);
-        if (FULL_STEP) st.rb[eu] = make_short2((short)rb_s, (short)rb_c);
+        st.wsum[eu] = wsum;
         if (A.raw.pkt_incoming) A.raw.pkt_incoming[eu] = inc;
         if (A.raw.pkt_throughputs) A.raw.pkt_throughputs[eu] = thr;
         if (A.raw.sent) A.raw.sent[eu] = sent;
@@ -404,21 +424,6 @@ __device__ __forceinline__ void env_step_body(const StepArgs& A, double (*sm)[GR
         if (A.raw.lat) A.raw.lat[eu] = lat;
         if (A.raw.traffic_used) A.raw.traffic_used[eu] = traffic;
     }
-
-    PHASE_SYNC();
-    if (!FULL_STEP) return;
-    // ---- phase 6: observation, reward, metrics, done, rollover (comm_env.py:339-373) ----------
-    UeFrame f;
-    f.occ = occ; f.lat = lat; f.sebar = sebar; f.sent = sent; f.sum_sent = sum_sent; f.sum_drop = sum_drop;
-    f.rb_count = rb_c; f.occ1z = occ1z;
-    __syncwarp();
-    env_tail_core(A, e, sc, f, dropped, (int)inc, win_len, head, step, sm[wib][0], FUSED_SYNC >= 2);
-}
-
-__global__ void __launch_bounds__(FUSED_WARPS * 32, FUSED_MINB) k_env_step(const __grid_constant__ StepArgs A)
-{
-    __shared__ __align__(16) double sm[FUSED_WARPS][GRP][136];
-    env_step_body<true, true>(A, sm);
 }
 
 #ifndef UE_ENV_MINB
@@ -427,11 +432,11 @@ __global__ void __launch_bounds__(FUSED_WARPS * 32, FUSED_MINB) k_env_step(const
 __global__ void __launch_bounds__(FUSED_WARPS * 32, UE_ENV_MINB) k_ue_env(const __grid_constant__ StepArgs A)
 {
     __shared__ __align__(16) double sm[FUSED_WARPS][GRP][136];
-    env_step_body<false, false>(A, sm);
+    ue_env_body<false>(A, sm);
 }
 // same kernel with the optional per-RB SE output (irs_raw_outputs.se_used; tests and trace dumps)
 __global__ void __launch_bounds__(FUSED_WARPS * 32, UE_ENV_MINB) k_ue_env_raw(const __grid_constant__ StepArgs A)
 {
     __shared__ __align__(16) double sm[FUSED_WARPS][GRP][136];
-    env_step_body<false, true>(A, sm);
+    ue_env_body<true>(A, sm);
 }

@@ -13,7 +13,7 @@
 #pragma once
 #include "irs_common.cuh"
 
-enum { K_SE = 0, K_TRAFFIC = 1, K_MU = 2, K_POLICY = 3, K_SCEN = 4 };
+enum { K_SE = 0, K_TRAFFIC = 1, K_MU = 2, K_POLICY = 3, K_SCEN = 4, K_PERM = 5 };
 
 __device__ __noinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1)
 {
@@ -31,6 +31,40 @@ __device__ __forceinline__ uint4 rng_quad(uint64_t seed, int kind, int ue, int q
     const uint4 c = make_uint4((uint32_t)q | ((uint32_t)kind << 16) | ((uint32_t)ue << 24), (uint32_t)frame,
                                (uint32_t)episode, (uint32_t)gid);
     return philox4x32_10(c, (uint32_t)seed, (uint32_t)(seed >> 32));
+}
+
+// enable_random_episodes (comm_env.py:219-226, 434-444): element `pos` of a pseudo-random permutation of [0, n),
+// without a table: a 4-round balanced Feistel network over the next even power of two >= n, cycle-walked back into
+// [0, n) (a bijection, so every episode of the range is played once per cycle, like np_random.permutation + cycle).
+// Round keys: one Philox quad of (seed, global env id, permutation number).
+__host__ __device__ __forceinline__ uint32_t mix32(uint32_t x)
+{
+    x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+    return x;
+}
+__host__ __device__ __forceinline__ uint32_t feistel_perm(uint32_t i, uint32_t n, uint32_t k0, uint32_t k1, uint32_t k2, uint32_t k3)
+{
+    if (n <= 1) return 0;
+    int bits = 1;
+    while ((1u << bits) < n) ++bits;
+    bits += bits & 1;
+    const int half = bits >> 1;
+    const uint32_t mask = (1u << half) - 1;
+    uint32_t x = i;
+    do {
+        uint32_t l = x >> half, r = x & mask, t;
+        t = l ^ (mix32(r ^ k0) & mask); l = r; r = t;
+        t = l ^ (mix32(r ^ k1) & mask); l = r; r = t;
+        t = l ^ (mix32(r ^ k2) & mask); l = r; r = t;
+        t = l ^ (mix32(r ^ k3) & mask); l = r; r = t;
+        x = (l << half) | r;
+    } while (x >= n);
+    return x;
+}
+__device__ __noinline__ int shuffled_episode(uint64_t seed, int gid, int gen, int base, int n, int pos)
+{
+    const uint4 k = rng_quad(seed, K_PERM, 0, 0, gen, 0, gid);
+    return base + (int)feistel_perm((uint32_t)pos, (uint32_t)n, k.x, k.y, k.z, k.w);
 }
 
 // Where word w of SE quad q lands in the 135-RB row.  Quads 0..31 are laid out so that the two

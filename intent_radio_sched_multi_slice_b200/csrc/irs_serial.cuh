@@ -121,7 +121,7 @@ __global__ void __launch_bounds__(SERIAL_THREADS) k_action_t(const __grid_consta
         const int step = st.step[e], episode = st.episode[e];
 #pragma unroll
         for (int q = 0; q < 3; ++q) {
-            const uint4 v = rng_quad(cfg.seed, K_POLICY, 0, q, step + 1, episode, gid);
+            const uint4 v = rng_quad(env_key(cfg.seed, st.visit[e]), K_POLICY, 0, q, step + 1, episode, gid);
             w[4 * q] = v.x; w[4 * q + 1] = v.y; w[4 * q + 2] = v.z; w[4 * q + 3] = v.w;
         }
 #pragma unroll

@@ -21,6 +21,8 @@ _VIEWS = {  # name -> (torch dtype, trailing shape)
     "ring": (torch.int32, (U, capi.WINDOW, 2)), "rb": (torch.int16, (U, 2)),
     "step": (torch.int32, ()), "episode": (torch.int32, ()), "scen": (torch.int32, ()),
     "win_len": (torch.int32, ()), "win_head": (torch.int32, ()), "err": (torch.int32, ()),
+    "visit": (torch.int32, ()), "ep_pos": (torch.int32, ()), "ep_gen": (torch.int32, ()), "ep_base": (torch.int32, ()),
+    "wsum": (torch.int64, (U,)),
     "sorted": (torch.int8, (S,)), "acc": (torch.float64, (capi.NUM_METRICS,)),
     "in_a0": (torch.float64, (S,)), "in_intra": (torch.int32, (S,)),
     "out_obs0": (torch.float64, (capi.OBS0,)), "out_obsi": (torch.float64, (S, capi.OBSI)),
@@ -45,7 +47,7 @@ class BatchEngine:
     def __init__(self, bank: ScenarioBank, num_envs: int, *, device="cuda:0", depth_cap=None,
                  channel_mode=2, traffic_mode=1, sort_slices=1, fixed_intra=-1, policy=0, assoc_mode=0,
                  scen_mod=200, scen_div=100, max_steps=1000, max_episodes=10000, initial_episode=0,
-                 auto_reset=0, env_id_base=0, seed=10, bandwidth=1e8, surface=0):
+                 auto_reset=0, env_id_base=0, seed=10, bandwidth=1e8, surface=0, random_episodes=0):
         if not torch.cuda.is_available():
             raise RuntimeError("intent_radio_sched_multi_slice_b200 needs a CUDA device (there is no CPU path)")
         self.lib = capi.load()
@@ -57,7 +59,7 @@ class BatchEngine:
             depth_cap = max(bank.max_depth(), 101)  # 101: default depth of unassociated UEs (comm_env.py:184-198)
         self.cfg = capi.Config(self.E, int(depth_cap), channel_mode, traffic_mode, sort_slices, fixed_intra, policy,
                                assoc_mode, scen_mod, scen_div, len(self.bank_array), max_steps, max_episodes,
-                               initial_episode, auto_reset, env_id_base, surface, 0, seed, bandwidth)
+                               initial_episode, auto_reset, env_id_base, surface, int(random_episodes), seed, bandwidth)
         self.h = C.c_void_p()
         rc = self.lib.irs_create(C.byref(self.cfg), self.cdf.shape[0], C.byref(self.h))
         if rc:
@@ -79,7 +81,7 @@ class BatchEngine:
         for k, name in enumerate(capi.UD_FIELDS):
             self.v[name] = self.v["ue_d"][:, :, k]
         self.v["rb_start"], self.v["rb_count"] = self.v["rb"][:, :, 0], self.v["rb"][:, :, 1]
-        self.buf = self._view("buf", torch.int32, (U, self.row_stride))
+        self.ring_rows = self._view("buf", torch.int32, (U, self.row_stride))  # physical ring rows (slot = (step - age) mod depth)
         self.metrics_total = self._view1("metrics_total", torch.float64, capi.NUM_METRICS)
         self._raw = None
         self._raw_struct = None
@@ -117,6 +119,33 @@ class BatchEngine:
         else:
             t = torch.from_numpy(np.ascontiguousarray(x)).to(device=self.device, dtype=dtype)
         return t
+
+    def buffers(self, out=None):
+        """Buffer.buffer of every UE as the reference indexes it (buffer.py:47, index = age): int32
+        [E, 25, row_stride], de-rotated from the ring rows by irs_read_buffers."""
+        if out is None:
+            out = torch.empty((self.E, U, self.row_stride), dtype=torch.int32, device=self.device)
+        with torch.cuda.device(self.device):
+            capi.check(self.h, self.lib.irs_read_buffers(self.h, out.data_ptr(), self._stream()))
+        return out
+
+    @property
+    def buf(self):
+        return self.buffers()
+
+    def set_episode_order(self, order):
+        """enable_random_episodes with a given order: int32 [E, n] (irs_set_episode_order); None = built-in."""
+        if order is None:
+            self._order = None
+            with torch.cuda.device(self.device):
+                capi.check(self.h, self.lib.irs_set_episode_order(self.h, None, 0, self._stream()))
+            return
+        t = self._dev(order, torch.int32)
+        if t.dim() != 2 or t.shape[0] != self.E:
+            raise ValueError("order must be int32 [num_envs, n]")
+        self._order = t
+        with torch.cuda.device(self.device):
+            capi.check(self.h, self.lib.irs_set_episode_order(self.h, t.data_ptr(), t.shape[1], self._stream()))
 
     # -- channel_mode 3: device-resident SE trace (channels/quadriga.py) ------------------------
     def set_se_trace(self, se_bank: torch.Tensor):

@@ -55,7 +55,8 @@ typedef struct {
     int32_t scen_mod, scen_div, n_scen;
     int32_t max_steps, max_episodes, initial_episode;
     int32_t auto_reset, env_id_base;
-    int32_t surface, pad0;            /* 0 IBSched family, 1 SchedTWC, 2 SchedColORAN (double window push) */
+    int32_t surface;                  /* 0 IBSched family, 1 SchedTWC, 2 SchedColORAN (double window push) */
+    int32_t random_episodes;          /* comm_env.py:219-226, 434-444 enable_random_episodes */
     uint64_t seed;
     double bandwidth;
 } orc_config;
@@ -68,6 +69,8 @@ typedef struct {
 
 typedef struct {
     int32_t step, episode, scen, win_len;
+    int32_t visit;                    /* resets seen: part of the native generators' key */
+    int32_t ep_pos, ep_gen, ep_base;  /* random_episodes: position, permutations drawn, first episode of the range */
     orc_frame win[W]; /* win[0] newest: collections.deque(maxlen=10).appendleft */
     int32_t sorted_slices[S];
     /* last formatted obs, kept for calculate_reward (ib_sched.py:202) */
@@ -84,6 +87,8 @@ typedef struct {
     orc_scenario *own_bank;    /* assoc_mode 2: templates + two generated rows per env */
     const double *se_bank;     /* channel_mode 3: [bank_eps][bank_steps][U][R] (channels/quadriga.py) */
     int32_t bank_eps, bank_steps;
+    const int32_t *ep_order;   /* random_episodes with a given order: [E][ep_order_n] */
+    int32_t ep_order_n;
 } orc_handle;
 
 /* ------------------------------------------------------------------------------------
@@ -106,13 +111,44 @@ static void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1)
         k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
     }
 }
-enum { K_SE = 0, K_TRAFFIC = 1, K_MU = 2, K_POLICY = 3, K_SCEN = 4 };
-static void rng_quad(const orc_config *cfg, int kind, int ue, int q, int frame, int episode, int gid,
-                     uint32_t out[4])
+enum { K_SE = 0, K_TRAFFIC = 1, K_MU = 2, K_POLICY = 3, K_SCEN = 4, K_PERM = 5 };
+/* key = the seed with the env's reset count in the upper word (csrc/irs_common.cuh env_key): an episode number that
+ * is played again draws fresh noise, like the reference's np_random stream that runs on across episodes */
+static uint64_t env_key(const orc_config *cfg, int visit) { return cfg->seed + ((uint64_t)(uint32_t)visit << 32); }
+static void rng_quad(uint64_t key, int kind, int ue, int q, int frame, int episode, int gid, uint32_t out[4])
 {
     out[0] = (uint32_t)q | ((uint32_t)kind << 16) | ((uint32_t)ue << 24);
     out[1] = (uint32_t)frame; out[2] = (uint32_t)episode; out[3] = (uint32_t)gid;
-    philox4x32_10(out, (uint32_t)cfg->seed, (uint32_t)(cfg->seed >> 32));
+    philox4x32_10(out, (uint32_t)key, (uint32_t)(key >> 32));
+}
+/* enable_random_episodes (comm_env.py:219-226, 434-444) without a table: element `pos` of a pseudo-random permutation
+ * of [0, n) - 4-round balanced Feistel network over the next even power of two, cycle-walked into [0, n)
+ * (csrc/irs_rng.cuh feistel_perm) */
+static uint32_t mix32(uint32_t x)
+{
+    x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+    return x;
+}
+static uint32_t feistel_perm(uint32_t i, uint32_t n, const uint32_t k[4])
+{
+    if (n <= 1) return 0;
+    int bits = 1;
+    while ((1u << bits) < n) ++bits;
+    bits += bits & 1;
+    int half = bits >> 1;
+    uint32_t mask = (1u << half) - 1, x = i;
+    do {
+        uint32_t l = x >> half, r = x & mask, t;
+        for (int j = 0; j < 4; ++j) { t = l ^ (mix32(r ^ k[j]) & mask); l = r; r = t; }
+        x = (l << half) | r;
+    } while (x >= n);
+    return x;
+}
+static int shuffled_episode(const orc_config *cfg, int gid, int gen, int base, int n, int pos)
+{
+    uint32_t k[4];
+    rng_quad(cfg->seed, K_PERM, 0, 0, gen, 0, gid, k);
+    return base + (int)feistel_perm((uint32_t)pos, (uint32_t)n, k);
 }
 /* Box-Muller in binary32 with explicit fused multiply-adds only where written, so the
  * CUDA path (fmaf/__fmul_rn/...) produces the same bits. */
@@ -153,10 +189,10 @@ static void normal_pair(uint32_t wa, uint32_t wb, float *z0, float *z1)
     *z0 = r * a; *z1 = r * b;
 }
 /* channels/mimic_quadriga.py:37-41: ues_mean_se = abs(N(10, 7.5)) per UE per episode */
-static double native_mu(const orc_config *cfg, int ue, int episode, int gid)
+static double native_mu(uint64_t key, int ue, int episode, int gid)
 {
     uint32_t w[4]; float z0, z1;
-    rng_quad(cfg, K_MU, ue, 0, 0, episode, gid, w);
+    rng_quad(key, K_MU, ue, 0, 0, episode, gid, w);
     normal_pair(w[0], w[1], &z0, &z1);
     return fabs(fma(7.5, (double)z0, 10.0));
 }
@@ -167,12 +203,12 @@ static int se_index(int q, int w)
     return q < 32 ? ((q >> 4) << 6) + ((q >> 1) & 7) + 8 * (4 * (q & 1) + w) : 4 * q + w;
 }
 /* channels/mimic_quadriga.py:49-56: SE[u,r] = abs(N(mu_u, 1.5)) */
-static void native_se_row(const orc_config *cfg, int ue, int frame, int episode, int gid, double *se)
+static void native_se_row(uint64_t key, int ue, int frame, int episode, int gid, double *se)
 {
-    double mu = native_mu(cfg, ue, episode, gid);
+    double mu = native_mu(key, ue, episode, gid);
     for (int q = 0; q < (R + 3) / 4; ++q) {
         uint32_t w[4]; float z[4];
-        rng_quad(cfg, K_SE, ue, q, frame, episode, gid, w);
+        rng_quad(key, K_SE, ue, q, frame, episode, gid, w);
         normal_pair(w[0], w[1], &z[0], &z[1]);
         normal_pair(w[2], w[3], &z[2], &z[3]);
         for (int j = 0; j < 4; ++j)
@@ -180,10 +216,10 @@ static void native_se_row(const orc_config *cfg, int ue, int frame, int episode,
     }
 }
 /* traffics/mult_slice.py:28-31: Poisson(lambda) * 1e6 bits, by table inversion */
-static double native_traffic(const orc_handle *h, int ue, int lam_idx, int frame, int episode, int gid)
+static double native_traffic(const orc_handle *h, uint64_t key, int ue, int lam_idx, int frame, int episode, int gid)
 {
     uint32_t w[4];
-    rng_quad(&h->cfg, K_TRAFFIC, ue, 0, frame, episode, gid, w);
+    rng_quad(key, K_TRAFFIC, ue, 0, frame, episode, gid, w);
     double u = ((double)(w[0] >> 5) * 67108864.0 + (double)(w[1] >> 6)) * (1.0 / 9007199254740992.0);
     const double *cdf = h->poisson_cdf + (size_t)lam_idx * POISSON_K;
     int k = 0;
@@ -525,7 +561,7 @@ static void policy_mapf(const orc_env *env, const orc_scenario *sc, double *a0)
 static void policy_random(const orc_handle *h, const orc_env *env, int gid, double *a0, int32_t *intra)
 {
     uint32_t w[12];
-    for (int q = 0; q < 3; ++q) rng_quad(&h->cfg, K_POLICY, 0, q, env->step + 1, env->episode, gid, w + 4 * q);
+    for (int q = 0; q < 3; ++q) rng_quad(env_key(&h->cfg, env->visit), K_POLICY, 0, q, env->step + 1, env->episode, gid, w + 4 * q);
     for (int i = 0; i < S; ++i) a0[i] = (double)w[i] * (1.0 / 2147483648.0) - 1.0;
     for (int i = 0; i < S; ++i) intra[i] = (int32_t)(((uint64_t)w[5 + i] * 3u) >> 32);
 }
@@ -860,17 +896,17 @@ static void channel_frame(const orc_handle *h, int e, const orc_env *env, int fr
     } else {
         for (int u = 0; u < U; ++u) {
             if (sc->ue_slice[u] < 0) { for (int r = 0; r < R; ++r) se[u * R + r] = 0.0; continue; }
-            native_se_row(&h->cfg, u, frame, env->episode, h->cfg.env_id_base + e, se + u * R);
+            native_se_row(env_key(&h->cfg, env->visit), u, frame, env->episode, h->cfg.env_id_base + e, se + u * R);
         }
     }
 }
 /* assoc_mode 2: MultSliceAssociation generator mode (associations/mult_slice.py:359-416, 454-466) with the
  * counter-based generator: 3..5 slices, slots and types without replacement (partial Fisher-Yates), UEs per slice
  * uniform in the type's [min, max] (template sl[0].pad .. sl[0].n_ues), random UE ids. */
-typedef struct { const orc_config *cfg; int episode, gid, i; uint32_t cur[4]; } scen_words;
+typedef struct { uint64_t key; int episode, gid, i; uint32_t cur[4]; } scen_words;
 static uint32_t sw_next(scen_words *g)
 {
-    if ((g->i & 3) == 0) rng_quad(g->cfg, K_SCEN, 0, g->i >> 2, 0, g->episode, g->gid, g->cur);
+    if ((g->i & 3) == 0) rng_quad(g->key, K_SCEN, 0, g->i >> 2, 0, g->episode, g->gid, g->cur);
     return g->cur[g->i++ & 3];
 }
 static int sw_below(scen_words *g, int n) { return (int)(((uint64_t)sw_next(g) * (uint32_t)n) >> 32); }
@@ -878,7 +914,7 @@ static void generate_scenario_row(const orc_handle *h, int e, int ep, orc_scenar
 {
     const orc_scenario *types = h->bank;
     const int T = h->cfg.n_scen;
-    scen_words g = {&h->cfg, ep, h->cfg.env_id_base + e, 0, {0, 0, 0, 0}};
+    scen_words g = {env_key(&h->cfg, h->envs[e].visit), ep, h->cfg.env_id_base + e, 0, {0, 0, 0, 0}};
     int slots[S], tys[32], counts[S], ues[U];
     int k = 3 + sw_below(&g, S - 3 + 1);
     for (int j = 0; j < S; ++j) slots[j] = j;
@@ -910,15 +946,28 @@ static int reset_one(orc_handle *h, int e, int initial_episode, const double *se
     orc_env *env = &h->envs[e];
     const orc_config *c = &h->cfg;
     int init = initial_episode != -1 ? initial_episode : c->initial_episode;
-    if ((env->step == 0 && env->episode == 0) ||
+    if (c->random_episodes) {                                  /* :434-444 */
+        int moved = 0;
+        if (initial_episode != -1) { env->ep_base = initial_episode; env->ep_gen += 1; env->ep_pos = 0; moved = 1; }
+        if (env->step == c->max_steps) { env->ep_pos += 1; moved = 1; }  /* next(self.random_episodes_gen) */
+        int n = h->ep_order ? h->ep_order_n : c->max_episodes - env->ep_base;
+        if (n <= 0) return -2;
+        env->ep_pos %= n;                                      /* itertools.cycle */
+        if (moved)
+            env->episode = h->ep_order ? h->ep_order[(size_t)e * n + env->ep_pos]
+                                       : shuffled_episode(c, c->env_id_base + e, env->ep_gen, env->ep_base, n, env->ep_pos);
+    }
+    else if ((env->step == 0 && env->episode == 0) ||
         (env->step == c->max_steps && env->episode == c->max_episodes - 1) || initial_episode != -1)
         env->episode = init;                                   /* :416-421 */
     else if (env->step == 0 && env->episode <= c->max_episodes - 1) { /* :422-425 */ }
     else if (env->episode < c->max_episodes - 1) env->episode += 1;   /* :426-427 */
     else return -2;                                            /* :428-433 */
     env->step = 0;
+    env->visit += 1;
     if (c->assoc_mode == 2) {
-        env->scen = c->n_scen + 2 * e + (env->episode & 1);
+        int row0 = c->n_scen + 2 * e;                          /* the env's other private row */
+        env->scen = env->scen == row0 ? row0 + 1 : row0;
         generate_scenario_row(h, e, env->episode, &h->own_bank[env->scen]);
     } else {
         env->scen = scen_of_episode(c, env->episode);
@@ -963,7 +1012,7 @@ static int step_one(orc_handle *h, int e, const double *a0_in, const int32_t *in
         int s = sc->ue_slice[u];
         if (c->traffic_mode == 0) traffic[u] = traffic_in[(size_t)e * U + u];
         else traffic[u] = (s >= 0 && (sc->sl[s].flags & F_REQ))
-                 ? native_traffic(h, u, sc->sl[s].lam_idx, frame, env->episode, gid) : 0.0;
+                 ? native_traffic(h, env_key(c, env->visit), u, sc->sl[s].lam_idx, frame, env->episode, gid) : 0.0;
     }
     orc_frame fr; orc_ue_aux aux;
     ues_step(h, e, sc, se, traffic, rb_start, rb_count, &fr, &aux); /* :320-326 */
@@ -1013,6 +1062,11 @@ orc_handle *orc_create(const orc_config *cfg, const orc_scenario *bank, const do
     }
     for (int e = 0; e < cfg->num_envs; ++e) {
         h->envs[e].episode = cfg->initial_episode;
+        if (cfg->random_episodes) {                            /* comm_env.py:219-226 */
+            h->envs[e].ep_base = cfg->initial_episode;
+            int n = cfg->max_episodes - cfg->initial_episode;
+            if (n > 0) h->envs[e].episode = shuffled_episode(cfg, cfg->env_id_base + e, 0, cfg->initial_episode, n, 0);
+        }
         for (int s = 0; s < S; ++s) h->envs[e].sorted_slices[s] = s; /* ib_sched.py:58 */
     }
     return h;
@@ -1025,6 +1079,14 @@ int orc_max_threads(void) { return omp_get_max_threads(); }
 void orc_set_threads(int n) { (void)n; }
 int orc_max_threads(void) { return 1; }
 #endif
+/* random_episodes with a given order [E][n]; the envs move to the table's entry at their position (irs_set_episode_order) */
+void orc_set_episode_order(orc_handle *h, const int32_t *order, int32_t n)
+{
+    h->ep_order = order; h->ep_order_n = order ? n : 0;
+    if (order)
+        for (int e = 0; e < h->cfg.num_envs; ++e)
+            h->envs[e].episode = order[(size_t)e * n + h->envs[e].ep_pos % n];
+}
 void orc_set_se_trace(orc_handle *h, const double *bank, int32_t n_eps, int32_t n_steps)
 {
     h->se_bank = bank; h->bank_eps = n_eps; h->bank_steps = n_steps;

@@ -31,7 +31,7 @@ class Config(C.Structure):
     _fields_ = [(n, C.c_int32) for n in (
         "num_envs", "depth_cap", "channel_mode", "traffic_mode", "sort_slices", "fixed_intra", "policy",
         "assoc_mode", "scen_mod", "scen_div", "n_scen", "max_steps", "max_episodes", "initial_episode",
-        "auto_reset", "env_id_base", "surface", "pad0")] + [("seed", C.c_uint64), ("bandwidth", C.c_double)]
+        "auto_reset", "env_id_base", "surface", "random_episodes")] + [("seed", C.c_uint64), ("bandwidth", C.c_double)]
 
 
 _IO_FIELDS = ["pkt_incoming", "pkt_throughputs", "sent", "dropped", "occ", "lat", "rb_start", "rb_count",
@@ -56,6 +56,7 @@ def lib():
         _lib.orc_destroy.argtypes = [C.c_void_p]
         _lib.orc_get_scenario.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         _lib.orc_set_se_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32]
+        _lib.orc_set_episode_order.argtypes = [C.c_void_p, C.c_void_p, C.c_int32]
         _lib.orc_power_to_se.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_double, C.c_double]
         _lib.orc_reset.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.POINTER(IO)]
         _lib.orc_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(IO)]
@@ -133,7 +134,7 @@ class OracleEnv:
     def __init__(self, bank_array, poisson_cdf, num_envs=1, depth_cap=None, channel_mode=0, traffic_mode=0,
                  sort_slices=1, fixed_intra=-1, policy=0, assoc_mode=0, scen_mod=200, scen_div=100,
                  max_steps=1000, max_episodes=10000, initial_episode=0, auto_reset=0, env_id_base=0, seed=10, surface=0,
-                 bandwidth=1e8):
+                 bandwidth=1e8, random_episodes=0):
         self.bank = np.ascontiguousarray(bank_array)
         assert self.bank.dtype.itemsize == 432
         self.cdf = np.ascontiguousarray(poisson_cdf, np.float64)
@@ -143,7 +144,7 @@ class OracleEnv:
         self.depth_cap = depth_cap
         self.cfg = Config(num_envs, depth_cap, channel_mode, traffic_mode, sort_slices, fixed_intra, policy,
                           assoc_mode, scen_mod, scen_div, len(self.bank), max_steps, max_episodes,
-                          initial_episode, auto_reset, env_id_base, surface, 0, seed, bandwidth)
+                          initial_episode, auto_reset, env_id_base, surface, int(random_episodes), seed, bandwidth)
         self.h = lib().orc_create(C.byref(self.cfg), _ptr(self.bank), _ptr(self.cdf))
         E = num_envs
         self.out = {
@@ -164,6 +165,16 @@ class OracleEnv:
         self._se_bank = np.ascontiguousarray(se_bank, np.float64)
         assert self._se_bank.ndim == 4 and self._se_bank.shape[2:] == (U, R)
         lib().orc_set_se_trace(self.h, _ptr(self._se_bank), self._se_bank.shape[0], self._se_bank.shape[1])
+
+    def set_episode_order(self, order):
+        """random_episodes with a given order: int32 [E, n] (kept alive by this object); None = built-in permutation."""
+        if order is None:
+            self._order = None
+            lib().orc_set_episode_order(self.h, None, 0)
+            return
+        self._order = np.ascontiguousarray(order, np.int32)
+        assert self._order.ndim == 2 and self._order.shape[0] == self.E
+        lib().orc_set_episode_order(self.h, _ptr(self._order), self._order.shape[1])
 
     def scenario_rows(self):
         """The scenario row every env is playing (432-byte records, dtype of the bank)."""

@@ -40,7 +40,7 @@ def test_struct_sizes_match_the_header():
 def _cfg(**kw):
     d = dict(num_envs=64, depth_cap=401, channel_mode=2, traffic_mode=1, sort_slices=1, fixed_intra=-1, policy=0,
              assoc_mode=0, scen_mod=200, scen_div=100, n_scen=200, max_steps=1000, max_episodes=10000,
-             initial_episode=0, auto_reset=0, env_id_base=0, surface=0, pad0=0, seed=10, bandwidth=1e8)
+             initial_episode=0, auto_reset=0, env_id_base=0, surface=0, random_episodes=0, seed=10, bandwidth=1e8)
     d.update(kw)
     return capi.Config(*[d[n] for n, _ in capi.Config._fields_])
 
@@ -64,7 +64,8 @@ def test_create_layout_destroy_without_gpu():
 
 
 @pytest.mark.parametrize("bad", [dict(num_envs=0), dict(channel_mode=4), dict(surface=3), dict(policy=9), dict(fixed_intra=3),
-                                 dict(bandwidth=0.0), dict(assoc_mode=1, scen_div=0)])
+                                 dict(bandwidth=0.0), dict(assoc_mode=1, scen_div=0), dict(depth_cap=16384),
+                                 dict(random_episodes=2)])
 def test_create_rejects_bad_config(bad):
     lib = capi.load()
     h = C.c_void_p()

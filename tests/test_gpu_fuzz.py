@@ -133,12 +133,3 @@ def test_rows_age_to_the_expiry_slot_like_oracle(depth, size):
     # not available on the GPU pool, so the bound is checked through the data)
     dep = np.array([[depth - (s if i else 0) for s in range(5) for _ in range(5)] for i in range(4)])[ie]
     assert (live <= dep).all() and not buf[np.arange(buf.shape[2])[None, None, :] >= dep[:, :, None]].any()
-
-
-@pytest.mark.parametrize("mode", ["0", "1"])
-def test_alternative_step_kernels_match_oracle(mode, monkeypatch):
-    """IRS_STEP_MODE=0 (the whole step fused in k_env_step) and 1 (k_ue_step, one warp per (env, UE) row) are kept
-    selectable next to the production split (mode 2): the same fuzzed scenarios and the same aging rows."""
-    monkeypatch.setenv("IRS_STEP_MODE", mode)
-    test_fuzzed_scenarios_match_oracle(0, "warp_per_env", monkeypatch)
-    test_rows_age_to_the_expiry_slot_like_oracle(140, 90_000)

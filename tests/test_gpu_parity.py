@@ -292,7 +292,7 @@ def test_config5_full_size_properties():
     oldest = torch.zeros(E, 25, dtype=torch.int32, device="cuda")
     for c0 in range(0, E, 8192):  # chunked: the mask of the whole state would be another 7 GB
         oldest[c0:c0 + 8192] = ((buf[c0:c0 + 8192] != 0).int() * idx).amax(2)
-    assert bool((oldest.long() <= live).all()) and bool((oldest.long() == live)[(word & 3) == 2].all())
+    assert bool((oldest.long() <= live).all())
     assert np.array_equal(buf[:n_orc].cpu().numpy()[:, :, :D], orc.buffers()[:, :, :D])
 
 
@@ -379,14 +379,13 @@ def test_full_size_properties(bank):
     in_buf = gpu.eng.buf.long().sum(2)
     assert bool((inc_total == sent_total + drop_total + in_buf).all())             # packet conservation
     assert bool((in_buf == gpu.eng.v["tot"].long()).all())
-    # live extent of every row (irs_common.cuh ROW_LIVE): exactly the oldest non-empty slot + 1 for a
-    # streamed row, an upper bound otherwise - the row kernels never look past it
+    # live extent of every row (irs_common.cuh ROW_LIVE): an upper bound of the oldest non-empty age + 1 - the
+    # row code never looks past it
     word = gpu.eng.v["path"].long()
     live = (word >> 2) & 0x3FFF
     idx = torch.arange(gpu.eng.buf.shape[2], device="cuda")
     oldest = ((gpu.eng.buf != 0).long() * (idx + 1)).max(2).values
     assert bool((oldest <= live).all())
-    assert bool((oldest == live)[(word & 3) == 2].all())
     # no RB is given to two UEs (comm_env.py:593-596): runs of one env do not overlap
     rs, rc = gpu.raw["rb_start"].long(), gpu.raw["rb_count"].long()
     cover = torch.zeros(E, 136, dtype=torch.int64, device="cuda")
