@@ -42,7 +42,7 @@ extern "C" {
 #define IRS_OBS0 50           /* agents/ib_sched.py:413-470: player_0 observations */
 #define IRS_OBSI 19           /* player_{s+1} observations */
 #define IRS_NUM_METRICS 16
-#define IRS_POISSON_K 256
+#define IRS_POISSON_K 512      /* Poisson CDF table length: lambda + 12 sqrt(lambda) + 10 <= 512, i.e. lambda <= 310 Mbit per step */
 
 typedef enum {
     IRS_OK = 0,
@@ -136,7 +136,7 @@ typedef struct {
     size_t sorted;           /* i8  [E][5] IBSched.sorted_slices */
     size_t acc;              /* f64 [E][16] episode-metric accumulators */
     size_t bank;             /* irs_scenario [n_scen] */
-    size_t cdf;              /* f64 [n_lambda][256] Poisson CDF tables */
+    size_t cdf;              /* f64 [n_lambda][IRS_POISSON_K] Poisson CDF tables */
     size_t in_a0;            /* f64 [E][5]  staging for irs_step_host */
     size_t in_intra;         /* i32 [E][5] */
     /* the env surface written by every step/reset */

@@ -31,7 +31,7 @@ __device__ __forceinline__ T sel4(const T (&a)[GRP], int j)
 }
 
 template <bool RAWSE>
-__device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP][136])
+__device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP][136], const float2* __restrict__ ntab)
 {
     const DevState& st = A.st;
     const irs_config& cfg = A.cfg;
@@ -97,35 +97,31 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
 #pragma unroll
             for (int j = 0; j < GRP; ++j)
                 if (todo) { ulp |= (uint32_t)(__ffs(todo) - 1) << (8 * j); ++n; todo &= todo - 1; }
-            // auxiliary pass: lane 6j+k serves UE j of the group - k < 4: a pair of the tail elements
-            // 128..134 (half of quad 32 / 33), k == 4: the per-episode mean, k == 5: the Poisson arrival
+            // auxiliary pass: lane 8j+k serves UE j of the group.  Lane 8j draws the tail quad (RBs 128..134),
+            // lane 8j+1 the per-episode mean, lane 8j+2 the Poisson arrival; then lane 8j+k turns half-word k
+            // of the tail quad into RB 128+k.
             {
-                const int j = lane / 6, k = lane - 6 * j;
+                const int j = lane >> 3, k = lane & 7;
                 const bool valid = j < n;
-                const int ue_j = (ulp >> (8 * (j & 3))) & 31;
-                const int kind = k < 4 ? K_SE : (k == 4 ? K_MU : K_TRAFFIC);
-                const int q = k < 2 ? 32 : (k < 4 ? 33 : 0);
-                const uint4 w = rng_quad(key, kind, ue_j, q, k == 4 ? 0 : frame, episode, gid);
-                const bool hi_pair = k < 4 && (k & 1);
-                float z0, z1;
-                normal_pair(hi_pair ? w.z : w.x, hi_pair ? w.w : w.y, z0, z1);
-                mu_l = fabs(__fma_rn(7.5, (double)z0, 10.0)); // meaningful on k == 4 (mimic_quadriga.py:37-41)
-                const double mu_aux = __shfl_sync(FULL, mu_l, (valid ? 6 * j : 0) + 4);
+                const int ue_j = (ulp >> (8 * j)) & 31;
+                const int kind = k == 1 ? K_MU : (k == 2 ? K_TRAFFIC : K_SE);
+                const uint4 w = rng_quad(key, kind, ue_j, k == 0 ? 16 : 0, k == 1 ? 0 : frame, episode, gid);
+                mu_l = fabs(__fma_rn(7.5, (double)normal_lo(w.x, ntab), 10.0)); // meaningful on k == 1 (mimic_quadriga.py:37-41)
+                const double mu_aux = __shfl_sync(FULL, mu_l, 8 * j + 1);
+                const uint32_t t0 = __shfl_sync(FULL, w.x, 8 * j), t1 = __shfl_sync(FULL, w.y, 8 * j);
+                const uint32_t t2 = __shfl_sync(FULL, w.z, 8 * j), t3 = __shfl_sync(FULL, w.w, 8 * j);
+                const uint32_t wk = (k & 4) ? ((k & 2) ? t3 : t2) : ((k & 2) ? t1 : t0); // word k >> 1 of the tail quad
+                const float z = (k & 1) ? normal_hi(wk, ntab) : normal_lo(wk, ntab);
                 const int rs_a = __shfl_sync(FULL, rb_s, ue_j), rc_a = __shfl_sync(FULL, rb_c, ue_j);
-                if (valid && k < 4) {
-                    const int t0 = 4 * (q - 32) + 2 * (k & 1); // tail index 0, 2, 4, 6 -> RB 128 + t0
-                    double2* tp = reinterpret_cast<double2*>(ws + 16 * j);
-                    const double x0 = fabs(__fma_rn(1.5, (double)z0, mu_aux));
-                    tp[t0] = make_double2(x0, (unsigned)(128 + t0 - rs_a) < (unsigned)rc_a ? A.bw_rb * x0 : 0.0);
-                    if (t0 + 1 < 7) {
-                        const double x1 = fabs(__fma_rn(1.5, (double)z1, mu_aux));
-                        tp[t0 + 1] = make_double2(x1, (unsigned)(129 + t0 - rs_a) < (unsigned)rc_a ? A.bw_rb * x1 : 0.0);
-                    }
+                if (valid && k < 7) {
+                    const double x = fabs(__fma_rn(1.5, (double)z, mu_aux));
+                    reinterpret_cast<double2*>(ws + 16 * j)[k] =
+                        make_double2(x, (unsigned)(128 + k - rs_a) < (unsigned)rc_a ? A.bw_rb * x : 0.0);
                 }
-                // Poisson arrival of UE j on lane 6j+5 (traffics/mult_slice.py:28-31)
+                // Poisson arrival of UE j on lane 8j+2 (traffics/mult_slice.py:28-31)
                 const int lam_j = __shfl_sync(FULL, lam_idx, ue_j);
                 const int ht_j = __shfl_sync(FULL, (int)has_traffic, ue_j);
-                if (valid && k == 5) {
+                if (valid && k == 2) {
                     int lo = 0;
                     if (ht_j) {
                         const double u01 = ((double)(w.x >> 5) * 67108864.0 + (double)(w.y >> 6)) * (1.0 / 9007199254740992.0);
@@ -140,35 +136,31 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
             }
             __syncwarp();
             // pair passes: lanes 0..15 serve UE ul[2p], lanes 16..31 UE ul[2p+1].  Lane m of a side
-            // generates SE quads 2m, 2m+1 = the 8 elements accumulator m & 7 of row half m >> 3
-            // visits (se_index), and adds them up in registers in NumPy's order: both 135-term
-            // sums (ues.py:108-116 throughput terms, np.mean(SE)) without a shared-memory row.
+            // generates SE quad m = the 8 elements accumulator m & 7 of row half m >> 3 visits
+            // (se_index), and adds them up in registers in NumPy's order: both 135-term sums
+            // (ues.py:108-116 throughput terms, np.mean(SE)) without a shared-memory row.
 #pragma unroll 1
             for (int pp = 0; 2 * pp < n; ++pp) {
                 const int side = lane >> 4;
                 const bool live = 2 * pp + side < n;      // odd n: side 1 of the last pass shadows side 0
                 const int jj = live ? 2 * pp + side : 2 * pp;
                 const int uj = (ulp >> (8 * jj)) & 31;
-                const double mu = __shfl_sync(FULL, mu_l, 6 * jj + 4);
+                const double mu = __shfl_sync(FULL, mu_l, 8 * jj + 1);
                 const int rs = __shfl_sync(FULL, rb_s, uj), rc = __shfl_sync(FULL, rb_c, uj);
                 const int l16 = lane & 15, base = ((l16 >> 3) << 6) + (l16 & 7);
                 const unsigned d0 = (unsigned)(base - rs);
                 double acc_se = 0.0, acc_t = 0.0;
                 double* se_out = (RAWSE && A.raw.se_used) ? A.raw.se_used + ((size_t)e * U + uj) * R : nullptr;
+                const uint4 wb = rng_quad(key, K_SE, uj, l16, frame, episode, gid);
+                const uint32_t ww[4] = {wb.x, wb.y, wb.z, wb.w};
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    const uint4 wb = rng_quad(key, K_SE, uj, 2 * l16 + h, frame, episode, gid);
-                    float y[4];
-                    normal_pair(wb.x, wb.y, y[0], y[1]);
-                    normal_pair(wb.z, wb.w, y[2], y[3]);
-#pragma unroll
-                    for (int w = 0; w < 4; ++w) {
-                        const double x = fabs(__fma_rn(1.5, (double)y[w], mu)); // channels/mimic_quadriga.py:49-56
-                        const double t = (d0 + 8u * (4 * h + w) < (unsigned)rc) ? A.bw_rb * x : 0.0; // ((BW/R) * sched) * SE
-                        if (h == 0 && w == 0) { acc_se = x; acc_t = t; }
-                        else { acc_se += x; acc_t += t; }
-                        if (RAWSE && se_out) se_out[base + 8 * (4 * h + w)] = x;
-                    }
+                for (int k = 0; k < 8; ++k) {
+                    const float y = (k & 1) ? normal_hi(ww[k >> 1], ntab) : normal_lo(ww[k >> 1], ntab);
+                    const double x = fabs(__fma_rn(1.5, (double)y, mu)); // channels/mimic_quadriga.py:49-56
+                    const bool in_run = d0 + 8u * k < (unsigned)rc;       // ((BW/R) * sched) * SE; adding the 0.0 of an
+                    if (k == 0) { acc_se = x; acc_t = in_run ? A.bw_rb * x : 0.0; } // unscheduled RB changes nothing (terms >= 0)
+                    else { acc_se += x; if (in_run) acc_t += A.bw_rb * x; }
+                    if (RAWSE && se_out) se_out[base + 8 * k] = x;
                 }
                 acc_se = acc_se + __shfl_down_sync(FULL, acc_se, 1);
                 acc_t = acc_t + __shfl_down_sync(FULL, acc_t, 1);
@@ -426,17 +418,31 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
     }
 }
 
+// the 4 KB normal table of the generators into shared memory, by the whole block (every warp of the block waits
+// here, so no warp may leave before this point)
+__device__ __forceinline__ void load_normal_tab(float2* ntab)
+{
+    const uint4* src = reinterpret_cast<const uint4*>(g_normal_tab);
+    uint4* dst = reinterpret_cast<uint4*>(ntab);
+    for (int i = threadIdx.x; i < IRS_NORMAL_TAB_N / 2; i += blockDim.x) dst[i] = __ldg(src + i);
+    __syncthreads();
+}
+
 #ifndef UE_ENV_MINB
 #define UE_ENV_MINB 8 /* 64 registers: 32 warps per SM measured fastest (profiles/r1_notes.md) */
 #endif
 __global__ void __launch_bounds__(FUSED_WARPS * 32, UE_ENV_MINB) k_ue_env(const __grid_constant__ StepArgs A)
 {
     __shared__ __align__(16) double sm[FUSED_WARPS][GRP][136];
-    ue_env_body<false>(A, sm);
+    __shared__ __align__(16) float2 ntab[IRS_NORMAL_TAB_N];
+    load_normal_tab(ntab);
+    ue_env_body<false>(A, sm, ntab);
 }
 // same kernel with the optional per-RB SE output (irs_raw_outputs.se_used; tests and trace dumps)
 __global__ void __launch_bounds__(FUSED_WARPS * 32, UE_ENV_MINB) k_ue_env_raw(const __grid_constant__ StepArgs A)
 {
     __shared__ __align__(16) double sm[FUSED_WARPS][GRP][136];
-    ue_env_body<true>(A, sm);
+    __shared__ __align__(16) float2 ntab[IRS_NORMAL_TAB_N];
+    load_normal_tab(ntab);
+    ue_env_body<true>(A, sm, ntab);
 }

@@ -3,22 +3,27 @@
 // The reference draws everything from ONE sequential PCG64 stream per env
 // (sixg_radio_mgmt/sixg_radio_mgmt/comm_env.py:631,666,673,679), which no parallel generator
 // can reproduce.  Native mode therefore defines its own stateless generators,
-// keyed so that a draw depends only on (seed, global env id, episode, frame, UE, index):
-//   Philox4x32-10 (Salmon et al., SC'11), key = seed, counter =
-//   (index | kind << 16 | ue << 24, frame, episode, global env id).
+// keyed so that a draw depends only on (seed, reset count, global env id, episode, frame, UE, index):
+//   Philox4x32-7 (Salmon et al., SC'11; 7 rounds pass BigCrush), key = env_key(seed, reset count),
+//   counter = (index | kind << 16 | ue << 24, frame, episode, global env id).
 // The distributions are the reference's: SE ~ |N(mu_u, 1.5)| with mu_u ~ |N(10, 7.5)| per
 // episode (channels/mimic_quadriga.py:37-56), traffic ~ Poisson(lambda_slice) * 1e6 bits
-// (traffics/mult_slice.py:28-31).  Every arithmetic step below is written with explicit
-// roundings so that a plain-C restatement reproduces the same bits (the test oracle does).
+// (traffics/mult_slice.py:28-31).
+// Normals: ONE per 16-bit half-word (8 per Philox quad) by table-driven inverse CDF - sign bit,
+// 15-bit tail probability, 512-entry (exact quantile, slope) table indexed by the exponent and top
+// mantissa bits of the tail count, one fused multiply-add (scripts/gen_normal_table.py: max
+// quantile error 5e-5, variance 1.000007, |z| <= 4.32).  Every step is an IEEE binary32/64
+// operation on shared constants (irs_normal_tab.h), so the plain-C oracle reproduces the bits.
 #pragma once
 #include "irs_common.cuh"
+#include "irs_normal_tab.h"
 
 enum { K_SE = 0, K_TRAFFIC = 1, K_MU = 2, K_POLICY = 3, K_SCEN = 4, K_PERM = 5 };
 
-__device__ __noinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1)
+__device__ __forceinline__ uint4 philox4x32_7(uint4 c, uint32_t k0, uint32_t k1)
 {
 #pragma unroll
-    for (int r = 0; r < 10; ++r) {
+    for (int r = 0; r < 7; ++r) {
         const uint64_t p0 = (uint64_t)0xD2511F53u * c.x, p1 = (uint64_t)0xCD9E8D57u * c.z;
         c = make_uint4((uint32_t)(p1 >> 32) ^ c.y ^ k0, (uint32_t)p1, (uint32_t)(p0 >> 32) ^ c.w ^ k1, (uint32_t)p0);
         k0 += 0x9E3779B9u;
@@ -30,11 +35,11 @@ __device__ __forceinline__ uint4 rng_quad(uint64_t seed, int kind, int ue, int q
 {
     const uint4 c = make_uint4((uint32_t)q | ((uint32_t)kind << 16) | ((uint32_t)ue << 24), (uint32_t)frame,
                                (uint32_t)episode, (uint32_t)gid);
-    return philox4x32_10(c, (uint32_t)seed, (uint32_t)(seed >> 32));
+    return philox4x32_7(c, (uint32_t)seed, (uint32_t)(seed >> 32));
 }
 
 // enable_random_episodes (comm_env.py:219-226, 434-444): element `pos` of a pseudo-random permutation of [0, n),
-// without a table: a 4-round balanced Feistel network over the next even power of two >= n, cycle-walked back into
+// without a table: an 8-round balanced Feistel network over the next even power of two >= n, cycle-walked back into
 // [0, n) (a bijection, so every episode of the range is played once per cycle, like np_random.permutation + cycle).
 // Round keys: one Philox quad of (seed, global env id, permutation number).
 __host__ __device__ __forceinline__ uint32_t mix32(uint32_t x)
@@ -53,10 +58,9 @@ __host__ __device__ __forceinline__ uint32_t feistel_perm(uint32_t i, uint32_t n
     uint32_t x = i;
     do {
         uint32_t l = x >> half, r = x & mask, t;
-        t = l ^ (mix32(r ^ k0) & mask); l = r; r = t;
-        t = l ^ (mix32(r ^ k1) & mask); l = r; r = t;
-        t = l ^ (mix32(r ^ k2) & mask); l = r; r = t;
-        t = l ^ (mix32(r ^ k3) & mask); l = r; r = t;
+        const uint32_t k[4] = {k0, k1, k2, k3};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { t = l ^ (mix32(r ^ k[j & 3] ^ (j * 0x9E3779B9u)) & mask); l = r; r = t; }
         x = (l << half) | r;
     } while (x >= n);
     return x;
@@ -67,84 +71,59 @@ __device__ __noinline__ int shuffled_episode(uint64_t seed, int gid, int gen, in
     return base + (int)feistel_perm((uint32_t)pos, (uint32_t)n, k.x, k.y, k.z, k.w);
 }
 
-// Where word w of SE quad q lands in the 135-RB row.  Quads 0..31 are laid out so that the two
-// quads 2m, 2m+1 hold exactly the 8 elements one accumulator of NumPy's pairwise sum visits
-// (row half m >> 3, accumulator m & 7: elements half * 64 + (m & 7) + 8k, k = 0..7 in order), so a
-// lane that generates both quads can add them up in registers in NumPy's order; quads 32, 33
-// are the serial tail 128..134 (word 3 of quad 33 is unused).
-__host__ __device__ __forceinline__ int se_index(int q, int w)
-{
-    return q < 32 ? ((q >> 4) << 6) + ((q >> 1) & 7) + 8 * (4 * (q & 1) + w) : 4 * q + w;
-}
+// ---- 16-bit inverse-CDF normal -------------------------------------------------------------------
+__device__ const uint32_t g_normal_tab[2 * IRS_NORMAL_TAB_N] = { IRS_NORMAL_TAB_WORDS };
 
-// Two standard normals from two 32-bit words: Box-Muller in binary32 with a fixed polynomial
-// log (atanh series on the mantissa) and octant-reduced sin/cos polynomials; no libm, no
-// fast-math intrinsics, so the result is a pure function of IEEE add/mul/fma/div/sqrt.
-__device__ __noinline__ float2 normal_pair2(uint32_t wa, uint32_t wb)
+// m = 15-bit magnitude word, signbit = 0 or 0x80000000; tab = the (c0, c1) table (shared or global memory)
+__device__ __forceinline__ float normal_from(uint32_t m, uint32_t signbit, const float2* __restrict__ tab)
 {
-    const float u1 = __fmul_rn((float)((wa >> 8) + 1u), 5.9604644775390625e-08f); // (0,1]
-    uint32_t bits = __float_as_uint(u1);
-    int e = (int)(bits >> 23) - 127;
-    float m = __uint_as_float((bits & 0x007FFFFFu) | 0x3F800000u);
-    if (m > 1.41421356f) { m = __fmul_rn(m, 0.5f); e += 1; }
-    const float s = __fdiv_rn(__fsub_rn(m, 1.0f), __fadd_rn(m, 1.0f));
-    const float s2 = __fmul_rn(s, s);
-    float p = __fmaf_rn(s2, 0.111111111f, 0.142857143f);
-    p = __fmaf_rn(s2, p, 0.2f);
-    p = __fmaf_rn(s2, p, 0.333333333f);
-    p = __fmaf_rn(s2, p, 1.0f);
-    const float lnm = __fmul_rn(__fmul_rn(2.0f, s), p);
-    const float lnu = __fmaf_rn((float)e, 0.693147181f, lnm);
-    const float r = __fsqrt_rn(__fmul_rn(-2.0f, lnu));
-    const uint32_t oct = wb >> 29;
-    const uint32_t t = (wb >> 6) & 0x7FFFFFu;
-    const float f = __fmul_rn((float)(2u * t + 1u), 5.9604644775390625e-08f);
-    const float phi = __fmul_rn(f, 0.785398163f);
-    const float x2 = __fmul_rn(phi, phi);
-    float sp = __fmaf_rn(x2, -1.98412698e-4f, 8.33333333e-3f);
-    sp = __fmaf_rn(x2, sp, -0.166666667f);
-    sp = __fmaf_rn(x2, sp, 1.0f);
-    const float sn = __fmul_rn(phi, sp);
-    float cp = __fmaf_rn(x2, 2.48015873e-5f, -1.38888889e-3f);
-    cp = __fmaf_rn(x2, cp, 4.16666667e-2f);
-    cp = __fmaf_rn(x2, cp, -0.5f);
-    const float cs = __fmaf_rn(x2, cp, 1.0f);
-    const bool swap = (oct == 0 || oct == 3 || oct == 4 || oct == 7);
-    float a = swap ? cs : sn;
-    float b = swap ? sn : cs;
-    if (oct >= 2 && oct <= 5) a = -a;
-    if (oct >= 4) b = -b;
-    return make_float2(__fmul_rn(r, a), __fmul_rn(r, b));
+    const uint32_t bits = __float_as_uint((float)(int)(32768u - m)); // tail count t in [1, 32768], exact in binary32
+    const float2 c = tab[(bits >> 18) - (127u << 5)];                // octave * 32 + top 5 mantissa bits
+    const float g = __uint_as_float(((bits & 0x3FFFFu) << 5) | 0x3F800000u); // position inside the segment, [1, 2)
+    return __uint_as_float(__float_as_uint(__fmaf_rn(c.y, g, c.x)) ^ signbit);
 }
-__device__ __forceinline__ void normal_pair(uint32_t wa, uint32_t wb, float& z0, float& z1)
+// half-word k (0 = low) of word w
+__device__ __forceinline__ float normal_lo(uint32_t w, const float2* __restrict__ tab)
 {
-    const float2 z = normal_pair2(wa, wb);
-    z0 = z.x;
-    z1 = z.y;
+    return normal_from(w & 0x7FFFu, (w << 16) & 0x80000000u, tab);
+}
+__device__ __forceinline__ float normal_hi(uint32_t w, const float2* __restrict__ tab)
+{
+    return normal_from((w >> 16) & 0x7FFFu, w & 0x80000000u, tab);
+}
+__device__ __forceinline__ const float2* normal_tab_global() { return reinterpret_cast<const float2*>(g_normal_tab); }
+
+// Where half-word k (0..7) of SE quad q lands in the 135-RB row.  Quad q < 16 holds exactly the 8 elements
+// one accumulator of NumPy's pairwise sum visits (row half q >> 3, accumulator q & 7: elements
+// half * 64 + (q & 7) + 8k, k = 0..7 in order), so a lane that generates the quad can add them up in
+// registers in NumPy's order; quad 16 is the serial tail 128..134 (its last half-word is unused).
+__host__ __device__ __forceinline__ int se_index(int q, int k)
+{
+    return q < 16 ? ((q >> 3) << 6) + (q & 7) + 8 * k : 128 + k;
 }
 
 // channels/mimic_quadriga.py:37-41
 __device__ __forceinline__ double native_mu(uint64_t seed, int ue, int episode, int gid)
 {
     const uint4 w = rng_quad(seed, K_MU, ue, 0, 0, episode, gid);
-    float z0, z1;
-    normal_pair(w.x, w.y, z0, z1);
-    return fabs(__fma_rn(7.5, (double)z0, 10.0));
+    return fabs(__fma_rn(7.5, (double)normal_lo(w.x, normal_tab_global()), 10.0));
 }
 
 // channels/mimic_quadriga.py:49-56: one UE row of SE into `se` (shared memory, 135 doubles),
-// produced cooperatively by the calling warp (quad q -> RBs 4q..4q+3).
+// produced cooperatively by the calling warp (reset path; the step generates in registers, irs_fused.cuh)
 __device__ __noinline__ void native_se_row(uint64_t seed, int ue, int frame, int episode, int gid, double* se)
 {
     const double mu = native_mu(seed, ue, episode, gid);
-    for (int q = lane_id(); q < (R + 3) / 4; q += 32) {
+    const float2* tab = normal_tab_global();
+    const int q = lane_id();
+    if (q <= 16) {
         const uint4 w = rng_quad(seed, K_SE, ue, q, frame, episode, gid);
-        float z[4];
-        normal_pair(w.x, w.y, z[0], z[1]);
-        normal_pair(w.z, w.w, z[2], z[3]);
+        const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-            if (se_index(q, j) < R) se[se_index(q, j)] = fabs(__fma_rn(1.5, (double)z[j], mu));
+        for (int k = 0; k < 8; ++k) {
+            const float z = (k & 1) ? normal_hi(ww[k >> 1], tab) : normal_lo(ww[k >> 1], tab);
+            if (se_index(q, k) < R) se[se_index(q, k)] = fabs(__fma_rn(1.5, (double)z, mu));
+        }
     }
 }
 
@@ -162,44 +141,4 @@ __device__ __noinline__ double native_traffic(uint64_t seed, const double* cdf_a
         if (__ldg(&cdf[mid]) <= u) lo = mid + 1; else hi = mid;
     }
     return (double)lo * 1e6;
-}
-
-// One UE row of a step in native mode, by the whole warp, in two generator passes:
-//   pass A  lane 0,1: SE quads 32,33 (RBs 128..134); lane 2: the UE's per-episode mean;
-//           lane 3: the Poisson arrival          (same counters and values as the functions above)
-//   pass B  lane l: SE quad l (RBs 4l..4l+3)
-// Returns the offered traffic in bits (0 when the UE's slice has no requirements).
-__device__ __noinline__ double native_row(uint64_t seed, const double* cdf_all, int ue, int lam_idx,
-                                             bool has_traffic, int frame, int episode, int gid, double* se)
-{
-    const int lane = lane_id();
-    const int kindA = lane == 2 ? K_MU : (lane == 3 ? K_TRAFFIC : K_SE);
-    const int qA = lane == 0 ? 32 : (lane == 1 ? 33 : 0);
-    const uint4 wa = rng_quad(seed, kindA, ue, qA, lane == 2 ? 0 : frame, episode, gid);
-    float z[4];
-    normal_pair(wa.x, wa.y, z[0], z[1]);
-    normal_pair(wa.z, wa.w, z[2], z[3]);
-    const double mu = __shfl_sync(FULL, fabs(__fma_rn(7.5, (double)z[0], 10.0)), 2);
-    if (lane < 2) {
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-            if (4 * qA + j < R) se[4 * qA + j] = fabs(__fma_rn(1.5, (double)z[j], mu));
-    }
-    // Poisson by table inversion (lane 3's words; the other lanes run along)
-    const double u = ((double)(wa.x >> 5) * 67108864.0 + (double)(wa.y >> 6)) * (1.0 / 9007199254740992.0);
-    const double* cdf = cdf_all + (size_t)lam_idx * IRS_POISSON_K;
-    int lo = 0;
-    if (has_traffic) {
-#pragma unroll
-        for (int step = IRS_POISSON_K / 2; step > 0; step >>= 1) // branch-free upper bound
-            if (__ldg(&cdf[lo + step - 1]) <= u) lo += step;
-        if (__ldg(&cdf[lo]) <= u) lo += 1; // lo in [0, 256]
-    }
-    const double traffic = __shfl_sync(FULL, (double)lo * 1e6, 3);
-    const uint4 wb = rng_quad(seed, K_SE, ue, lane, frame, episode, gid);
-    normal_pair(wb.x, wb.y, z[0], z[1]);
-    normal_pair(wb.z, wb.w, z[2], z[3]);
-#pragma unroll
-    for (int j = 0; j < 4; ++j) se[se_index(lane, j)] = fabs(__fma_rn(1.5, (double)z[j], mu));
-    return traffic;
 }

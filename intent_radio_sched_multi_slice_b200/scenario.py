@@ -12,7 +12,7 @@ import numpy as np
 MAX_UES = 25  # env_config/mult_slice.yml:14
 MAX_SLICES = 5  # env_config/mult_slice.yml:13
 NUM_RBS = 135  # env_config/mult_slice.yml:5
-POISSON_K = 256
+POISSON_K = 512
 
 F_ACTIVE, F_REQ, F_THR, F_REL, F_LAT, F_EMBB, F_URLLC = 1, 2, 4, 8, 16, 32, 64
 

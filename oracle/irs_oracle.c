@@ -29,7 +29,7 @@
 #define W 10   /* agents/ib_sched.py:49 max_obs_memory */
 #define NS 5   /* agents/ib_sched.py:50 max_number_ues_slice */
 #define RBG 5  /* agents/ib_sched.py:56 rbs_per_rbg */
-#define POISSON_K 256
+#define POISSON_K 512
 
 /* ---- scenario bank row (mirrors include/irs_b200.h; restated, not included) ---- */
 enum { F_ACTIVE = 1, F_REQ = 2, F_THR = 4, F_REL = 8, F_LAT = 16, F_EMBB = 32, F_URLLC = 64 };
@@ -95,12 +95,12 @@ typedef struct {
  * Counter-based RNG (native mode).  Not in the reference (it uses one sequential PCG64
  * stream per env, comm_env.py:631); this is the CPU restatement of the generators the
  * CUDA path defines in csrc/irs_rng.cuh so that native mode is parity-checkable too.
- * Philox4x32-10 (Salmon et al. 2011), key=(seed_lo,seed_hi),
+ * Philox4x32-7 (Salmon et al. 2011), key = env_key(seed, reset count),
  * counter=(q | kind<<16 | ue<<24, frame, episode, global env id).
  * ------------------------------------------------------------------------------------ */
-static void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1)
+static void philox4x32_7(uint32_t c[4], uint32_t k0, uint32_t k1)
 {
-    for (int r = 0; r < 10; ++r) {
+    for (int r = 0; r < 7; ++r) {
         uint64_t p0 = (uint64_t)0xD2511F53u * c[0];
         uint64_t p1 = (uint64_t)0xCD9E8D57u * c[2];
         uint32_t n0 = (uint32_t)(p1 >> 32) ^ c[1] ^ k0;
@@ -119,10 +119,10 @@ static void rng_quad(uint64_t key, int kind, int ue, int q, int frame, int episo
 {
     out[0] = (uint32_t)q | ((uint32_t)kind << 16) | ((uint32_t)ue << 24);
     out[1] = (uint32_t)frame; out[2] = (uint32_t)episode; out[3] = (uint32_t)gid;
-    philox4x32_10(out, (uint32_t)key, (uint32_t)(key >> 32));
+    philox4x32_7(out, (uint32_t)key, (uint32_t)(key >> 32));
 }
 /* enable_random_episodes (comm_env.py:219-226, 434-444) without a table: element `pos` of a pseudo-random permutation
- * of [0, n) - 4-round balanced Feistel network over the next even power of two, cycle-walked into [0, n)
+ * of [0, n) - 8-round balanced Feistel network over the next even power of two, cycle-walked into [0, n)
  * (csrc/irs_rng.cuh feistel_perm) */
 static uint32_t mix32(uint32_t x)
 {
@@ -139,7 +139,7 @@ static uint32_t feistel_perm(uint32_t i, uint32_t n, const uint32_t k[4])
     uint32_t mask = (1u << half) - 1, x = i;
     do {
         uint32_t l = x >> half, r = x & mask, t;
-        for (int j = 0; j < 4; ++j) { t = l ^ (mix32(r ^ k[j]) & mask); l = r; r = t; }
+        for (int j = 0; j < 8; ++j) { t = l ^ (mix32(r ^ k[j & 3] ^ ((uint32_t)j * 0x9E3779B9u)) & mask); l = r; r = t; }
         x = (l << half) | r;
     } while (x >= n);
     return x;
@@ -150,69 +150,44 @@ static int shuffled_episode(const orc_config *cfg, int gid, int gen, int base, i
     rng_quad(cfg->seed, K_PERM, 0, 0, gen, 0, gid, k);
     return base + (int)feistel_perm((uint32_t)pos, (uint32_t)n, k);
 }
-/* Box-Muller in binary32 with explicit fused multiply-adds only where written, so the
- * CUDA path (fmaf/__fmul_rn/...) produces the same bits. */
-static void normal_pair(uint32_t wa, uint32_t wb, float *z0, float *z1)
+/* One standard normal per 16-bit half-word by table-driven inverse CDF (csrc/irs_rng.cuh normal_from; table and
+ * its derivation: scripts/gen_normal_table.py -> csrc/irs_normal_tab.h, shared with the CUDA kernels) */
+#include "../intent_radio_sched_multi_slice_b200/csrc/irs_normal_tab.h"
+static const uint32_t normal_tab[2 * IRS_NORMAL_TAB_N] = { IRS_NORMAL_TAB_WORDS };
+static float bits_to_float(uint32_t b) { float f; memcpy(&f, &b, 4); return f; }
+static uint32_t float_to_bits(float f) { uint32_t b; memcpy(&b, &f, 4); return b; }
+static float normal16(uint32_t h)
 {
-    float u1 = (float)((wa >> 8) + 1u) * 5.9604644775390625e-08f; /* 2^-24, (0,1] */
-    union { float f; uint32_t i; } cv; cv.f = u1;
-    int e = (int)(cv.i >> 23) - 127;
-    cv.i = (cv.i & 0x007FFFFFu) | 0x3F800000u;
-    float m = cv.f;
-    if (m > 1.41421356f) { m = m * 0.5f; e += 1; }
-    float s = (m - 1.0f) / (m + 1.0f);
-    float s2 = s * s;
-    float p = fmaf(s2, 0.111111111f, 0.142857143f);
-    p = fmaf(s2, p, 0.2f);
-    p = fmaf(s2, p, 0.333333333f);
-    p = fmaf(s2, p, 1.0f);
-    float lnm = (2.0f * s) * p;
-    float lnu = fmaf((float)e, 0.693147181f, lnm);
-    float r = sqrtf(-2.0f * lnu);
-    uint32_t oct = wb >> 29;
-    uint32_t t = (wb >> 6) & 0x7FFFFFu;
-    float f = (float)(2u * t + 1u) * 5.9604644775390625e-08f;
-    float phi = f * 0.785398163f;
-    float x2 = phi * phi;
-    float sp = fmaf(x2, -1.98412698e-4f, 8.33333333e-3f);
-    sp = fmaf(x2, sp, -0.166666667f);
-    sp = fmaf(x2, sp, 1.0f);
-    float sn = phi * sp;
-    float cp = fmaf(x2, 2.48015873e-5f, -1.38888889e-3f);
-    cp = fmaf(x2, cp, 4.16666667e-2f);
-    cp = fmaf(x2, cp, -0.5f);
-    float cs = fmaf(x2, cp, 1.0f);
-    float a = (oct == 0 || oct == 3 || oct == 4 || oct == 7) ? cs : sn; /* |cos(theta)| */
-    float b = (oct == 0 || oct == 3 || oct == 4 || oct == 7) ? sn : cs; /* |sin(theta)| */
-    if (oct >= 2 && oct <= 5) a = -a;
-    if (oct >= 4) b = -b;
-    *z0 = r * a; *z1 = r * b;
+    uint32_t m = h & 0x7FFFu, signbit = (h & 0x8000u) << 16;
+    uint32_t bits = float_to_bits((float)(int)(32768u - m));
+    uint32_t idx = (bits >> 18) - (127u << 5);
+    float c0 = bits_to_float(normal_tab[2 * idx]), c1 = bits_to_float(normal_tab[2 * idx + 1]);
+    float g = bits_to_float(((bits & 0x3FFFFu) << 5) | 0x3F800000u);
+    return bits_to_float(float_to_bits(fmaf(c1, g, c0)) ^ signbit);
 }
+static float normal_half(const uint32_t w[4], int k) { return normal16((w[k >> 1] >> (16 * (k & 1))) & 0xFFFFu); }
 /* channels/mimic_quadriga.py:37-41: ues_mean_se = abs(N(10, 7.5)) per UE per episode */
 static double native_mu(uint64_t key, int ue, int episode, int gid)
 {
-    uint32_t w[4]; float z0, z1;
+    uint32_t w[4];
     rng_quad(key, K_MU, ue, 0, 0, episode, gid, w);
-    normal_pair(w[0], w[1], &z0, &z1);
-    return fabs(fma(7.5, (double)z0, 10.0));
+    return fabs(fma(7.5, (double)normal_half(w, 0), 10.0));
 }
-/* where word w of SE quad q lands in the row: quads 2m, 2m+1 hold the 8 elements that accumulator
- * m & 7 of half m >> 3 of NumPy's pairwise sum visits, in order; quads 32, 33 are the tail 128..134 */
-static int se_index(int q, int w)
+/* where half-word k of SE quad q lands in the row: quad q < 16 holds the 8 elements that accumulator q & 7 of half
+ * q >> 3 of NumPy's pairwise sum visits, in order; quad 16 is the tail 128..134 */
+static int se_index(int q, int k)
 {
-    return q < 32 ? ((q >> 4) << 6) + ((q >> 1) & 7) + 8 * (4 * (q & 1) + w) : 4 * q + w;
+    return q < 16 ? ((q >> 3) << 6) + (q & 7) + 8 * k : 128 + k;
 }
 /* channels/mimic_quadriga.py:49-56: SE[u,r] = abs(N(mu_u, 1.5)) */
 static void native_se_row(uint64_t key, int ue, int frame, int episode, int gid, double *se)
 {
     double mu = native_mu(key, ue, episode, gid);
-    for (int q = 0; q < (R + 3) / 4; ++q) {
-        uint32_t w[4]; float z[4];
+    for (int q = 0; q <= 16; ++q) {
+        uint32_t w[4];
         rng_quad(key, K_SE, ue, q, frame, episode, gid, w);
-        normal_pair(w[0], w[1], &z[0], &z[1]);
-        normal_pair(w[2], w[3], &z[2], &z[3]);
-        for (int j = 0; j < 4; ++j)
-            if (se_index(q, j) < R) se[se_index(q, j)] = fabs(fma(1.5, (double)z[j], mu));
+        for (int k = 0; k < 8; ++k)
+            if (se_index(q, k) < R) se[se_index(q, k)] = fabs(fma(1.5, (double)normal_half(w, k), mu));
     }
 }
 /* traffics/mult_slice.py:28-31: Poisson(lambda) * 1e6 bits, by table inversion */
@@ -1149,5 +1124,6 @@ int orc_sizeof_scenario(void) { return (int)sizeof(orc_scenario); }
 /* exposed for unit tests of the NumPy summation model and the RNG restatement */
 double orc_np_sum(const double *a, int n) { return np_sum(a, n); }
 void orc_round_int_equal_sum(const double *x, int n, int64_t target, int64_t *out) { round_int_equal_sum(x, n, target, out); }
-void orc_normal_pair(uint32_t wa, uint32_t wb, float *z) { normal_pair(wa, wb, &z[0], &z[1]); }
-void orc_philox(uint32_t *c, uint32_t k0, uint32_t k1) { philox4x32_10(c, k0, k1); }
+float orc_normal16(uint32_t h) { return normal16(h); }
+uint32_t orc_feistel_perm(uint32_t i, uint32_t n, const uint32_t *k) { return feistel_perm(i, n, k); }
+void orc_philox(uint32_t *c, uint32_t k0, uint32_t k1) { philox4x32_7(c, k0, k1); }

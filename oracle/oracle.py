@@ -69,7 +69,10 @@ def lib():
         _lib.orc_np_sum.restype = C.c_double
         _lib.orc_np_sum.argtypes = [C.c_void_p, C.c_int]
         _lib.orc_round_int_equal_sum.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.c_void_p]
-        _lib.orc_normal_pair.argtypes = [C.c_uint32, C.c_uint32, C.c_void_p]
+        _lib.orc_normal16.restype = C.c_float
+        _lib.orc_normal16.argtypes = [C.c_uint32]
+        _lib.orc_feistel_perm.restype = C.c_uint32
+        _lib.orc_feistel_perm.argtypes = [C.c_uint32, C.c_uint32, C.c_void_p]
         _lib.orc_philox.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32]
         assert _lib.orc_sizeof_config() == C.sizeof(Config)
         assert _lib.orc_sizeof_scenario() == 432
@@ -116,10 +119,14 @@ def round_int_equal_sum(x, target):
     return out
 
 
-def normal_pair(wa, wb):
-    z = np.zeros(2, np.float32)
-    lib().orc_normal_pair(int(wa), int(wb), _ptr(z))
-    return z
+def normal16(h):
+    """One standard normal from a 16-bit word (the native generators' inverse-CDF table transform)."""
+    return float(lib().orc_normal16(int(h)))
+
+
+def feistel_perm(i, n, keys):
+    k = np.asarray(keys, np.uint32)
+    return int(lib().orc_feistel_perm(int(i), int(n), _ptr(k)))
 
 
 def philox(counter, k0, k1):

@@ -57,7 +57,11 @@ TRACES = {
     # the baseline agents' surfaces (negative action seed: flat 5-vector actions)
     "twc": ("sched_twc", "mimic", "mult_slice", 19, 4, 300, 100, None, -8),
     "colran": ("sched_colran", "mimic", "mult_slice", 20, 8, 300, 100, None, -9),
+    # enable_random_episodes=True (every training configuration of simu.py:220-328): 25-step episodes shuffled over
+    # [3, 12); 14 rollovers wrap the 9-episode cycle; reset 8 passes options={"initial_episode": 6} (new permutation)
+    "random_eps": ("ib_sched", "mimic", "mult_slice", 21, 3, 375, 25, 12, 10),
 }
+EXTRA = {"random_eps": dict(random_episodes=True, reperm={8: 6})}
 
 
 def record(name):
@@ -71,17 +75,30 @@ def record(name):
         if not os.path.exists(f"{dst}/mult_slice"):
             os.symlink(src, f"{dst}/mult_slice")
     shims.QUADRIGA_STEPS["n"] = max_steps
+    extra = EXTRA.get(name, {})
     env, ag = refenv.make_env(wd, agent=agent, channel=channel, assoc=assoc, seed=seed,
-                              initial_episode=init_ep, max_episode_number=max_eps)
+                              initial_episode=init_ep, max_episode_number=max_eps,
+                              random_episodes=extra.get("random_episodes", False))
     fn = policy if act_seed is None else (rand_actions(act_seed) if act_seed > 0 else rand_flat(-act_seed))
-    steps, resets, ckpt = refenv.run_trace(env, ag, n_steps, fn, seed, init_ep)
+    steps, resets, ckpt = refenv.run_trace(env, ag, n_steps, fn, seed, init_ep, reperm=extra.get("reperm"))
+    if extra.get("random_episodes"):  # the env played what the predicted permutations say
+        pos, cur = 0, -1
+        for ri, (init, ep) in enumerate(zip(resets["initial"], resets["episode"])):
+            if init != -1:
+                cur, pos = cur + 1, 0
+                if ri > 0:
+                    pos = 1  # that reset also ends an episode: next() right after the new permutation
+            elif ri > 0:
+                pos += 1
+            order = resets[f"order_{cur}"]
+            assert ep == order[pos % len(order)], (ri, ep, order, pos)
     from golden_inputs import bits_checksum
 
     out = {
         "meta_agent": np.array(agent), "meta_channel": np.array(channel), "meta_assoc": np.array(assoc),
         "meta_seed": np.array(seed), "meta_initial_episode": np.array(init_ep), "meta_n_steps": np.array(n_steps),
         "meta_max_steps": np.array(max_steps), "meta_max_episodes": np.array(10000 if max_eps is None else max_eps),
-        "meta_numpy": np.array(np.__version__),
+        "meta_numpy": np.array(np.__version__), "meta_random_episodes": np.array(int(bool(extra.get("random_episodes")))),
         "se_checksum": bits_checksum(steps["se"]), "reset_se_checksum": bits_checksum(resets["se"]),
     }
     if channel.startswith("quadriga"):

@@ -127,6 +127,21 @@ def regenerate(meta, d):
     reset_se, step_se, step_tr = [], np.empty((n, U, R)), np.empty((n, U))
     ri = 0
     ep0 = int(d["reset_episode"][0])
+    n_perm = [0]
+
+    def permutation_draw(ri):
+        """enable_random_episodes: a reset with options["initial_episode"] != -1 draws a new permutation from the
+        env's generator BEFORE the scenario is created (comm_env.py:435-442) - the recorded order must be what the
+        stream gives at that point."""
+        if not int(meta.get("random_episodes", 0)) or int(d["reset_initial"][ri]) == -1:
+            return
+        want = d[f"reset_order_{n_perm[0]}"]
+        got = src.rng.permutation(np.arange(int(d["reset_initial"][ri]), int(meta["max_episodes"])))
+        if not np.array_equal(got, want):
+            raise AssertionError("regenerated episode permutation does not match the fixture")
+        n_perm[0] += 1
+
+    permutation_draw(0)
     reset_se.append(src.reset_frame(scen_of_episode(meta, ep0), ep0))
     k_in_ep = 0  # the env's step counter when channel.step is called (comm_env.py:303-305)
     for k in range(n):
@@ -136,6 +151,7 @@ def regenerate(meta, d):
         if d["done"][k]:
             ri += 1
             epr = int(d["reset_episode"][ri])
+            permutation_draw(ri)
             reset_se.append(src.reset_frame(scen_of_episode(meta, epr), epr))
             k_in_ep = 0
     reset_se = np.stack(reset_se)

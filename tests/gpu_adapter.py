@@ -42,7 +42,10 @@ class CudaEnv:
         return self._out()
 
     def buffers(self):
-        return self.eng.buf.cpu().numpy()
+        return self.eng.buffers().cpu().numpy()
+
+    def set_episode_order(self, order):
+        self.eng.set_episode_order(order)
 
     def state(self):
         v = self.eng.v

@@ -92,4 +92,4 @@ def test_scenario_bank_compiles_the_reference_scenarios(bank):
     assert n_act.min() >= 3 and n_act.max() <= 5
     assert ((arr["ue_slice"][:, :25] >= 0).sum(axis=1) == arr["sl"]["n_ues"].sum(axis=1)).all()
     cdf = bank.poisson_cdf()
-    assert cdf.shape[1] == 256 and np.all(np.diff(cdf, axis=1) >= 0) and np.allclose(cdf[:, -1], 1.0)
+    assert cdf.shape[1] == 512 and np.all(np.diff(cdf, axis=1) >= 0) and np.allclose(cdf[:, -1], 1.0)

@@ -20,10 +20,11 @@ pytestmark = pytest.mark.gpu
 def per_env_kernels(request, monkeypatch):
     """Every test of this file runs with both families of per-env kernels: k_action / k_env_tail (one warp
     per env, small batches) and k_action_t / k_env_tail_t + k_rollover (one thread per env, the default from
-    8,192 envs per launch; irs_serial.cuh)."""
+    49,152 envs per launch; irs_serial.cuh)."""
     monkeypatch.setenv("IRS_SERIAL_MIN_ENVS", "1" if request.param == "thread_per_env" else str(1 << 30))
 
-TRACES = ["cfg1_marr", "mapf", "ibsched_mimic", "ibsched_fixed", "seq_mimic", "seq_fixed", "sweep_scen", "twc", "colran"]
+TRACES = ["cfg1_marr", "mapf", "ibsched_mimic", "ibsched_fixed", "seq_mimic", "seq_fixed", "sweep_scen", "twc", "colran",
+          "random_eps"]
 
 
 def _cuda_env_factory(bank):
@@ -32,7 +33,8 @@ def _cuda_env_factory(bank):
         return CudaEnv(bank, 1, channel_mode=0, traffic_mode=0, sort_slices=sort, fixed_intra=fixed,
                        surface=trace_replay.agent_surface(meta),
                        assoc_mode=0 if meta["assoc"] == "mult_slice" else 1, max_steps=int(meta["max_steps"]),
-                       max_episodes=int(meta["max_episodes"]), initial_episode=int(meta["initial_episode"]))
+                       max_episodes=int(meta["max_episodes"]), initial_episode=int(meta["initial_episode"]),
+                       random_episodes=int(meta.get("random_episodes", 0)))
     return make
 
 
@@ -320,6 +322,53 @@ def test_generated_scenarios_match_oracle():
     assert np.array_equal(gpu.state()["scen"], orc.state()["scen"])
 
 
+def test_random_episodes_native_matches_oracle(bank):
+    """enable_random_episodes with the built-in (Feistel) permutation: CUDA and oracle play the same shuffled cycles,
+    per env, across wrap-arounds and a mid-run reset that draws a new permutation (comm_env.py:219-226, 434-444)."""
+    E = 40
+    kw = dict(channel_mode=2, traffic_mode=1, policy=3, fixed_intra=-1, sort_slices=1, max_steps=3, max_episodes=17,
+              initial_episode=6, auto_reset=1, random_episodes=1, seed=21, env_id_base=100)
+    from oracle import oracle
+    orc = oracle.OracleEnv(bank.array(), bank.poisson_cdf(), E, depth_cap=404, **kw)
+    gpu = CudaEnv(bank, E, depth_cap=401, **kw)
+    assert np.array_equal(gpu.state()["episode"], orc.state()["episode"])  # drawn at construction (comm_env.py:225)
+    compare_outputs(gpu.reset(), orc.reset(), "reset", keys=["obs0", "obs_i", "mask0", "mask_i", "sorted_slices"])
+    eps = []
+    for k in range(3 * 25):
+        compare_outputs(gpu.step(), orc.step(), f"step {k}")
+        assert np.array_equal(gpu.state()["episode"], orc.state()["episode"]), k
+        if k % 3 == 2:
+            eps.append(gpu.state()["episode"].copy())
+    eps = np.array(eps)
+    for e in range(E):  # 11 episodes per cycle, every one exactly once, same order in the second cycle
+        assert sorted(eps[:11, e]) == list(range(6, 17)) and np.array_equal(eps[:11, e], eps[11:22, e])
+    m = (np.arange(E) % 2).astype(np.uint8)
+    compare_outputs(gpu.reset(mask=m, initial_episode=12), orc.reset(mask=m, initial_episode=12), "re-permute",
+                    keys=["obs0", "obs_i", "mask0", "mask_i", "sorted_slices"])
+    for k in range(3 * 7):
+        compare_outputs(gpu.step(), orc.step(), f"after re-permute step {k}")
+        assert np.array_equal(gpu.state()["episode"], orc.state()["episode"]), k
+    assert (gpu.state()["episode"][m == 1] >= 12).all()
+    assert np.array_equal(gpu.buffers()[:, :, :401], orc.buffers()[:, :, :401])
+
+
+def test_episode_numbers_played_again_draw_fresh_noise(bank):
+    """The reference keeps one np_random stream running across episodes (comm_env.py:631-679), so an episode NUMBER
+    that comes round again sees new channel and traffic noise; the native generators' key carries the env's reset
+    count for the same effect."""
+    gpu = CudaEnv(bank, 4, channel_mode=2, traffic_mode=1, policy=1, fixed_intra=0, sort_slices=0, seed=3)
+    gpu.eng.enable_raw_outputs()
+    gpu.raw = gpu.eng._raw
+    gpu.reset(initial_episode=5)
+    gpu.step()
+    a = gpu.raw["se_used"].cpu().numpy().copy()
+    gpu.reset(initial_episode=5)
+    gpu.step()
+    b = gpu.raw["se_used"].cpu().numpy()
+    active = a.sum(axis=2) > 0
+    assert active.any() and not np.array_equal(a, b) and (np.abs(a - b)[active].mean() > 0.5)
+
+
 def test_native_se_statistics(bank):
     """Native mimic_quadriga / Poisson draws follow the reference's distributions
     (channels/mimic_quadriga.py:37-56: |N(mu_u, 1.5)|, mu_u = |N(10, 7.5)|;
@@ -335,6 +384,11 @@ def test_native_se_statistics(bank):
     mu = se_a.mean(axis=2)  # per (env, ue): close to the UE's mean (|N| folding is negligible for mu >> 1.5)
     resid = (se_a - mu[..., None])[mu > 6]
     assert abs(resid.std() - 1.5) < 0.02
+    # Kolmogorov-Smirnov: deviations from the row mean are exactly N(0, 1.5^2 (1 - 1/135)) when the draws are normal
+    # and nothing folds at zero (mu > 8 against |z| <= 4.32 sigma); critical value at alpha = 0.001 and n = 2e5: 4.4e-3
+    from scipy import stats
+    z = (se_a - mu[..., None])[mu > 8].ravel()[:200_000] / (1.5 * np.sqrt(1 - 1 / 135))
+    assert z.size == 200_000 and stats.kstest(z, "norm").statistic < 4.4e-3
     # the same statistic from NumPy draws of the reference's distributions
     rng = np.random.default_rng(0)
     mu_ref = np.abs(rng.normal(10, 7.5, 20000))

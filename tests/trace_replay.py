@@ -51,8 +51,15 @@ def replay(name, make_env, tight=False):
             cmp("reset " + key, out[key][0], d["reset_" + key][ri], k, True)
 
     ri = 0
+    random_eps = bool(int(meta.get("random_episodes", 0)))
+    n_perm = 0
+    if random_eps:  # replay the permutation the reference drew from its np_random (comm_env.py:435-442)
+        env.set_episode_order(d["reset_order_0"][None])
+        n_perm = 1
     out = env.reset(initial_episode=int(meta["initial_episode"]), se=rse[0][None])
     cmp_reset(out, 0, -1)
+    if random_eps:
+        assert int(env.state()["episode"][0]) == int(d["reset_episode"][0])
     ck = 0
     for k in range(int(meta["n_steps"])):
         out = env.step(d["a0"][k][None], np.maximum(d["intra"][k], 0)[None], sse[k][None], stf[k][None])
@@ -78,7 +85,13 @@ def replay(name, make_env, tight=False):
             ck += 1
         if d["done"][k]:
             ri += 1
-            out = env.reset(initial_episode=-1, se=rse[ri][None])
+            init = int(d["reset_initial"][ri]) if random_eps else -1
+            if random_eps and init != -1:
+                env.set_episode_order(d[f"reset_order_{n_perm}"][None])
+                n_perm += 1
+            out = env.reset(initial_episode=init, se=rse[ri][None])
             cmp_reset(out, ri, k)
+            if random_eps:
+                assert int(env.state()["episode"][0]) == int(d["reset_episode"][ri]), (ri, k)
     assert ck == len(d["ckpt_at_step"])
     return env
