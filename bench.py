@@ -187,7 +187,7 @@ def cpu_oracle_run(args, bank, n_envs, warmup, steps=None, budget_s=12.0, fill=0
     m = np.ones(n_envs, np.uint8)
     if args.workload == "trace":  # one bank slot per env, like the GPU arm
         power = 10.0 ** rng.uniform(-13.5, -9.5, (n_envs, args.trace_steps, 135, 25))
-        env.set_se_trace(oracle.power_to_se(power, layout=0))
+        env.set_se_trace(oracle.power_to_se(power, layout=0), wrap=True)
         del power
     for e0 in range(200):  # stagger the scenarios like the GPU arm: env e starts at episode e % 200
         m[:] = (np.arange(n_envs) % 200) == e0
@@ -276,7 +276,7 @@ def run_b200(args):
             eng.power_to_se(power, layout=0, out=se_bank[c0:c0 + n])
         torch.cuda.synchronize(dev)
         del power
-        eng.set_se_trace(se_bank)
+        eng.set_se_trace(se_bank, wrap=True)
         trace_bytes = se_bank.numel() * 8
         wl = (f"SE trace channel (QuadrigaChannel-shaped): one {T}-frame episode file per env resident in HBM, "
               "mult_slice scenario mix (200 scenarios, D 21..401)")

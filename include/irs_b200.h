@@ -154,6 +154,11 @@ typedef struct {
 typedef struct {
     const double* a0;        /* [E][5] inter-slice scores in [-1,1] (player_0) */
     const int32_t* intra;    /* [E][5] intra-slice algorithm per slice (player_1..5), may be NULL */
+    const uint32_t* sched_bits; /* [E][25][5] or NULL.  When given, the step takes this scheduling matrix as it is
+                                (bit r of UE u's 135-bit row = RB r, words little-end first) instead of running the
+                                built-in action_format: the slot for an ARBITRARY agent callback, which the caller
+                                evaluates on the host (comm_env.py:300, 484-512).  a0 / intra are then ignored.  An RB
+                                given to two UEs sets error bit 16 (comm_env.py:593-596).  irs_step only. */
 } irs_actions;
 
 typedef struct {
@@ -228,13 +233,15 @@ int irs_set_seed(irs_env* env, uint64_t seed);
 
 /* channel_mode 3 - QuadrigaChannel / QuadrigaChannelSeq (channels/quadriga.py:38-87,
  * channels/quadriga_seq.py:28-39) as a device-resident trace: `se_bank_dev` is f64
- * [n_episodes][n_steps][25][135], owned by the caller and kept alive while the env uses it.  An env
- * in episode `ep` at step counter `k` reads frame [ep % n_episodes][k % n_steps]: like the
- * reference, reset and the first step of an episode both read frame 0 (comm_env.py:303-305,449-451
- * call channel.step with the step counter before it is incremented).  The (association, episode)
- * file choice of choose_episode (quadriga.py:79-87, quadriga_seq.py:28-39) is the order in which
- * the caller lays the episodes out in the bank. */
-int irs_set_se_trace(irs_env* env, const double* se_bank_dev, int32_t n_episodes, int32_t n_steps);
+ * [n_episodes][n_steps][25][135], owned by the caller and kept alive while the env uses it.  Slot i of the bank
+ * holds the file of env episode first_episode + i (the reference opens a new target_cell_power.mat per episode,
+ * quadriga.py:46-55, 78-87).  An env in episode `ep` at step counter `k` reads frame
+ * [ep - first_episode][k % n_steps]: like the reference, reset and the first step of an episode both read frame 0
+ * (comm_env.py:303-305,449-451 call channel.step with the step counter before it is incremented).  An episode
+ * outside the bank sets the env's error word (bit 8, irs_check_errors) unless wrap != 0, which maps episodes onto
+ * slots modulo n_episodes (synthetic banks: benchmarks). */
+int irs_set_se_trace(irs_env* env, const double* se_bank_dev, int32_t n_episodes, int32_t n_steps, int32_t first_episode,
+                     int32_t wrap);
 
 /* The per-frame transform of QuadrigaChannel.step (channels/quadriga.py:56-74):
  *   SE = log2(1 + ((tx_power / 135) * p) / (0 + noise_power)),

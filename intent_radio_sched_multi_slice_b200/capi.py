@@ -13,7 +13,7 @@ from . import build as _build
 MAX_UES, MAX_SLICES, NUM_RBS, WINDOW, OBS0, OBSI, NUM_METRICS = 25, 5, 135, 10, 50, 19, 16
 
 IRS_OK, IRS_ERR_ARG, IRS_ERR_UNBOUND, IRS_ERR_CUDA, IRS_ERR_ENV = 0, -1, -2, -3, -4
-ERR_INTRA_ACTION, ERR_EPISODE_RANGE, ERR_RB_SUM = 1, 2, 4
+ERR_INTRA_ACTION, ERR_EPISODE_RANGE, ERR_RB_SUM, ERR_TRACE_EPISODE, ERR_RB_SHARED = 1, 2, 4, 8, 16
 
 METRIC_NAMES = [
     "reward_player_0", "reward_player_1", "reward_player_2", "reward_player_3", "reward_player_4",
@@ -44,7 +44,7 @@ class Layout(C.Structure):
 
 
 class Actions(C.Structure):
-    _fields_ = [("a0", C.c_void_p), ("intra", C.c_void_p)]
+    _fields_ = [("a0", C.c_void_p), ("intra", C.c_void_p), ("sched_bits", C.c_void_p)]
 
 
 class Inject(C.Structure):
@@ -81,7 +81,7 @@ SYMBOLS = {
     "irs_step_profiled": (C.c_int, [_P, C.POINTER(Actions), C.POINTER(Inject), C.POINTER(RawOutputs), _P,
                                     C.POINTER(C.c_float)]),
     "irs_set_seed": (C.c_int, [_P, C.c_uint64]),
-    "irs_set_se_trace": (C.c_int, [_P, _P, C.c_int32, C.c_int32]),
+    "irs_set_se_trace": (C.c_int, [_P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32]),
     "irs_power_to_se": (C.c_int, [_P, _P, C.c_int64, C.c_int32, C.c_double, C.c_double, _P]),
     "irs_run": (C.c_int, [_P, C.c_int32, _P]),
     "irs_step_host": (C.c_int, [_P, C.POINTER(Actions), C.POINTER(HostSurface), _P]),

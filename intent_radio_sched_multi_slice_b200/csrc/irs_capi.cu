@@ -37,7 +37,7 @@ struct irs_env {
                                    // use the thread-per-env action / tail kernels (irs_serial.cuh); below that one
                                    // thread per env leaves the SMs too empty to hide its serial latency
     const double* se_bank;         // channel_mode 3 (irs_set_se_trace)
-    int32_t bank_eps, bank_steps;
+    int32_t bank_eps, bank_steps, bank_first, bank_wrap;
     const int32_t* ep_order;       // random_episodes with a given order (irs_set_episode_order)
     int32_t ep_order_n;
     char err[256];
@@ -101,6 +101,8 @@ static StepArgs make_args(const irs_env* env)
     A.se_bank = env->se_bank;
     A.bank_eps = env->bank_eps;
     A.bank_steps = env->bank_steps;
+    A.bank_first = env->bank_first;
+    A.bank_wrap = env->bank_wrap;
     A.ep_order = env->ep_order;
     A.ep_order_n = env->ep_order_n;
     A.win_cap = env->cfg.surface ? W / 2 : W;
@@ -285,13 +287,14 @@ static int launch_step(irs_env* env, const StepArgs& A, cudaStream_t st, bool pr
     if (E <= 0) return IRS_OK;
     if (profile) CK(cudaEventRecord(env->ev[0], st));
     const bool serial = E >= env->serial_min;
-    if (serial) k_action_t<<<(E + SERIAL_THREADS - 1) / SERIAL_THREADS, SERIAL_THREADS, 0, st>>>(A);
+    if (A.sched_bits) k_sched_runs<<<(E + 7) / 8, 256, 0, st>>>(A);
+    else if (serial) k_action_t<<<(E + SERIAL_THREADS - 1) / SERIAL_THREADS, SERIAL_THREADS, 0, st>>>(A);
     else k_action<<<(E + 7) / 8, 256, 0, st>>>(A);
     if (profile) CK(cudaEventRecord(env->ev[1], st));
     StepArgs B2 = A; // small batches: 2 or 4 warps per env, so that the launch still puts ~32 warps on every SM
     B2.ue_split_log2 = env->ue_split >= 0 ? env->ue_split : (E <= 1184 ? 2 : (E <= 2368 ? 1 : 0));
     const unsigned env_warps = (unsigned)E << B2.ue_split_log2;
-    if (A.raw.se_used) k_ue_env_raw<<<(env_warps + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(B2);
+    if (A.raw.se_used || A.sched_bits) k_ue_env_raw<<<(env_warps + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(B2);
     else k_ue_env<<<(env_warps + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(B2);
     if (profile) CK(cudaEventRecord(env->ev[2], st));
     const bool alt = env->cfg.surface != 0; // SchedTWC / SchedColORAN: their surface reads the step's records before
@@ -318,12 +321,14 @@ static int step_args(irs_env* env, const irs_actions* actions, const irs_inject*
 {
     int rc = check_ready(env, inject);
     if (rc) return rc;
-    const bool given = actions && actions->a0; // explicit actions override the on-device policy
-    if (env->cfg.policy == 0 && !given) return fail(env, IRS_ERR_ARG, "policy 0 needs actions.a0");
+    const bool sched = actions && actions->sched_bits; // a scheduling matrix replaces the built-in action_format
+    const bool given = actions && actions->a0 && !sched; // explicit actions override the on-device policy
+    if (env->cfg.policy == 0 && !given && !sched) return fail(env, IRS_ERR_ARG, "policy 0 needs actions.a0");
     if (given && env->cfg.fixed_intra < 0 && !actions->intra) return fail(env, IRS_ERR_ARG, "fixed_intra -1 needs actions.intra");
     if (env->cfg.traffic_mode == 0 && !(inject && inject->traffic)) return fail(env, IRS_ERR_ARG, "traffic_mode 0 needs inject.traffic");
     *A = make_args(env);
     if (given) { A->a0 = actions->a0; A->intra = actions->intra; A->cfg.policy = 0; }
+    if (sched) A->sched_bits = actions->sched_bits;
     if (inject) { A->se = inject->se; A->traffic = inject->traffic; }
     if (raw) A->raw = *raw;
     return IRS_OK;
@@ -362,7 +367,8 @@ int irs_set_seed(irs_env* env, uint64_t seed)
     return IRS_OK;
 }
 
-int irs_set_se_trace(irs_env* env, const double* se_bank_dev, int32_t n_episodes, int32_t n_steps)
+int irs_set_se_trace(irs_env* env, const double* se_bank_dev, int32_t n_episodes, int32_t n_steps, int32_t first_episode,
+                     int32_t wrap)
 {
     if (!env) return IRS_ERR_ARG;
     if (!se_bank_dev || n_episodes <= 0 || n_steps <= 0) return fail(env, IRS_ERR_ARG, "irs_set_se_trace: empty bank");
@@ -370,6 +376,8 @@ int irs_set_se_trace(irs_env* env, const double* se_bank_dev, int32_t n_episodes
     env->se_bank = se_bank_dev;
     env->bank_eps = n_episodes;
     env->bank_steps = n_steps;
+    env->bank_first = first_episode;
+    env->bank_wrap = wrap ? 1 : 0;
     return IRS_OK;
 }
 

@@ -17,7 +17,7 @@
 #define FULL 0xffffffffu
 #define UE_LANES 0x01ffffffu /* lanes 0..24 */
 
-enum { ERR_INTRA_ACTION = 1, ERR_EPISODE_RANGE = 2, ERR_RB_SUM = 4 };
+enum { ERR_INTRA_ACTION = 1, ERR_EPISODE_RANGE = 2, ERR_RB_SUM = 4, ERR_TRACE_EPISODE = 8, ERR_RB_SHARED = 16 };
 
 // Per-UE state is kept as small records so that one warp-wide access moves a whole record:
 //   ue_i[E][25][8]  int32: the fields below (UI_*)
@@ -61,10 +61,12 @@ struct StepArgs {
     double bw_rb;          // cfg.bandwidth / 135 (ues.py:110), rounded once on the host
     const double* a0;      // actions (device) or NULL
     const int32_t* intra;  // or NULL
+    const uint32_t* sched_bits; // [E][25][5] scheduling matrix given directly (irs_actions.sched_bits) or NULL
     const double* se;      // injected SE or NULL
     const double* traffic; // injected traffic or NULL
     const double* se_bank; // channel_mode 3: [bank_eps][bank_steps][U][R] SE trace (irs_set_se_trace)
     int32_t bank_eps, bank_steps;
+    int32_t bank_first, bank_wrap; // slot of an episode = episode - bank_first (modulo bank_eps when bank_wrap)
     const int32_t* ep_order; // random_episodes with a given order: [E][ep_order_n] (irs_set_episode_order), else NULL
     int32_t ep_order_n;
     irs_raw_outputs raw;   // optional extra outputs (all may be NULL)
@@ -232,7 +234,12 @@ __device__ __noinline__ double np_sum135_pair(const double* rowA, const double* 
 // Same reduction order, both sums of one SE row at once: lanes 0..15 sum the throughput
 // terms ((BW/R) * sched[r]) * SE[r] (ues.py:108-116; sched is 1 inside the UE's RB run, else
 // 0), lanes 16..31 sum SE[r] itself.  Results valid in lanes 0 and 16.
-__device__ __noinline__ double np_sum135_thr_se(const double* se, int rb_s, int rb_e, double bw_rb)
+// sched[u, r] of the step: inside the UE's contiguous RB run, or bit r of a scheduling matrix given directly
+__device__ __forceinline__ bool sched_at(const uint32_t* bits, int rb_s, int rb_c, int r)
+{
+    return bits ? ((bits[r >> 5] >> (r & 31)) & 1u) != 0 : (unsigned)(r - rb_s) < (unsigned)rb_c;
+}
+__device__ __noinline__ double np_sum135_thr_se(const double* se, int rb_s, int rb_e, double bw_rb, const uint32_t* bits = nullptr)
 {
     const int lane = lane_id();
     const int j = lane & 7;
@@ -240,7 +247,7 @@ __device__ __noinline__ double np_sum135_thr_se(const double* se, int rb_s, int 
     const bool terms = lane < 16;
     auto elem = [&](int r) -> double {
         const double x = se[r];
-        const double sched = (r >= rb_s && r < rb_e) ? 1.0 : 0.0;
+        const double sched = sched_at(bits, rb_s, rb_e - rb_s, r) ? 1.0 : 0.0;
         return terms ? (bw_rb * sched) * x : x;
     };
     double r = elem(base);
@@ -264,10 +271,18 @@ __device__ __forceinline__ int scen_of_episode(const irs_config& c, int episode)
 }
 
 // channel_mode 3: the SE frame env state (episode, step counter k) reads (channels/quadriga.py:38-87)
-__device__ __forceinline__ const double* trace_frame(const StepArgs& A, int episode, int k)
+__device__ __forceinline__ const double* trace_frame(const StepArgs& A, int e, int episode, int k)
 {
     const int f = (k < 0 ? 0 : k) % A.bank_steps; // a trace shorter than the episode wraps around
-    return A.se_bank + ((size_t)(episode % A.bank_eps) * A.bank_steps + (size_t)f) * (U * R);
+    int slot = episode - A.bank_first;             // the reference opens this episode's own file (quadriga.py:46-55, 78-87)
+    if (A.bank_wrap) {
+        slot %= A.bank_eps;
+        if (slot < 0) slot += A.bank_eps;
+    } else if (slot < 0 || slot >= A.bank_eps) {   // an episode the bank does not hold: flagged, never replaced silently
+        if (lane_id() == 0) atomicOr(&A.st.err[e], ERR_TRACE_EPISODE);
+        slot = 0;
+    }
+    return A.se_bank + ((size_t)slot * A.bank_steps + (size_t)f) * (U * R);
 }
 
 // per-UE buffer parameters: the UE's slice (associations/mult_slice.py:468-488 update_ues);

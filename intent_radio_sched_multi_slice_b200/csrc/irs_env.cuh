@@ -332,6 +332,41 @@ __global__ void k_init(const __grid_constant__ StepArgs A)
     for (int s = 0; s < S; ++s) A.st.sorted[(size_t)e * S + s] = (int8_t)s;
 }
 
+// A scheduling matrix given directly (irs_actions.sched_bits) instead of the built-in action_format: RBs per UE =
+// its row sum (what ib_sched.py:188-190 reads from sched_decision), first RB for the raw outputs; an RB given to two
+// UEs is the reference's "same RB for more than one UE" exception (comm_env.py:593-596).  One warp per env.
+__global__ void __launch_bounds__(256) k_sched_runs(const __grid_constant__ StepArgs A)
+{
+    const int e = A.env_begin + (int)((blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 5);
+    if (e >= A.env_end) return;
+    const int lane = lane_id();
+    int cnt = 0, first = 0;
+    uint32_t w[5] = {0, 0, 0, 0, 0};
+    if (lane < U) {
+        const uint32_t* sb = A.sched_bits + ((size_t)e * U + lane) * 5;
+#pragma unroll
+        for (int i = 4; i >= 0; --i) {
+            w[i] = sb[i] & (i == 4 ? 0x7fu : 0xffffffffu); // 135 = 4 * 32 + 7 RBs
+            cnt += __popc(w[i]);
+            if (w[i]) first = 32 * i + __ffs(w[i]) - 1;
+        }
+        A.st.rb[(size_t)e * U + lane] = make_short2((short)first, (short)cnt);
+        if (A.raw.rb_start) A.raw.rb_start[(size_t)e * U + lane] = (int16_t)first;
+        if (A.raw.rb_count) A.raw.rb_count[(size_t)e * U + lane] = (int16_t)cnt;
+    }
+    int total = cnt, covered = 0;
+#pragma unroll
+    for (int i = 0; i < 5; ++i) {
+        uint32_t o = w[i];
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) o |= __shfl_xor_sync(FULL, o, d);
+        covered += __popc(o);
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) total += __shfl_xor_sync(FULL, total, d);
+    if (lane == 0 && total != covered) atomicOr(&A.st.err[e], ERR_RB_SHARED);
+}
+
 // irs_set_episode_order: every env moves to the given table's entry at its current position
 __global__ void k_apply_order(const __grid_constant__ StepArgs A)
 {

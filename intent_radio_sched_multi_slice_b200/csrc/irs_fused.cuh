@@ -115,8 +115,8 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
                 const int rs_a = __shfl_sync(FULL, rb_s, ue_j), rc_a = __shfl_sync(FULL, rb_c, ue_j);
                 if (valid && k < 7) {
                     const double x = fabs(__fma_rn(1.5, (double)z, mu_aux));
-                    reinterpret_cast<double2*>(ws + 16 * j)[k] =
-                        make_double2(x, (unsigned)(128 + k - rs_a) < (unsigned)rc_a ? A.bw_rb * x : 0.0);
+                    const uint32_t* sb = (RAWSE && A.sched_bits) ? A.sched_bits + ((size_t)e * U + ue_j) * 5 : nullptr;
+                    reinterpret_cast<double2*>(ws + 16 * j)[k] = make_double2(x, sched_at(sb, rs_a, rc_a, 128 + k) ? A.bw_rb * x : 0.0);
                 }
                 // Poisson arrival of UE j on lane 8j+2 (traffics/mult_slice.py:28-31)
                 const int lam_j = __shfl_sync(FULL, lam_idx, ue_j);
@@ -153,11 +153,13 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
                 double* se_out = (RAWSE && A.raw.se_used) ? A.raw.se_used + ((size_t)e * U + uj) * R : nullptr;
                 const uint4 wb = rng_quad(key, K_SE, uj, l16, frame, episode, gid);
                 const uint32_t ww[4] = {wb.x, wb.y, wb.z, wb.w};
+                const uint32_t* sb = (RAWSE && A.sched_bits) ? A.sched_bits + ((size_t)e * U + uj) * 5 : nullptr;
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {
                     const float y = (k & 1) ? normal_hi(ww[k >> 1], ntab) : normal_lo(ww[k >> 1], ntab);
                     const double x = fabs(__fma_rn(1.5, (double)y, mu)); // channels/mimic_quadriga.py:49-56
-                    const bool in_run = d0 + 8u * k < (unsigned)rc;       // ((BW/R) * sched) * SE; adding the 0.0 of an
+                    const bool in_run = (RAWSE && sb) ? sched_at(sb, 0, 0, base + 8 * k)
+                                                     : d0 + 8u * k < (unsigned)rc; // ((BW/R) * sched) * SE; adding the 0.0 of an
                     if (k == 0) { acc_se = x; acc_t = in_run ? A.bw_rb * x : 0.0; } // unscheduled RB changes nothing (terms >= 0)
                     else { acc_se += x; if (in_run) acc_t += A.bw_rb * x; }
                     if (RAWSE && se_out) se_out[base + 8 * k] = x;
@@ -197,7 +199,7 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
         // the row holds (ues.py:108-116), and their mean SE is never observed (ib_sched.py:111,147).
         const double* frame_base = nullptr;
         if (cfg.channel_mode == 0) frame_base = A.se + (size_t)e * U * R;
-        else if (cfg.channel_mode == 3) frame_base = trace_frame(A, episode, step);
+        else if (cfg.channel_mode == 3) frame_base = trace_frame(A, e, episode, step);
         double* ws = &sm[wib][0][0];
         const bool all_rows = RAWSE && A.raw.se_used;
         uint32_t todo = __ballot_sync(FULL, ue_lane && (s_mine >= 0 || all_rows));
@@ -234,19 +236,19 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
             const bool live = side ? live1 : true;
             const int rs = __shfl_sync(FULL, rb_s, uj), rc = __shfl_sync(FULL, rb_c, uj);
             const int l16 = lane & 15, base = ((l16 >> 3) << 6) + (l16 & 7);
-            const unsigned d0 = (unsigned)(base - rs);
             const double* rowp = frame_base ? frame_base + (size_t)uj * R : nullptr;
             double x[8], xt[7];
 #pragma unroll
             for (int k = 0; k < 8; ++k) x[k] = rowp ? __ldg(rowp + base + 8 * k) : 2.0; // channels/fixed_se.py:26
 #pragma unroll
             for (int k = 0; k < 7; ++k) xt[k] = (l16 == 8 || all_rows) ? (rowp ? __ldg(rowp + 128 + k) : 2.0) : 0.0;
+            const uint32_t* sb = (RAWSE && A.sched_bits) ? A.sched_bits + ((size_t)e * U + uj) * 5 : nullptr;
             double acc_se = x[0];
-            double acc_t = (d0 < (unsigned)rc) ? A.bw_rb * x[0] : 0.0; // ((BW/R) * sched) * SE, ues.py:108-116
+            double acc_t = sched_at(sb, rs, rc, base) ? A.bw_rb * x[0] : 0.0; // ((BW/R) * sched) * SE, ues.py:108-116
 #pragma unroll
             for (int k = 1; k < 8; ++k) {
                 acc_se += x[k];
-                acc_t += (d0 + 8u * k < (unsigned)rc) ? A.bw_rb * x[k] : 0.0;
+                acc_t += sched_at(sb, rs, rc, base + 8 * k) ? A.bw_rb * x[k] : 0.0;
             }
             acc_se = acc_se + __shfl_down_sync(FULL, acc_se, 1);
             acc_t = acc_t + __shfl_down_sync(FULL, acc_t, 1);
@@ -258,7 +260,7 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
 #pragma unroll
                 for (int k = 0; k < 7; ++k) {
                     acc_se += xt[k];
-                    acc_t += ((unsigned)(128 + k - rs) < (unsigned)rc) ? A.bw_rb * xt[k] : 0.0;
+                    acc_t += sched_at(sb, rs, rc, 128 + k) ? A.bw_rb * xt[k] : 0.0;
                 }
             }
             const double res_se = 0. + (acc_se + __shfl_down_sync(FULL, acc_se, 8)); // valid on lanes 0, 16
@@ -297,7 +299,8 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
         for (int jj = 0; jj < n; ++jj) {
             const int uj = sel4(ul, jj);
             const int rs = __shfl_sync(FULL, rb_s, uj), rc = __shfl_sync(FULL, rb_c, uj);
-            const double sums = np_sum135_thr_se(sm[wib][jj], rs, rs + rc, A.bw_rb);
+            const double sums = np_sum135_thr_se(sm[wib][jj], rs, rs + rc, A.bw_rb,
+                                                 (RAWSE && A.sched_bits) ? A.sched_bits + ((size_t)e * U + uj) * 5 : nullptr);
             const double a = __shfl_sync(FULL, sums, 0), b = __shfl_sync(FULL, sums, 16);
             if (lane == uj) { sum_t = a; sum_se = b; }
             if (RAWSE && A.raw.se_used)

@@ -78,7 +78,7 @@ __device__ __noinline__ void channel_row(const StepArgs& A, uint64_t key, int e,
         const double* src = A.se + ((size_t)e * U + u) * R;
         for (int r = lane; r < R; r += 32) se[r] = src[r];
     } else if (A.cfg.channel_mode == 3) { // frame 0 at reset, frame k at the step whose counter is k
-        const double* src = trace_frame(A, episode, frame > 0 ? frame - 1 : 0) + (size_t)u * R;
+        const double* src = trace_frame(A, e, episode, frame > 0 ? frame - 1 : 0) + (size_t)u * R;
         for (int r = lane; r < R; r += 32) se[r] = src[r];
     } else if (A.cfg.channel_mode == 1) {
         for (int r = lane; r < R; r += 32) se[r] = 2.0; // channels/fixed_se.py:26

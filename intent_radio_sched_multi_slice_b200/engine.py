@@ -148,15 +148,18 @@ class BatchEngine:
             capi.check(self.h, self.lib.irs_set_episode_order(self.h, t.data_ptr(), t.shape[1], self._stream()))
 
     # -- channel_mode 3: device-resident SE trace (channels/quadriga.py) ------------------------
-    def set_se_trace(self, se_bank: torch.Tensor):
+    def set_se_trace(self, se_bank: torch.Tensor, first_episode: int = 0, wrap: bool = False):
         """Bind a float64 [n_episodes, n_steps, 25, 135] SE bank living on this engine's device
-        (irs_set_se_trace).  The engine keeps a reference so the memory outlives its use."""
+        (irs_set_se_trace): slot i = the file of env episode first_episode + i; `wrap` maps episodes onto slots
+        modulo n_episodes instead of flagging an episode outside the bank.  The engine keeps a reference so the
+        memory outlives its use."""
         if se_bank.dtype != torch.float64 or se_bank.dim() != 4 or tuple(se_bank.shape[2:]) != (U, R):
             raise ValueError("se_bank must be float64 [n_episodes, n_steps, 25, 135]")
         if se_bank.device != self.device or not se_bank.is_contiguous():
             raise ValueError("se_bank must be a contiguous tensor on the engine's device")
         self._se_bank = se_bank
-        capi.check(self.h, self.lib.irs_set_se_trace(self.h, se_bank.data_ptr(), se_bank.shape[0], se_bank.shape[1]))
+        capi.check(self.h, self.lib.irs_set_se_trace(self.h, se_bank.data_ptr(), se_bank.shape[0], se_bank.shape[1],
+                                                     int(first_episode), int(bool(wrap))))
 
     def power_to_se(self, power: torch.Tensor, layout: int = 0, tx_power: float = 100.0, noise_power: float = 10e-14,
                     out: torch.Tensor | None = None):
@@ -193,13 +196,21 @@ class BatchEngine:
                 self.h, m.data_ptr() if m is not None else None, int(initial_episode),
                 ie.data_ptr() if ie is not None else None, C.byref(inj), self._raw_ref(), self._stream()))
 
-    def step(self, a0=None, intra=None, se=None, traffic=None):
-        """CommunicationEnv.step for every env (comm_env.py:271-373).  Asynchronous."""
+    def step(self, a0=None, intra=None, se=None, traffic=None, sched_bits=None):
+        """CommunicationEnv.step for every env (comm_env.py:271-373).  Asynchronous.  `sched_bits` (int32/uint32
+        [E, 25, 5], bit r of a UE's 135-bit row = RB r) gives the scheduling matrix directly instead of an action."""
         a0_t, in_t = self._dev(a0, torch.float64), self._dev(intra, torch.int32)
         se_t, tr_t = self._dev(se, torch.float64), self._dev(traffic, torch.float64)
-        act = capi.Actions(a0_t.data_ptr() if a0_t is not None else None, in_t.data_ptr() if in_t is not None else None)
+        sb_t = None
+        if sched_bits is not None:
+            sb = sched_bits if isinstance(sched_bits, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(sched_bits).view(np.int32))
+            sb_t = sb.to(device=self.device).contiguous()
+            if tuple(sb_t.shape) != (self.E, U, 5) or sb_t.element_size() != 4:
+                raise ValueError("sched_bits must be 32-bit words [num_envs, 25, 5]")
+        act = capi.Actions(a0_t.data_ptr() if a0_t is not None else None, in_t.data_ptr() if in_t is not None else None,
+                           sb_t.data_ptr() if sb_t is not None else None)
         inj = capi.Inject(se_t.data_ptr() if se_t is not None else None, tr_t.data_ptr() if tr_t is not None else None)
-        self._keep = (a0_t, in_t, se_t, tr_t)
+        self._keep = (a0_t, in_t, se_t, tr_t, sb_t)
         with torch.cuda.device(self.device):
             capi.check(self.h, self.lib.irs_step(self.h, C.byref(act), C.byref(inj), self._raw_ref(), self._stream()))
 

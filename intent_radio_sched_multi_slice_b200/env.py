@@ -54,9 +54,9 @@ class BatchedMARLCommEnv:
         self.simu_name = simu_name if simu_name is not None else data["simulation"]["simu_name"]
         self.root_path, self.agent_name, self.seed, self.debug = root_path, agent_name, seed, debug
         self.initial_episode_number = initial_episode_number
-        if enable_random_episodes:
-            raise NotImplementedError("enable_random_episodes (comm_env.py:219-226) is not built; pass explicit "
-                                      "initial episodes per env instead")
+        # comm_env.py:219-226, 434-444: every env plays its own shuffled cycle of [initial_episode, max_episodes)
+        # (a counter-based permutation keyed by (seed, global env id); see irs_b200.h cfg.random_episodes)
+        self.enable_random_episodes = bool(enable_random_episodes)
         # save_hist (comm_env.py:345-350): hist/<simu>/<agent>/ep_N.npz per finished episode, for the envs in
         # `hist_envs` (default: the single env of a MARLCommEnv; nothing for a batch unless asked)
         self.save_hist = bool(save_hist)
@@ -82,7 +82,12 @@ class BatchedMARLCommEnv:
             acls = AssociationClass if hasattr(AssociationClass, "scenario_bank") else plugins.MultSliceAssociation
             scenario_bank = acls.scenario_bank(root_path)
         self.bank = scenario_bank
-        self.auto_reset = (self.num_envs > 1) if auto_reset is None else bool(auto_reset)
+        hooked = self._host_channel is not None or self._host_traffic is not None
+        if hooked and auto_reset:
+            # the device rollover cannot call a host plugin for the new episode's step-0 frame (comm_env.py:449-451)
+            raise ValueError("auto_reset=True needs device-side channel and traffic plugins; with host plugin hooks "
+                             "reset finished envs with reset(mask=done)")
+        self.auto_reset = (self.num_envs > 1 and not hooked) if auto_reset is None else bool(auto_reset)
         self.env_id_base = env_id_base
         self.channel_episodes = channel_episodes  # channel_mode 3: env episodes whose files form the SE bank
         self.agents = {f"player_{i}" for i in range(self.max_number_slices + 1)}  # marl_comm_env.py:20-24
@@ -93,6 +98,7 @@ class BatchedMARLCommEnv:
         self.eng = None
         self._first_reset = True
         self._np_rngs = None
+        self._callbacks = None
         if obs_space_format is not None:
             self.set_agent_functions(obs_space_format, action_format, calculate_reward, obs_space, action_space)
 
@@ -100,13 +106,21 @@ class BatchedMARLCommEnv:
     def set_agent_functions(self, obs_space_format, action_format, calculate_reward, obs_space=None,
                             action_space=None):
         surf = {agents_mod.surface_of(cb) for cb in (obs_space_format, action_format, calculate_reward)}
-        if len(surf) != 1 or None in surf:
-            raise NotImplementedError(
-                "set_agent_functions: only the built-in agent surfaces (IBSched, MARR, MAPF, IBSchedSB3[PF]) run "
-                "on the device; pass the bound methods of one of those agent objects")
-        self._surface = surf.pop()
-        self.observation_space = obs_space if obs_space is not None else self._surface().get_obs_space()
-        self.action_space = action_space if action_space is not None else self._surface().get_action_space()
+        if len(surf) == 1 and None not in surf:  # a built-in surface: evaluated by the kernels
+            self._callbacks = None
+            self._surface = surf.pop()
+            self.observation_space = obs_space if obs_space is not None else self._surface().get_obs_space()
+            self.action_space = action_space if action_space is not None else self._surface().get_action_space()
+        else:
+            # Arbitrary callables (comm_env.py:484-512): honoured on the HOST path.  action_format runs here and its
+            # scheduling matrix goes to the device as it is (irs_actions.sched_bits); UEs.step runs on the device; the
+            # raw frame comes back and obs_space_format / calculate_reward run here on the reference's dict
+            # (comm_env.py:320-341).  One Python call per env and step: the slow path, for agents that are not built in.
+            if not all(callable(cb) for cb in (obs_space_format, action_format, calculate_reward)):
+                raise ValueError("set_agent_functions needs three callables (comm_env.py:484-512)")
+            self._callbacks = (obs_space_format, action_format, calculate_reward)
+            self._surface = agents_mod.IBSched  # still written by the tail kernel; not returned on this path
+            self.observation_space, self.action_space = obs_space, action_space
         if self.eng is not None:
             self.eng.close()
             self.eng = None
@@ -121,15 +135,32 @@ class BatchedMARLCommEnv:
                                    fixed_intra=s.fixed_intra, policy=s.policy, surface=s.surface, max_steps=self.max_number_steps,
                                    max_episodes=self.max_number_episodes, initial_episode=self.initial_episode_number,
                                    auto_reset=int(self.auto_reset), env_id_base=self.env_id_base, seed=self.seed,
-                                   bandwidth=float(self.bandwidths[0]), **kw)
+                                   bandwidth=float(self.bandwidths[0]), random_episodes=int(self.enable_random_episodes),
+                                   **kw)
             if kw["channel_mode"] == 3:  # QuadrigaChannel[Seq]: transform the power files once, keep SE in HBM
                 ch = self.ChannelClass if hasattr(self.ChannelClass, "power_bank") else \
                     plugins.BUILTIN[self.ChannelClass.__name__]
-                eps = self.channel_episodes if self.channel_episodes is not None else \
-                    range(self.initial_episode_number, self.initial_episode_number + 1)
+                eps = self.channel_episodes
+                if eps is None:  # every episode the run can visit (quadriga.py:46-55 opens one file per episode)
+                    if getattr(ch, "_registered", None) is not None:
+                        eps = range(ch._registered_first, ch._registered_first + len(ch._registered))
+                    elif self.max_number_episodes - self.initial_episode_number <= 64:
+                        eps = range(self.initial_episode_number, self.max_number_episodes)
+                    else:
+                        raise ValueError(
+                            f"{ch.__name__}: the run can visit episodes {self.initial_episode_number}.."
+                            f"{self.max_number_episodes - 1}; pass channel_episodes=range(first, last + 1) (the files "
+                            "kept in HBM, 27 MB per 1000-step episode) or a smaller max_episode_number")
+                eps = [int(x) for x in eps]
+                if eps != list(range(eps[0], eps[0] + len(eps))):
+                    raise ValueError("channel_episodes must be a contiguous ascending range of env episode numbers")
                 power = torch.from_numpy(ch.power_bank(self.root_path, eps)).to(self.device)
+                # slot i = episode eps[0] + i; an env that reaches an episode outside the bank raises (debug) instead
+                # of replaying another episode's file
                 self.eng.set_se_trace(self.eng.power_to_se(power, layout=0, tx_power=ch.transmission_power,
-                                                           noise_power=ch.thermal_noise_power))
+                                                           noise_power=ch.thermal_noise_power), first_episode=eps[0])
+            if self._callbacks is not None:
+                self.eng.enable_raw_outputs()
         return self.eng
 
     # ---- host tensor hooks (slow path; any Channel/Traffic class) -------------------------------
@@ -208,6 +239,10 @@ class BatchedMARLCommEnv:
         rec = self._history()
         if rec is not None:
             rec.mark_reset()
+        if self._callbacks is not None:
+            frames = self._raw_frames(None, None, reset=True)
+            obs = [self._callbacks[0](f) for f in frames]
+            return (obs[0] if self.num_envs == 1 else obs), {}
         return self._format_obs(), {}
 
     def _history(self):
@@ -225,7 +260,76 @@ class BatchedMARLCommEnv:
         return self._recorder
 
     # ---- comm_env.py:271-373 / marl_comm_env.py:42-66 ------------------------------------------
+    # ---- arbitrary agent callbacks: the host path (comm_env.py:300, 320-341) ------------------------
+    def _raw_frames(self, scheds, actions, reset=False):
+        """The reference's raw observation dict (ues.py:236-243 + comm_env.py:327-338) of every env, from the
+        device's per-UE outputs.  At reset the metrics are zero (comm_env.py:455-478; `pkt_incoming` of the reset
+        frame - a draw the reference shows but never enqueues - is zero here)."""
+        from . import scenario as scn
+        eng = self.eng
+        raw = {k: v.cpu().numpy() for k, v in eng._raw.items()}
+        rows = eng.scenario_rows()
+        scen = eng.v["scen"].cpu().numpy()
+        frames = []
+        for e in range(self.num_envs):
+            if scen[e] < len(self.bank.reqs):
+                req, sua = self.bank.reqs[scen[e]], self.bank.assocs[scen[e]]
+            else:  # generated on the device (assoc_mode 2)
+                req, sua = scn.req_from_row(rows[e])
+            f = {"mobility": np.ones((25, 2)), "spectral_efficiencies": raw["se_used"][e][None],
+                 "basestation_ue_assoc": (sua.sum(axis=0) > 0).astype(np.float64)[None],
+                 "basestation_slice_assoc": np.array([[1.0 if req.get(f"slice_{s}", {}) != {} else 0.0 for s in range(5)]]),
+                 "slice_ue_assoc": sua.copy(), "slice_req": scn.callable_req(req)}
+            if reset:
+                z = np.zeros(25)
+                f.update({"sched_decision": np.zeros((1, 25, 135)), "pkt_incoming": z.copy(), "pkt_throughputs": z.copy(),
+                          "pkt_effective_thr": z.copy(), "buffer_occupancies": z.copy(), "buffer_latencies": z.copy(),
+                          "dropped_pkts": z.copy()})
+            else:
+                f.update({"sched_decision": scheds[e], "pkt_incoming": raw["pkt_incoming"][e],
+                          "pkt_throughputs": raw["pkt_throughputs"][e],
+                          "pkt_effective_thr": raw["sent"][e].astype(np.int64), "buffer_occupancies": raw["occ"][e],
+                          "buffer_latencies": raw["lat"][e], "dropped_pkts": raw["dropped"][e].astype(np.int64),
+                          "agent_action": actions[e]})
+            frames.append(f)
+        return frames
+
+    def _step_callbacks(self, action):
+        eng = self._engine()
+        obs_fmt, act_fmt, rew_fn = self._callbacks
+        E = self.num_envs
+        acts = [action] if E == 1 else list(action)
+        if len(acts) != E:
+            raise ValueError(f"expected one action per env ({E})")
+        scheds, bits = [], np.zeros((E, 25, 5), np.uint32)
+        weights = (1 << np.arange(32, dtype=np.uint64))
+        for e in range(E):
+            sd = np.asarray(act_fmt(acts[e]), np.float64)  # comm_env.py:300
+            if sd.shape != (1, 25, 135):
+                raise ValueError("action_format must return the scheduling matrix [1, 25, 135] (comm_env.py:271-296)")
+            scheds.append(sd)
+            m = np.zeros((25, 160), np.uint64)
+            m[:, :135] = sd[0] != 0
+            bits[e] = (m.reshape(25, 5, 32) * weights).sum(axis=2).astype(np.uint32)
+        se, tr = self._hook_frames()
+        eng.step(se=se, traffic=tr, sched_bits=bits)
+        self._check()
+        frames = self._raw_frames(scheds, acts)
+        obs = [obs_fmt(f) for f in frames]      # comm_env.py:340
+        rew = [rew_fn(f) for f in frames]       # comm_env.py:341
+        done = eng.v["out_done"].cpu().numpy().astype(bool)
+        if E > 1:
+            return obs, rew, done, done.copy(), [{} for _ in range(E)]
+        d = bool(done[0])
+        if isinstance(action, dict):            # marl_comm_env.py:51-66
+            term = {a: d for a in sorted(self.agents)}
+            term["__all__"] = d
+            return obs[0], rew[0], term, dict(term), {}
+        return obs[0], rew[0], d, d, {}
+
     def step(self, action):
+        if self._callbacks is not None:
+            return self._step_callbacks(action)
         eng = self._engine()
         a0, intra = self._parse_action(action)
         se, tr = self._hook_frames()
@@ -290,6 +394,10 @@ class BatchedMARLCommEnv:
                 raise ValueError("Invalid intra-slice scheduling action")
             if code & capi.ERR_EPISODE_RANGE:
                 raise Exception("Episode number received is greater than the maximum number of episodes")
+            if code & capi.ERR_RB_SHARED:  # comm_env.py:593-596
+                raise Exception("Scheduling decision allocated the same RB for more than one UE")
+            if code & capi.ERR_TRACE_EPISODE:
+                raise Exception(f"env {env}: its episode has no channel file in the SE bank (channel_episodes)")
             raise Exception(f"env {env}: scheduling decision violates the RB invariants (code {code})")
 
     def _format_obs(self):

@@ -68,13 +68,15 @@ class QuadrigaChannel:
 
     Device mode: the files of `episodes` are transformed once (irs_power_to_se) into a float64
     [n_episodes, n_steps, 25, 135] bank that stays in HBM (irs_set_se_trace, channel_mode 3); an env in
-    episode `ep` reads bank slot `ep % n_episodes`.  Supply the powers either as .mat files under
-    root_path (needs h5py, like the reference) or through `register_power(power)` with an array
-    [n_episodes, n_steps, 135, 25] (the file order) - e.g. synthetic or pre-converted data."""
+    episode `ep` reads bank slot `ep - first_episode` (an episode outside the bank is an error, never another
+    episode's file).  Supply the powers either as .mat files under root_path (needs h5py, like the reference) or
+    through `register_power(power, first_episode)` with an array [n_episodes, n_steps, 135, 25] (the file order) -
+    e.g. synthetic or pre-converted data."""
     device_mode = {"channel_mode": 3}
     transmission_power, thermal_noise_power = 100.0, 10e-14  # quadriga.py:33-34
     channel_eps_per_scenario = 100
     _registered = None
+    _registered_first = 0
 
     def __init__(self, max_number_ues, max_number_basestations, num_available_rbs, rng=np.random.default_rng(),
                  root_path="", scenario_name="mult_slice"):
@@ -83,12 +85,14 @@ class QuadrigaChannel:
         self.current_episode_number, self._power = -1, None
 
     @classmethod
-    def register_power(cls, power):
-        """Use an in-memory array [n_episodes, n_steps, 135, 25] instead of .mat files."""
+    def register_power(cls, power, first_episode=0):
+        """Use an in-memory array [n_episodes, n_steps, 135, 25] instead of .mat files; power[i] is the file of env
+        episode first_episode + i."""
         power = np.ascontiguousarray(power, np.float64)
         if power.ndim != 4 or power.shape[2:] != (135, 25):
             raise ValueError("power must be [n_episodes, n_steps, 135, 25] (target_cell_power.mat order)")
         cls._registered = power
+        cls._registered_first = int(first_episode)
 
     @classmethod
     def choose_episode(cls, episode_number):
@@ -114,7 +118,10 @@ class QuadrigaChannel:
     def power_bank(cls, root_path, episodes):
         """Powers of `episodes` (env episode numbers) as [len(episodes), n_steps, 135, 25]."""
         if cls._registered is not None:
-            return cls._registered
+            idx = [int(ep) - cls._registered_first for ep in episodes]
+            if min(idx) < 0 or max(idx) >= len(cls._registered):
+                raise ValueError("an episode lies outside the registered power array")
+            return cls._registered[idx]
         return np.stack([cls.read_file(root_path, ep) for ep in episodes])
 
     def step(self, step_number, episode_number, mobilities, sched_decision=None):
@@ -122,7 +129,7 @@ class QuadrigaChannel:
         if episode_number != self.current_episode_number:
             self.current_episode_number = episode_number
             bank = type(self)._registered
-            self._power = (bank[episode_number % len(bank)] if bank is not None
+            self._power = (bank[episode_number - type(self)._registered_first] if bank is not None
                            else self.read_file(self.root_path, episode_number))
         p = self._power[step_number]
         se = np.log2(1 + np.divide((self.transmission_power / self.num_available_rbs[0]) * p,
@@ -133,6 +140,7 @@ class QuadrigaChannel:
 class QuadrigaChannelSeq(QuadrigaChannel):
     """channels/quadriga_seq.py:8-39: (association, episode) = (episode // 100, episode % 100)."""
     _registered = None
+    _registered_first = 0
 
     @classmethod
     def choose_episode(cls, episode_number):

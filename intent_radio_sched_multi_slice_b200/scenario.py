@@ -75,6 +75,59 @@ def _operator_name(op) -> str:
     return {"greater_equal": "at_least", "less_equal": "at_most"}.get(getattr(op, "__name__", ""), "unsupported")
 
 
+_OPERATORS = {"at_least": np.greater_equal, "at_most": np.less_equal}
+
+
+def callable_req(slice_req: dict) -> dict:
+    """A slice_req dict with the operators as the reference holds them in memory (NumPy ufuncs,
+    associations/mult_slice.py:48-55), for agent callbacks that call parameter["operator"](metric, value)
+    (agents/common.py:124-135).  Deep copy; names given as strings are mapped."""
+    out = {}
+    for k, v in slice_req.items():
+        if not v:
+            out[k] = {}
+            continue
+        w = dict(v)
+        w["ues"] = dict(v["ues"])
+        w["parameters"] = {pk: dict(pv, operator=_OPERATORS.get(pv["operator"], pv["operator"]))
+                           for pk, pv in v.get("parameters", {}).items()}
+        out[k] = w
+    return out
+
+
+def req_from_row(row) -> tuple[dict, np.ndarray]:
+    """(slice_req, slice_ue_assoc [5, 25]) of a dense scenario row - what Association.step returns for it
+    (association.py:60-109).  Used where the row was generated on the device (assoc_mode 2) and no dict exists."""
+    sua = np.zeros((MAX_SLICES, MAX_UES))
+    for u in range(MAX_UES):
+        if row["ue_slice"][u] >= 0:
+            sua[int(row["ue_slice"][u]), u] = 1
+    req = {}
+    for s in range(MAX_SLICES):
+        sl = row["sl"][s]
+        if not (int(sl["flags"]) & F_REQ):
+            req[f"slice_{s}"] = {}
+            continue
+        params = {}
+        for flag, name, key, unit, op in ((F_REL, "reliability", "rel_value", "rate", "at_least"),
+                                         (F_LAT, "latency", "lat_value", "ms", "at_most"),
+                                         (F_THR, "throughput", "thr_value", "Mbps", "at_least")):
+            if int(sl["flags"]) & flag:
+                params[f"par{len(params) + 1}"] = {"name": name, "value": float(sl[key]), "unit": unit, "operator": op}
+        ues = {"buffer_size": int(sl["buffer_size"]), "buffer_latency": int(sl["buffer_latency"]),
+               "message_size": int(sl["message_size"]), "traffic": float(sl["traffic"])}
+        name = "custom"
+        for t in SLICE_TYPES:  # the slice type with these parameters, when there is one
+            ref = slice_req_from_type(SLICE_TYPE_NAMES.index(t[0]))
+            if all(ref["ues"][k] == ues[k] for k in ues) and ref["priority"] == sl["priority"] and \
+                    {p["name"]: p["value"] for p in ref["parameters"].values()} == {p["name"]: p["value"] for p in params.values()}:
+                name = t[0]
+                ues = dict(ref["ues"])
+                break
+        req[f"slice_{s}"] = {"name": name, "priority": int(sl["priority"]), "parameters": params, "ues": ues}
+    return req, sua
+
+
 class ScenarioBank:
     """Dense table of scenarios + the Poisson CDF tables their traffic classes need."""
 

@@ -86,7 +86,7 @@ typedef struct {
     const double *poisson_cdf; /* [n_lambda][POISSON_K] */
     orc_scenario *own_bank;    /* assoc_mode 2: templates + two generated rows per env */
     const double *se_bank;     /* channel_mode 3: [bank_eps][bank_steps][U][R] (channels/quadriga.py) */
-    int32_t bank_eps, bank_steps;
+    int32_t bank_eps, bank_steps, bank_first, bank_wrap;
     const int32_t *ep_order;   /* random_episodes with a given order: [E][ep_order_n] */
     int32_t ep_order_n;
 } orc_handle;
@@ -315,6 +315,7 @@ typedef struct {
  * Fills frame->{sent,dropped,occ,lat,sebar}. */
 static void ues_step(const orc_handle *h, int e, const orc_scenario *sc, const double *se,
                      const double *traffic, const int16_t *rb_start, const int16_t *rb_count,
+                     const uint32_t *sched_bits /* [U][5] or NULL: a scheduling matrix given directly */,
                      orc_frame *fr, orc_ue_aux *aux)
 {
     const double bw_rb = h->cfg.bandwidth / (double)R; /* ues.py:110 */
@@ -323,7 +324,8 @@ static void ues_step(const orc_handle *h, int e, const orc_scenario *sc, const d
         ue_params(sc, u, &depth, &max_pkts, &pkt_bits);
         double terms[R];
         for (int r = 0; r < R; ++r) {
-            double sched = (r >= rb_start[u] && r < rb_start[u] + rb_count[u]) ? 1.0 : 0.0;
+            double sched = sched_bits ? (double)((sched_bits[u * 5 + (r >> 5)] >> (r & 31)) & 1u)
+                                      : ((r >= rb_start[u] && r < rb_start[u] + rb_count[u]) ? 1.0 : 0.0);
             terms[r] = (bw_rb * sched) * se[u * R + r];
         }
         double thr = floor(np_sum(terms, R) / pkt_bits); /* ues.py:108-116 */
@@ -865,7 +867,10 @@ static void channel_frame(const orc_handle *h, int e, const orc_env *env, int fr
          * (0 at reset AND at the first step: comm_env.py:303-305 runs before step_number += 1) */
         int k = frame > 0 ? frame - 1 : 0;
         k %= h->bank_steps; /* a trace shorter than the episode wraps around */
-        memcpy(se, h->se_bank + ((size_t)(env->episode % h->bank_eps) * h->bank_steps + k) * U * R, sizeof(double) * U * R);
+        int slot = env->episode - h->bank_first;   /* the reference opens this episode's own file (quadriga.py:46-55, 78-87) */
+        if (h->bank_wrap) { slot %= h->bank_eps; if (slot < 0) slot += h->bank_eps; }
+        else if (slot < 0 || slot >= h->bank_eps) slot = 0; /* the CUDA path flags this (ERR_TRACE_EPISODE) */
+        memcpy(se, h->se_bank + ((size_t)slot * h->bank_steps + k) * U * R, sizeof(double) * U * R);
     } else if (h->cfg.channel_mode == 1) {
         for (int i = 0; i < U * R; ++i) se[i] = 2.0; /* channels/fixed_se.py:26 */
     } else {
@@ -963,14 +968,16 @@ static int reset_one(orc_handle *h, int e, int initial_episode, const double *se
     return 0;
 }
 static int step_one(orc_handle *h, int e, const double *a0_in, const int32_t *intra_in, const double *se_in,
-                    const double *traffic_in, const orc_io *io)
+                    const double *traffic_in, const uint32_t *sched_in, const orc_io *io)
 {
     orc_env *env = &h->envs[e];
     const orc_config *c = &h->cfg;
     const orc_scenario *sc = &h->bank[env->scen];
     int gid = c->env_id_base + e;
-    double a0[S]; int32_t intra[S] = {0, 0, 0, 0, 0};
-    if (c->policy == 0) {
+    double a0[S] = {0, 0, 0, 0, 0}; int32_t intra[S] = {0, 0, 0, 0, 0};
+    const uint32_t *bits = sched_in ? sched_in + (size_t)e * U * 5 : NULL;
+    if (bits) { /* action_format ran outside (comm_env.py:300 with the caller's own callback) */ }
+    else if (c->policy == 0) {
         memcpy(a0, a0_in + (size_t)e * S, sizeof(a0));
         if (intra_in) memcpy(intra, intra_in + (size_t)e * S, sizeof(intra));
     } else if (c->policy == 1) policy_marr(sc, a0);
@@ -979,6 +986,16 @@ static int step_one(orc_handle *h, int e, const double *a0_in, const int32_t *in
     if (io->a0_used) memcpy(io->a0_used + (size_t)e * S, a0, sizeof(a0));
     if (io->intra_used) memcpy(io->intra_used + (size_t)e * S, intra, sizeof(intra));
     int16_t rb_start[U], rb_count[U]; int64_t rbs_per_slice[S];
+    if (bits) { /* the matrix is given: RBs per UE = its row sum (ib_sched.py:188-190 reads sched_decision) */
+        uint32_t seen[5] = {0, 0, 0, 0, 0};
+        for (int u = 0; u < U; ++u) {
+            int cnt = 0, first = 0;
+            for (int r = R - 1; r >= 0; --r)
+                if ((bits[u * 5 + (r >> 5)] >> (r & 31)) & 1u) { ++cnt; first = r; }
+            rb_start[u] = (int16_t)first; rb_count[u] = (int16_t)cnt;
+            for (int w = 0; w < 5; ++w) { if (seen[w] & bits[u * 5 + w]) return -3; seen[w] |= bits[u * 5 + w]; } /* comm_env.py:593-596 */
+        }
+    } else
     if (action_format(h, env, sc, a0, intra, rb_start, rb_count, rbs_per_slice)) return -1; /* comm_env.py:300 */
     int frame = env->step + 1;
     double se[U * R], traffic[U];
@@ -990,7 +1007,7 @@ static int step_one(orc_handle *h, int e, const double *a0_in, const int32_t *in
                  ? native_traffic(h, env_key(c, env->visit), u, sc->sl[s].lam_idx, frame, env->episode, gid) : 0.0;
     }
     orc_frame fr; orc_ue_aux aux;
-    ues_step(h, e, sc, se, traffic, rb_start, rb_count, &fr, &aux); /* :320-326 */
+    ues_step(h, e, sc, se, traffic, rb_start, rb_count, bits, &fr, &aux); /* :320-326 */
     env->step += 1;                                            /* :339 */
     window_push(env, &fr);
     if (c->surface) window_push(env, &fr);                     /* sched_twc.py:176-179: the frame is pushed twice */
@@ -1062,9 +1079,9 @@ void orc_set_episode_order(orc_handle *h, const int32_t *order, int32_t n)
         for (int e = 0; e < h->cfg.num_envs; ++e)
             h->envs[e].episode = order[(size_t)e * n + h->envs[e].ep_pos % n];
 }
-void orc_set_se_trace(orc_handle *h, const double *bank, int32_t n_eps, int32_t n_steps)
+void orc_set_se_trace(orc_handle *h, const double *bank, int32_t n_eps, int32_t n_steps, int32_t first, int32_t wrap)
 {
-    h->se_bank = bank; h->bank_eps = n_eps; h->bank_steps = n_steps;
+    h->se_bank = bank; h->bank_eps = n_eps; h->bank_steps = n_steps; h->bank_first = first; h->bank_wrap = wrap;
 }
 /* channels/quadriga.py:56-74 on one frame in file order [R][U] -> SE [U][R] */
 void orc_power_to_se(const double *power, double *se, int64_t n_frames, int layout, double tx_power, double noise)
@@ -1092,12 +1109,12 @@ int orc_reset(orc_handle *h, const uint8_t *mask, int initial_episode, const dou
     return rc;
 }
 int orc_step(orc_handle *h, const double *a0, const int32_t *intra, const double *se, const double *traffic,
-             const orc_io *io)
+             const uint32_t *sched_bits /* [E][U][5] or NULL */, const orc_io *io)
 {
     int rc = 0;
 #pragma omp parallel for schedule(static) reduction(min : rc)
     for (int e = 0; e < h->cfg.num_envs; ++e) {
-        int r = step_one(h, e, a0, intra, se, traffic, io);
+        int r = step_one(h, e, a0, intra, se, traffic, sched_bits, io);
         if (r < rc) rc = r;
     }
     return rc;

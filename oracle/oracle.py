@@ -55,11 +55,11 @@ def lib():
         _lib.orc_create.argtypes = [C.POINTER(Config), C.c_void_p, C.c_void_p]
         _lib.orc_destroy.argtypes = [C.c_void_p]
         _lib.orc_get_scenario.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
-        _lib.orc_set_se_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32]
+        _lib.orc_set_se_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32]
         _lib.orc_set_episode_order.argtypes = [C.c_void_p, C.c_void_p, C.c_int32]
         _lib.orc_power_to_se.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_double, C.c_double]
         _lib.orc_reset.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.POINTER(IO)]
-        _lib.orc_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(IO)]
+        _lib.orc_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(IO)]
         _lib.orc_buffers.restype = C.POINTER(C.c_int32)
         _lib.orc_buffers.argtypes = [C.c_void_p]
         _lib.orc_get_state.argtypes = [C.c_void_p] * 4
@@ -167,11 +167,13 @@ class OracleEnv:
         }
         self._io = None
 
-    def set_se_trace(self, se_bank):
-        """channel_mode 3: float64 [n_episodes, n_steps, 25, 135] (kept alive by this object)."""
+    def set_se_trace(self, se_bank, first_episode=0, wrap=False):
+        """channel_mode 3: float64 [n_episodes, n_steps, 25, 135] (kept alive by this object); slot i = env episode
+        first_episode + i (modulo n_episodes with `wrap`)."""
         self._se_bank = np.ascontiguousarray(se_bank, np.float64)
         assert self._se_bank.ndim == 4 and self._se_bank.shape[2:] == (U, R)
-        lib().orc_set_se_trace(self.h, _ptr(self._se_bank), self._se_bank.shape[0], self._se_bank.shape[1])
+        lib().orc_set_se_trace(self.h, _ptr(self._se_bank), self._se_bank.shape[0], self._se_bank.shape[1],
+                               int(first_episode), int(bool(wrap)))
 
     def set_episode_order(self, order):
         """random_episodes with a given order: int32 [E, n] (kept alive by this object); None = built-in permutation."""
@@ -207,12 +209,14 @@ class OracleEnv:
             raise RuntimeError(f"oracle reset failed rc={rc}")
         return self.out
 
-    def step(self, a0=None, intra=None, se=None, traffic=None):
+    def step(self, a0=None, intra=None, se=None, traffic=None, sched_bits=None):
+        """sched_bits: uint32 [E, 25, 5] - a scheduling matrix given directly (bit r of the 135-bit row = RB r)."""
+        sched_bits = None if sched_bits is None else np.ascontiguousarray(sched_bits, np.uint32)
         a0 = None if a0 is None else np.ascontiguousarray(a0, np.float64)
         intra = None if intra is None else np.ascontiguousarray(intra, np.int32)
         se = None if se is None else np.ascontiguousarray(se, np.float64)
         traffic = None if traffic is None else np.ascontiguousarray(traffic, np.float64)
-        rc = lib().orc_step(self.h, _ptr(a0), _ptr(intra), _ptr(se), _ptr(traffic), C.byref(self._get_io()))
+        rc = lib().orc_step(self.h, _ptr(a0), _ptr(intra), _ptr(se), _ptr(traffic), _ptr(sched_bits), C.byref(self._get_io()))
         if rc:
             raise RuntimeError(f"oracle step failed rc={rc}")
         return self.out

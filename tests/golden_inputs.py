@@ -183,3 +183,16 @@ def quadriga_bank_powers(meta, d, n_eps=8):
         a, f = quadriga_file_of_episode(meta["channel"], int(e))
         power[e % n_eps] = quadriga_power(a, f, T)[:, :, 0, 0, :]
     return power
+
+
+def quadriga_episode_powers(meta, d):
+    """The same files laid out the way the env surface wants them (QuadrigaChannel.register_power): one slot per env
+    episode of the contiguous range the trace visits, slot = episode - first.  Returns (first_episode, power)."""
+    T = int(meta["max_steps"])
+    eps = sorted(set(d["episode"].tolist()) | set(d["reset_episode"].tolist()))
+    first, last = int(eps[0]), int(eps[-1])
+    power = np.zeros((last - first + 1, T, R, U))
+    for e in range(first, last + 1):
+        a, f = quadriga_file_of_episode(meta["channel"], e)
+        power[e - first] = quadriga_power(a, f, T)[:, :, 0, 0, :]
+    return first, power

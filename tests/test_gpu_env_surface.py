@@ -51,7 +51,8 @@ def test_env_api_replays_reference_trace(name, agent, n, bank):
     Ch, Tr, state = _trace_plugins(rse, sse, stf)
     if meta["channel"].startswith("quadriga"):  # the built-in device channel: SE bank in HBM (channel_mode 3)
         Ch = plugins.QuadrigaChannel if meta["channel"] == "quadriga" else plugins.QuadrigaChannelSeq
-        Ch.register_power(golden_inputs.quadriga_bank_powers(meta, d))
+        first, power = golden_inputs.quadriga_episode_powers(meta, d)  # slot = episode - first (first = 3 / 99 here)
+        Ch.register_power(power, first_episode=first)
     Assoc = plugins.MultSliceAssociation if meta["assoc"] == "mult_slice" else plugins.MultSliceAssociationSeq
     env = MARLCommEnv(Ch, Tr, plugins.SimpleMobility, Assoc, "mult_slice", agent.lower(), int(meta["seed"]),
                       root_path="/nonexistent", initial_episode_number=int(meta["initial_episode"]),
@@ -117,8 +118,32 @@ def test_env_api_errors_like_the_reference(bank):
     bad.update({f"player_{i}": 7 for i in range(1, 6)})
     with pytest.raises(ValueError, match="Invalid intra-slice scheduling action"):  # ib_sched.py:341-344
         env.step(bad)
-    with pytest.raises(NotImplementedError):
-        env.set_agent_functions(lambda o: o, lambda a: a, lambda o: 0.0)
+    env.close()
+
+
+def test_trace_channel_episode_outside_the_bank_raises(bank):
+    """An env that reaches an episode whose channel file is not in the SE bank raises (debug=True) instead of
+    replaying another episode's file (the reference opens a new file per episode, channels/quadriga.py:46-55)."""
+    from intent_radio_sched_multi_slice_b200 import agents, plugins
+    from intent_radio_sched_multi_slice_b200.env import MARLCommEnv
+
+    meta, d = golden_inputs.load_trace("quadriga")
+    first, power = golden_inputs.quadriga_episode_powers(meta, d)
+    plugins.QuadrigaChannel.register_power(power[:2], first_episode=first)
+    env = MARLCommEnv(plugins.QuadrigaChannel, plugins.MultSliceTraffic, plugins.SimpleMobility,
+                      plugins.MultSliceAssociation, "mult_slice", "ib_sched", 10, save_hist=False, scenario_bank=bank,
+                      root_path="/nonexistent", initial_episode_number=first, debug=True)
+    env.max_number_steps = 3
+    env.reset(options={"initial_episode": first})
+    act = {"player_0": np.zeros(5)}
+    act.update({f"player_{i}": 0 for i in range(1, 6)})
+    for ep in range(2):
+        for k in range(3):
+            env.step(act)
+        if ep == 0:
+            env.reset()
+    with pytest.raises(Exception, match="no channel file"):
+        env.reset()
     env.close()
 
 

@@ -37,7 +37,7 @@ def test_cuda_power_to_se_and_bank_mode_match_reference(name, bank):
                       assoc_mode=0 if meta_["assoc"] == "mult_slice" else 1, max_steps=int(meta_["max_steps"]),
                       max_episodes=int(meta_["max_episodes"]), initial_episode=int(meta_["initial_episode"]))
         se_bank = env.eng.power_to_se(torch.from_numpy(power).to(env.eng.device), layout=0)
-        env.eng.set_se_trace(se_bank)
+        env.eng.set_se_trace(se_bank, wrap=True)
         made["bank"] = se_bank.cpu().numpy()
         return BankEnv(env)
 
@@ -67,12 +67,12 @@ def test_batch_trace_bank_matches_oracle(bank, raw_se):
     kw = dict(channel_mode=3, traffic_mode=1, policy=3, fixed_intra=-1, sort_slices=1, assoc_mode=0, max_steps=T,
               auto_reset=1, env_id_base=77, seed=99, initial_episode=0)
     orc = oracle.OracleEnv(bank.array(), bank.poisson_cdf(), E, depth_cap=404, **kw)
-    orc.set_se_trace(se_bank)
+    orc.set_se_trace(se_bank, wrap=True)
     gpu = CudaEnv(bank, E, depth_cap=401, **kw)
     if not raw_se:  # drop the per-RB output: the production kernel skips rows of unassociated UEs
         gpu.raw = gpu.eng.enable_raw_outputs([n for n in gpu.raw if n != "se_used"])
         gpu.raw["se_used"] = None
-    gpu.eng.set_se_trace(torch.from_numpy(se_bank).to(gpu.eng.device))
+    gpu.eng.set_se_trace(torch.from_numpy(se_bank).to(gpu.eng.device), wrap=True)
     ie = (np.arange(E) % 7 + 2).astype(np.int32)
     for e in range(E):
         m = np.zeros(E, np.uint8)
