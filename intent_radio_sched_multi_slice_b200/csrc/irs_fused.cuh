@@ -21,6 +21,22 @@
 #endif
 #define GRP 4         /* UE rows generated per group */
 
+// The 4 KB normal table of the generators goes to shared memory with cp.async at kernel entry and is waited for right
+// before the generators run, so the copy overlaps the prologue's record loads.
+__device__ __forceinline__ void normal_tab_request(float2* ntab)
+{
+    const char* src = reinterpret_cast<const char*>(g_normal_tab);
+    const uint32_t dst = (uint32_t)__cvta_generic_to_shared(ntab);
+    for (int i = threadIdx.x; i < IRS_NORMAL_TAB_N / 2; i += blockDim.x)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16 * i), "l"(src + 16 * i));
+    asm volatile("cp.async.commit_group;");
+}
+__device__ __forceinline__ void normal_tab_wait()
+{
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+}
+
 template <typename T>
 __device__ __forceinline__ T sel4(const T (&a)[GRP], int j)
 {
@@ -40,7 +56,7 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
     const int split = A.ue_split_log2, gmask = (1 << split) - 1;
     const int wglob = blockIdx.x * FUSED_WARPS + wib;
     const int e = A.env_begin + (wglob >> split), grp = wglob & gmask; // this warp serves the UEs u with (u & gmask) == grp
-    if (e >= A.env_end) return;
+    if (e >= A.env_end) { normal_tab_wait(); return; } // every warp of the block meets the table barrier exactly once
 
     // ---- phase 0: env scalars, this lane's UE record, and the ring slots the step can touch -------
     const int step = st.step[e], episode = st.episode[e];
@@ -76,6 +92,7 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
     const short2 run = st.rb[eu];
     const int rb_s = run.x, rb_c = run.y;
 
+    normal_tab_wait(); // the generators' table, requested at kernel entry, is in shared memory from here on
     // ---- phase 2: channel + traffic of this frame, and the two row sums per UE --------------
     const bool native = cfg.channel_mode == 2 && cfg.traffic_mode == 1;
     const int fl_mine = s_mine >= 0 ? __ldg(&sc->sl[s_mine].flags) : 0;
@@ -87,109 +104,96 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
         else if (has_traffic) traffic = native_traffic(key, st.cdf, lane, lam_idx, frame, episode, gid);
     }
     if (native) {
-        // Per-warp scratch in shared memory: tail (SE, throughput term) pairs of the group's rows at
-        // ws[16 j .. 16 j + 13], per-UE results (sum_t, sum_se, traffic) at ws[64 + 4 u ..].
+        // Per-warp scratch in shared memory: tail (SE, throughput term) pairs of UE u at ws[14 u .. 14 u + 13],
+        // per-UE results (sum_t, sum_se) at ws[352 + 4 u ..].
         double* ws = &sm[wib][0][0];
-        uint32_t todo = __ballot_sync(FULL, ue_lane && s_mine >= 0);
-        while (todo != 0) { // warp-uniform
-            uint32_t ulp = 0; // lane ids of the group's UEs, one byte each
-            int n = 0;
+        const bool gen = ue_lane && s_mine >= 0; // an unassociated UE has SE 0 and no traffic in native mode
+        // pass A, lane = UE: the per-episode mean (mimic_quadriga.py:37-41), the serial tail of the row (RBs 128..134,
+        // SE quad 16) with its throughput terms, and the Poisson arrival (traffics/mult_slice.py:28-31)
+        if (gen) {
+            const uint4 wm = rng_quad(key, K_MU, lane, 0, 0, episode, gid);
+            mu_l = fabs(__fma_rn(7.5, (double)normal_lo(wm.x, ntab), 10.0));
+            const uint4 wt = rng_quad(key, K_SE, lane, 16, frame, episode, gid);
+            const uint32_t ww[4] = {wt.x, wt.y, wt.z, wt.w};
+            const uint32_t* sb = (RAWSE && A.sched_bits) ? A.sched_bits + eu * 5 : nullptr;
+            double2* tp = reinterpret_cast<double2*>(ws + 14 * lane);
 #pragma unroll
-            for (int j = 0; j < GRP; ++j)
-                if (todo) { ulp |= (uint32_t)(__ffs(todo) - 1) << (8 * j); ++n; todo &= todo - 1; }
-            // auxiliary pass: lane 8j+k serves UE j of the group.  Lane 8j draws the tail quad (RBs 128..134),
-            // lane 8j+1 the per-episode mean, lane 8j+2 the Poisson arrival; then lane 8j+k turns half-word k
-            // of the tail quad into RB 128+k.
-            {
-                const int j = lane >> 3, k = lane & 7;
-                const bool valid = j < n;
-                const int ue_j = (ulp >> (8 * j)) & 31;
-                const int kind = k == 1 ? K_MU : (k == 2 ? K_TRAFFIC : K_SE);
-                const uint4 w = rng_quad(key, kind, ue_j, k == 0 ? 16 : 0, k == 1 ? 0 : frame, episode, gid);
-                mu_l = fabs(__fma_rn(7.5, (double)normal_lo(w.x, ntab), 10.0)); // meaningful on k == 1 (mimic_quadriga.py:37-41)
-                const double mu_aux = __shfl_sync(FULL, mu_l, 8 * j + 1);
-                const uint32_t t0 = __shfl_sync(FULL, w.x, 8 * j), t1 = __shfl_sync(FULL, w.y, 8 * j);
-                const uint32_t t2 = __shfl_sync(FULL, w.z, 8 * j), t3 = __shfl_sync(FULL, w.w, 8 * j);
-                const uint32_t wk = (k & 4) ? ((k & 2) ? t3 : t2) : ((k & 2) ? t1 : t0); // word k >> 1 of the tail quad
-                const float z = (k & 1) ? normal_hi(wk, ntab) : normal_lo(wk, ntab);
-                const int rs_a = __shfl_sync(FULL, rb_s, ue_j), rc_a = __shfl_sync(FULL, rb_c, ue_j);
-                if (valid && k < 7) {
-                    const double x = fabs(__fma_rn(1.5, (double)z, mu_aux));
-                    const uint32_t* sb = (RAWSE && A.sched_bits) ? A.sched_bits + ((size_t)e * U + ue_j) * 5 : nullptr;
-                    reinterpret_cast<double2*>(ws + 16 * j)[k] = make_double2(x, sched_at(sb, rs_a, rc_a, 128 + k) ? A.bw_rb * x : 0.0);
-                }
-                // Poisson arrival of UE j on lane 8j+2 (traffics/mult_slice.py:28-31)
-                const int lam_j = __shfl_sync(FULL, lam_idx, ue_j);
-                const int ht_j = __shfl_sync(FULL, (int)has_traffic, ue_j);
-                if (valid && k == 2) {
-                    int lo = 0;
-                    if (ht_j) {
-                        const double u01 = ((double)(w.x >> 5) * 67108864.0 + (double)(w.y >> 6)) * (1.0 / 9007199254740992.0);
-                        const double* cdf = st.cdf + (size_t)lam_j * IRS_POISSON_K;
-#pragma unroll
-                        for (int stp = IRS_POISSON_K / 2; stp > 0; stp >>= 1)
-                            if (__ldg(&cdf[lo + stp - 1]) <= u01) lo += stp;
-                        if (__ldg(&cdf[lo]) <= u01) lo += 1;
-                    }
-                    ws[64 + 4 * ue_j + 2] = (double)lo * 1e6;
-                }
+            for (int k = 0; k < 7; ++k) {
+                const float z = (k & 1) ? normal_hi(ww[k >> 1], ntab) : normal_lo(ww[k >> 1], ntab);
+                const double x = fabs(__fma_rn(1.5, (double)z, mu_l));
+                tp[k] = make_double2(x, sched_at(sb, rb_s, rb_c, 128 + k) ? A.bw_rb * x : 0.0);
+                if (RAWSE && A.raw.se_used) A.raw.se_used[eu * R + 128 + k] = x;
             }
-            __syncwarp();
-            // pair passes: lanes 0..15 serve UE ul[2p], lanes 16..31 UE ul[2p+1].  Lane m of a side
-            // generates SE quad m = the 8 elements accumulator m & 7 of row half m >> 3 visits
-            // (se_index), and adds them up in registers in NumPy's order: both 135-term sums
-            // (ues.py:108-116 throughput terms, np.mean(SE)) without a shared-memory row.
-#pragma unroll 1
-            for (int pp = 0; 2 * pp < n; ++pp) {
-                const int side = lane >> 4;
-                const bool live = 2 * pp + side < n;      // odd n: side 1 of the last pass shadows side 0
-                const int jj = live ? 2 * pp + side : 2 * pp;
-                const int uj = (ulp >> (8 * jj)) & 31;
-                const double mu = __shfl_sync(FULL, mu_l, 8 * jj + 1);
-                const int rs = __shfl_sync(FULL, rb_s, uj), rc = __shfl_sync(FULL, rb_c, uj);
-                const int l16 = lane & 15, base = ((l16 >> 3) << 6) + (l16 & 7);
-                const unsigned d0 = (unsigned)(base - rs);
-                double acc_se = 0.0, acc_t = 0.0;
-                double* se_out = (RAWSE && A.raw.se_used) ? A.raw.se_used + ((size_t)e * U + uj) * R : nullptr;
-                const uint4 wb = rng_quad(key, K_SE, uj, l16, frame, episode, gid);
-                const uint32_t ww[4] = {wb.x, wb.y, wb.z, wb.w};
-                const uint32_t* sb = (RAWSE && A.sched_bits) ? A.sched_bits + ((size_t)e * U + uj) * 5 : nullptr;
+            if (has_traffic) {
+                const uint4 wq = rng_quad(key, K_TRAFFIC, lane, 0, frame, episode, gid);
+                const double u01 = ((double)(wq.x >> 5) * 67108864.0 + (double)(wq.y >> 6)) * (1.0 / 9007199254740992.0);
+                const double* cdf = st.cdf + (size_t)lam_idx * IRS_POISSON_K;
+                int lo = 0;
 #pragma unroll
-                for (int k = 0; k < 8; ++k) {
-                    const float y = (k & 1) ? normal_hi(ww[k >> 1], ntab) : normal_lo(ww[k >> 1], ntab);
-                    const double x = fabs(__fma_rn(1.5, (double)y, mu)); // channels/mimic_quadriga.py:49-56
-                    const bool in_run = (RAWSE && sb) ? sched_at(sb, 0, 0, base + 8 * k)
-                                                     : d0 + 8u * k < (unsigned)rc; // ((BW/R) * sched) * SE; adding the 0.0 of an
-                    if (k == 0) { acc_se = x; acc_t = in_run ? A.bw_rb * x : 0.0; } // unscheduled RB changes nothing (terms >= 0)
-                    else { acc_se += x; if (in_run) acc_t += A.bw_rb * x; }
-                    if (RAWSE && se_out) se_out[base + 8 * k] = x;
-                }
-                acc_se = acc_se + __shfl_down_sync(FULL, acc_se, 1);
-                acc_t = acc_t + __shfl_down_sync(FULL, acc_t, 1);
-                acc_se = acc_se + __shfl_down_sync(FULL, acc_se, 2);
-                acc_t = acc_t + __shfl_down_sync(FULL, acc_t, 2);
-                acc_se = acc_se + __shfl_down_sync(FULL, acc_se, 4);
-                acc_t = acc_t + __shfl_down_sync(FULL, acc_t, 4);
-                const double2* tp = reinterpret_cast<const double2*>(ws + 16 * jj);
-                if (l16 == 8) { // second half: the 7-element tail is added serially after the tree
-#pragma unroll
-                    for (int k = 0; k < 7; ++k) {
-                        const double2 xt = tp[k];
-                        acc_se += xt.x;
-                        acc_t += xt.y;
-                    }
-                }
-                if (RAWSE && se_out && l16 < 7) se_out[128 + l16] = tp[l16].x;
-                const double res_se = 0. + (acc_se + __shfl_down_sync(FULL, acc_se, 8)); // valid on lanes 0, 16
-                const double res_t = 0. + (acc_t + __shfl_down_sync(FULL, acc_t, 8));
-                if (l16 == 0 && live) *reinterpret_cast<double2*>(ws + 64 + 4 * uj) = make_double2(res_t, res_se);
+                for (int stp = IRS_POISSON_K / 2; stp > 0; stp >>= 1)
+                    if (__ldg(&cdf[lo + stp - 1]) <= u01) lo += stp;
+                if (__ldg(&cdf[lo]) <= u01) lo += 1;
+                traffic = (double)lo * 1e6;
             }
-            __syncwarp();
         }
-        if (ue_lane && s_mine >= 0) {
-            const double2 r2 = *reinterpret_cast<const double2*>(ws + 64 + 4 * lane);
+        __syncwarp();
+        // pair passes: lanes 0..15 serve one associated UE, lanes 16..31 the next.  Lane m of a side generates
+        // SE quad m = the 8 elements accumulator m & 7 of row half m >> 3 visits (se_index), and adds them up in
+        // registers in NumPy's order: both 135-term sums (ues.py:108-116 throughput terms, np.mean(SE)) without a
+        // shared-memory row.
+        uint32_t todo = __ballot_sync(FULL, gen);
+#pragma unroll 1
+        while (todo != 0) { // warp-uniform
+            const int u0 = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const bool live1 = todo != 0;                 // odd count: side 1 of the last pass shadows side 0
+            const int u1 = live1 ? __ffs(todo) - 1 : u0;
+            todo &= todo - 1;
+            const int side = lane >> 4;
+            const int uj = side ? u1 : u0;
+            const bool live = side ? live1 : true;
+            const double mu = __shfl_sync(FULL, mu_l, uj);
+            const int rs = __shfl_sync(FULL, rb_s, uj), rc = __shfl_sync(FULL, rb_c, uj);
+            const int l16 = lane & 15, base = ((l16 >> 3) << 6) + (l16 & 7);
+            const unsigned d0 = (unsigned)(base - rs);
+            double acc_se = 0.0, acc_t = 0.0;
+            double* se_out = (RAWSE && A.raw.se_used) ? A.raw.se_used + ((size_t)e * U + uj) * R : nullptr;
+            const uint4 wb = rng_quad(key, K_SE, uj, l16, frame, episode, gid);
+            const uint32_t ww[4] = {wb.x, wb.y, wb.z, wb.w};
+            const uint32_t* sb = (RAWSE && A.sched_bits) ? A.sched_bits + ((size_t)e * U + uj) * 5 : nullptr;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const float y = (k & 1) ? normal_hi(ww[k >> 1], ntab) : normal_lo(ww[k >> 1], ntab);
+                const double x = fabs(__fma_rn(1.5, (double)y, mu)); // channels/mimic_quadriga.py:49-56
+                const bool in_run = (RAWSE && sb) ? sched_at(sb, 0, 0, base + 8 * k)
+                                                 : d0 + 8u * k < (unsigned)rc; // ((BW/R) * sched) * SE; adding the 0.0 of an
+                if (k == 0) { acc_se = x; acc_t = in_run ? A.bw_rb * x : 0.0; } // unscheduled RB changes nothing (terms >= 0)
+                else { acc_se += x; if (in_run) acc_t += A.bw_rb * x; }
+                if (RAWSE && se_out) se_out[base + 8 * k] = x;
+            }
+            acc_se = acc_se + __shfl_down_sync(FULL, acc_se, 1);
+            acc_t = acc_t + __shfl_down_sync(FULL, acc_t, 1);
+            acc_se = acc_se + __shfl_down_sync(FULL, acc_se, 2);
+            acc_t = acc_t + __shfl_down_sync(FULL, acc_t, 2);
+            acc_se = acc_se + __shfl_down_sync(FULL, acc_se, 4);
+            acc_t = acc_t + __shfl_down_sync(FULL, acc_t, 4);
+            if (l16 == 8) { // second half: the 7-element tail is added serially after the tree
+                const double2* tp = reinterpret_cast<const double2*>(ws + 14 * uj);
+#pragma unroll
+                for (int k = 0; k < 7; ++k) {
+                    const double2 xt = tp[k];
+                    acc_se += xt.x;
+                    acc_t += xt.y;
+                }
+            }
+            const double res_se = 0. + (acc_se + __shfl_down_sync(FULL, acc_se, 8)); // valid on lanes 0, 16
+            const double res_t = 0. + (acc_t + __shfl_down_sync(FULL, acc_t, 8));
+            if (l16 == 0 && live) *reinterpret_cast<double2*>(ws + 352 + 4 * uj) = make_double2(res_t, res_se);
+        }
+        __syncwarp();
+        if (gen) {
+            const double2 r2 = *reinterpret_cast<const double2*>(ws + 352 + 4 * lane);
             sum_t = r2.x; sum_se = r2.y;
-            traffic = ws[64 + 4 * lane + 2];
         }
     } else if (cfg.channel_mode != 2) {
         // Rows that come from memory (injected frame, SE trace bank) or are constant (fixed_se):
@@ -421,16 +425,6 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
     }
 }
 
-// the 4 KB normal table of the generators into shared memory, by the whole block (every warp of the block waits
-// here, so no warp may leave before this point)
-__device__ __forceinline__ void load_normal_tab(float2* ntab)
-{
-    const uint4* src = reinterpret_cast<const uint4*>(g_normal_tab);
-    uint4* dst = reinterpret_cast<uint4*>(ntab);
-    for (int i = threadIdx.x; i < IRS_NORMAL_TAB_N / 2; i += blockDim.x) dst[i] = __ldg(src + i);
-    __syncthreads();
-}
-
 #ifndef UE_ENV_MINB
 #define UE_ENV_MINB 8 /* 64 registers: 32 warps per SM measured fastest (profiles/r1_notes.md) */
 #endif
@@ -438,7 +432,7 @@ __global__ void __launch_bounds__(FUSED_WARPS * 32, UE_ENV_MINB) k_ue_env(const 
 {
     __shared__ __align__(16) double sm[FUSED_WARPS][GRP][136];
     __shared__ __align__(16) float2 ntab[IRS_NORMAL_TAB_N];
-    load_normal_tab(ntab);
+    normal_tab_request(ntab);
     ue_env_body<false>(A, sm, ntab);
 }
 // same kernel with the optional per-RB SE output (irs_raw_outputs.se_used; tests and trace dumps)
@@ -446,6 +440,6 @@ __global__ void __launch_bounds__(FUSED_WARPS * 32, UE_ENV_MINB) k_ue_env_raw(co
 {
     __shared__ __align__(16) double sm[FUSED_WARPS][GRP][136];
     __shared__ __align__(16) float2 ntab[IRS_NORMAL_TAB_N];
-    load_normal_tab(ntab);
+    normal_tab_request(ntab);
     ue_env_body<true>(A, sm, ntab);
 }

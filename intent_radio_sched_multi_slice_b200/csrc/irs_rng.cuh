@@ -72,7 +72,7 @@ __device__ __noinline__ int shuffled_episode(uint64_t seed, int gid, int gen, in
 }
 
 // ---- 16-bit inverse-CDF normal -------------------------------------------------------------------
-__device__ const uint32_t g_normal_tab[2 * IRS_NORMAL_TAB_N] = { IRS_NORMAL_TAB_WORDS };
+__device__ __align__(16) const uint32_t g_normal_tab[2 * IRS_NORMAL_TAB_N] = { IRS_NORMAL_TAB_WORDS };
 
 // m = 15-bit magnitude word, signbit = 0 or 0x80000000; tab = the (c0, c1) table (shared or global memory)
 __device__ __forceinline__ float normal_from(uint32_t m, uint32_t signbit, const float2* __restrict__ tab)

@@ -32,7 +32,7 @@ class BatchedMARLCommEnv:
                  calculate_reward=None, obs_space=None, action_space=None, debug=True, root_path=".",
                  initial_episode_number=0, max_episode_number=None, simu_name=None, save_hist=True,
                  enable_random_episodes=False, *, num_envs=1, device="cuda:0", scenario_bank=None,
-                 auto_reset=None, env_id_base=0, channel_episodes=None, hist_envs=None, hist_with_se=False,
+                 auto_reset=None, env_id_base=0, channel_episodes=None, hist_envs=None, hist_with_se=True,
                  hist_root_path=None):
         path = os.path.join(root_path, "env_config", f"{config_file}.yml")
         if not os.path.exists(path):
@@ -61,6 +61,8 @@ class BatchedMARLCommEnv:
         # `hist_envs` (default: the single env of a MARLCommEnv; nothing for a batch unless asked)
         self.save_hist = bool(save_hist)
         self.hist_envs = hist_envs
+        # spectral_efficiencies in the history files: results/gen_results.py:260-322 computes throughputs from this
+        # key, so it is recorded by default (27 MB of HBM per recorded env and 1000-step episode); False writes zeros
         self.hist_with_se = bool(hist_with_se)
         self.hist_root_path = hist_root_path if hist_root_path is not None else \
             data["simulation"].get("hist_root_path", "./")  # comm_env.py:211,682
@@ -134,7 +136,8 @@ class BatchedMARLCommEnv:
             self.eng = BatchEngine(self.bank, self.num_envs, device=self.device, sort_slices=s.sort_slices,
                                    fixed_intra=s.fixed_intra, policy=s.policy, surface=s.surface, max_steps=self.max_number_steps,
                                    max_episodes=self.max_number_episodes, initial_episode=self.initial_episode_number,
-                                   auto_reset=int(self.auto_reset), env_id_base=self.env_id_base, seed=self.seed,
+                                   auto_reset=int(self.auto_reset and not self._records()), env_id_base=self.env_id_base,
+                                   seed=self.seed,
                                    bandwidth=float(self.bandwidths[0]), random_episodes=int(self.enable_random_episodes),
                                    **kw)
             if kw["channel_mode"] == 3:  # QuadrigaChannel[Seq]: transform the power files once, keep SE in HBM
@@ -245,6 +248,13 @@ class BatchedMARLCommEnv:
             return (obs[0] if self.num_envs == 1 else obs), {}
         return self._format_obs(), {}
 
+    def _records(self):
+        """True when episode history files are written for some env of the batch (save_hist)."""
+        if not self.save_hist:
+            return False
+        ids = self.hist_envs if self.hist_envs is not None else ([0] if self.num_envs == 1 else [])
+        return len(ids) > 0
+
     def _history(self):
         if not self.save_hist:
             return None
@@ -339,6 +349,14 @@ class BatchedMARLCommEnv:
         if rec is not None:
             rec.record()
             rec.flush()
+            if self.auto_reset:
+                # With a recorder the device does not roll finished envs over inside the step (the last frame's
+                # observation and SE would be overwritten before they are recorded): one masked reset here instead.
+                done = eng.v["out_done"].bool()
+                if bool(done.any()):
+                    eng.reset(mask=done)
+                    self._check()
+                    rec.mark_reset()
         obs = self._format_obs()
         s = eng.surface()
         if self.num_envs > 1:

@@ -59,6 +59,7 @@ class HistoryRecorder:
             self.h["se"] = torch.zeros((n, T, U, R), dtype=torch.float64, device=dev)
         self.episode = torch.zeros(n, dtype=torch.int32, device=dev)   # episode / scenario the open block belongs to
         self.scen = torch.zeros(n, dtype=torch.int32, device=dev)
+        self.scen_rows = None  # the scenario rows themselves (they may have been generated on the device: assoc_mode 2)
         self.ar = torch.arange(n, device=dev)
         self.written: list[str] = []
 
@@ -67,6 +68,7 @@ class HistoryRecorder:
         v = self.eng.v
         self.episode.copy_(v["episode"][self.ids])
         self.scen.copy_(v["scen"][self.ids])
+        self.scen_rows = self.eng.scenario_rows()[self.ids.cpu().numpy()]
 
     def record(self):
         """Call right after a step (asynchronous; no host synchronisation)."""
@@ -95,19 +97,17 @@ class HistoryRecorder:
         out = []
         for i in np.flatnonzero(done):
             out.append(self._write(int(i)))
-        if done.any():  # blocks of envs that auto-reset now belong to their new episode
-            v = self.eng.v
-            m = self._done
-            self.episode[m] = v["episode"][self.ids][m]
-            self.scen[m] = v["scen"][self.ids][m]
         return out
 
     def _write(self, i: int) -> str:
         T = self.T
         h = {k: t[i].cpu().numpy() for k, t in self.h.items()}
         scen, ep = int(self.scen[i].item()), int(self.episode[i].item())
-        sua = self.bank.assocs[scen]
-        req = self.bank.reqs[scen]
+        if scen < len(self.bank.reqs):
+            sua, req = self.bank.assocs[scen], self.bank.reqs[scen]
+        else:  # a scenario generated on the device (assoc_mode 2): the dicts are rebuilt from its dense row
+            from . import scenario as scn
+            req, sua = scn.req_from_row(self.scen_rows[i])
         bsa = np.array([[1.0 if req.get(f"slice_{s}", {}) != {} else 0.0 for s in range(S)]])
         rep = lambda a: np.repeat(np.asarray(a)[None], T, axis=0)
         reward = np.empty(T, object)

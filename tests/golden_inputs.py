@@ -196,3 +196,90 @@ def quadriga_episode_powers(meta, d):
         a, f = quadriga_file_of_episode(meta["channel"], e)
         power[e - first] = quadriga_power(a, f, T)[:, :, 0, 0, :]
     return first, power
+
+
+# ---- BASELINE config 2 as a batch: 64 envs x 1000 steps recorded from the unmodified reference ------------------
+def load_config2():
+    f = np.load(os.path.join(GOLDEN, "config2_batch.npz"), allow_pickle=False)
+    return {k: f[k] for k in f.files}
+
+
+class Config2Frames:
+    """SE / traffic frames of the config-2 fixture, regenerated env by env from the recipe (env e: seed 10 + e,
+    episode e mod 200; oracle/refharness/gen_config2.py) and verified against the stored checksums."""
+
+    def __init__(self, d, envs):
+        st, us = load_scenarios()
+        self.d, self.envs = d, list(envs)
+        self.src = [FrameSource(10 + e, "mimic", st, us) for e in self.envs]
+        self.k = 0
+        self.n_reset = 0
+
+    def reset_frames(self):
+        ri = self.n_reset
+        se = np.stack([s.reset_frame(int(self.d["reset_episode"][e, ri]) % 200) for s, e in zip(self.src, self.envs)])
+        if not np.array_equal(bits_checksum(se), self.d["reset_se_checksum"][self.envs, ri]):
+            raise AssertionError("regenerated reset SE frames do not match the fixture checksum")
+        self.n_reset += 1
+        return se
+
+    def step_frames(self):
+        k = self.k
+        out = [s.step_frame(int(self.d["episode"][e, k]) % 200) for s, e in zip(self.src, self.envs)]
+        se, tr = np.stack([o[0] for o in out]), np.stack([o[1] for o in out])
+        if not np.array_equal(bits_checksum(se), self.d["se_checksum"][self.envs, k]):
+            raise AssertionError("regenerated SE frames do not match the fixture checksum (NumPy RNG stream differs)")
+        if not np.array_equal(tr, self.d["traffic_mbit"][self.envs, k].astype(np.float64) * 1e6):
+            raise AssertionError("regenerated traffic frames do not match the fixture")
+        self.k += 1
+        return se, tr
+
+
+def replay_config2(env, d, envs, n_steps=None, rtol=1e-5):
+    """Drive `env` (reset(initial_episodes, se) / step(a0, intra, se, traffic) / buffers(), batch = len(envs)) with the
+    fixture's actions and frames as ONE batch and compare every output the fixture holds: integers bit-exact at every
+    step, rewards at every step and observations / occupancy / delay at every 8th step against float32 (rtol 1e-5,
+    the tolerance of the path), buffers at the checkpoints."""
+    envs = list(envs)
+    frames = Config2Frames(d, envs)
+    n = int(d["meta_n_steps"]) if n_steps is None else n_steps
+    every = int(d["meta_obs_every"])
+    ie = d["reset_episode"][envs, 0].astype(np.int32)
+    out = env.reset(initial_episodes=ie, se=frames.reset_frames())
+
+    def close(tag, got, want, k):
+        np.testing.assert_allclose(np.asarray(got, np.float64), np.asarray(want, np.float64), rtol=rtol, atol=1e-30,
+                                   err_msg=f"config 2: {tag} at step {k}")
+
+    def exact(tag, got, want, k):
+        got, want = np.asarray(got), np.asarray(want)
+        assert np.array_equal(got.astype(np.int64), want.astype(np.int64)), f"config 2: {tag} differs at step {k}"
+
+    for key in ("obs0", "obs_i"):
+        close("reset " + key, out[key], d["reset_" + key][envs, 0], -1)
+    for key in ("mask0", "mask_i", "sorted_slices"):
+        exact("reset " + key, out[key], d["reset_" + key][envs, 0], -1)
+    ck = 0
+    for k in range(n):
+        se, tr = frames.step_frames()
+        out = env.step(d["a0"][envs, k], d["intra"][envs, k], se, tr)
+        for key, gold in (("rb_start", "rb_start"), ("rb_count", "rb_count"), ("pkt_incoming", "pkt_incoming"),
+                          ("pkt_throughputs", "pkt_throughputs"), ("sent", "pkt_effective_thr"),
+                          ("dropped", "dropped_pkts"), ("mask0", "mask0"), ("mask_i", "mask_i"),
+                          ("sorted_slices", "sorted_slices"), ("done", "done")):
+            exact(key, out[key], d[gold][envs, k], k)
+        close("reward", out["reward"], d["reward"][envs, k], k)
+        if k % every == every - 1:
+            j = k // every
+            close("obs0", out["obs0"], d["obs0"][envs, j], k)
+            close("obs_i", out["obs_i"], d["obs_i"][envs, j], k)
+            close("occ", out["occ"], d["buffer_occupancies"][envs, j], k)
+            close("lat", out["lat"], d["buffer_latencies"][envs, j], k)
+        if ck < d["ckpt_at_step"].shape[1] and d["ckpt_at_step"][envs[0], ck] == k:
+            buf = np.asarray(env.buffers())
+            for i, e in enumerate(envs):
+                for u in range(U):
+                    dep = int(d["ckpt_depth"][e, ck, u])
+                    assert np.array_equal(buf[i, u, :dep], d["ckpt_buf"][e, ck, u, :dep]), f"buffer env {e} UE {u} step {k}"
+            ck += 1
+    return ck

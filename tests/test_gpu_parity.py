@@ -322,6 +322,30 @@ def test_generated_scenarios_match_oracle():
     assert np.array_equal(gpu.state()["scen"], orc.state()["scen"])
 
 
+def test_config2_batch_fixture_from_the_reference(bank):
+    """BASELINE config 2 against the REFERENCE itself: 64 envs x 1000 steps recorded from the unmodified reference
+    (env e: episode e mod 200, seed 10 + e, actions default_rng(1234 + e); oracle/refharness/gen_config2.py) replayed
+    as ONE CUDA batch with the recorded SE / traffic frames injected (channel_mode 0, traffic_mode 0): RB runs, packet
+    counts, masks, slice order bit-exact at every step, rewards at every step, observations every 8th step, buffers
+    at the checkpoints, the episode rollover included."""
+    d = golden_inputs.load_config2()
+    envs = list(range(64))
+    gpu = CudaEnv(bank, 64, channel_mode=0, traffic_mode=0, sort_slices=1, fixed_intra=-1)
+
+    class Env:
+        def reset(self, initial_episodes, se):
+            return gpu.reset(initial_episodes=initial_episodes, initial_episode=0, se=se)
+
+        def step(self, a0, intra, se, tr):
+            return gpu.step(a0, intra, se, tr)
+
+        def buffers(self):
+            return gpu.buffers()
+
+    assert golden_inputs.replay_config2(Env(), d, envs) == 4
+    assert bool(gpu.eng.v["out_done"].all())
+
+
 def test_random_episodes_native_matches_oracle(bank):
     """enable_random_episodes with the built-in (Feistel) permutation: CUDA and oracle play the same shuffled cycles,
     per env, across wrap-arounds and a mid-run reset that draws a new permutation (comm_env.py:219-226, 434-444)."""
