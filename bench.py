@@ -47,6 +47,9 @@ def parse():
     p.add_argument("--cpu-envs", type=int, default=0,
                    help="env instances of the CPU baseline sample (default 512 for the sweep, whose buffers take "
                         "thousands of steps to fill, else 2048)")
+    p.add_argument("--d2h-probe", action="store_true",
+                   help="no kernels: every rank copies one step's float64 surface (81.2 MB at 65,536 envs) device->pinned "
+                        "host in a loop; prints the aggregate GB/s, the ceiling of the e2e figure at N GPUs")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
     a = p.parse_args()
@@ -170,7 +173,7 @@ def cpu_fill_steps(args, bank):
     return {401: 1664, 1024: 2944, 4096: 4736}.get(bank.max_depth(), 3 * bank.max_depth())
 
 
-def cpu_oracle_run(args, bank, n_envs, warmup, steps=None, budget_s=12.0, fill=0):
+def cpu_oracle_run(args, bank, n_envs, warmup, steps=None, budget_s=12.0, fill=0, min_wall_s=0.0):
     """The oracle port (oracle/irs_oracle.c, OpenMP over envs) on the host cores: same scenario
     bank, generators, agent surface and action distribution as the GPU arm."""
     n_envs = n_envs or (512 if args.workload == "sweep" else 2048)
@@ -201,15 +204,20 @@ def cpu_oracle_run(args, bank, n_envs, warmup, steps=None, budget_s=12.0, fill=0
             env.step(*pool[k % 4])
         per = (time.perf_counter() - t) / 3
         steps = int(max(5, min(2000, budget_s / max(per, 1e-6))))
-    t = time.perf_counter()
-    for k in range(steps):
-        env.step(*pool[k % 4])
-    dt = time.perf_counter() - t
+    blocks, wall = [], 0.0
+    while not blocks or (wall < min_wall_s and len(blocks) < 200):
+        t = time.perf_counter()
+        for k in range(steps):
+            env.step(*pool[k % 4])
+        blocks.append(time.perf_counter() - t)
+        wall += blocks[-1]
+    dt = float(np.median(blocks))
     env.close()
+    rep = f" (median of {len(blocks)} blocks of {steps} steps, {wall:.1f} s measured)" if len(blocks) > 1 else ""
     return {"value": n_envs * U * steps / dt, "unit": "UE-steps/s", "cores": cores, "kind": "port",
             "sample": f"{n_envs} envs x {steps} steps of the same workload after {fill} untimed fill steps, "
-                      f"oracle/irs_oracle.c with OpenMP on {cores} threads", "envs": n_envs,
-            "seconds": dt, "ms_per_step": dt / steps * 1e3, "steps": steps}
+                      f"oracle/irs_oracle.c with OpenMP on {cores} threads" + rep, "envs": n_envs,
+            "seconds": dt, "ms_per_step": dt / steps * 1e3, "steps": steps, "blocks": len(blocks)}
 
 
 def run_reference(args):
@@ -221,7 +229,9 @@ def run_reference(args):
         return
     bank, wl = make_bank(args.depth)
     n_envs = args.cpu_envs
-    r = cpu_oracle_run(args, bank, n_envs, args.warmup, steps=args.steps, fill=cpu_fill_steps(args, bank))
+    # the --steps block is repeated until at least 4 s of wall time have been measured and the MEDIAN block is
+    # reported: a 20-step block is 85 ms on this sample, and one such window moved the driver's ratio by 30 %
+    r = cpu_oracle_run(args, bank, n_envs, args.warmup, steps=args.steps, fill=cpu_fill_steps(args, bank), min_wall_s=4.0)
     n_envs = r["envs"]
     line = {
         "impl": "reference", "metric": "UE-steps/sec (env-steps/sec x UEs)", "value": r["value"], "unit": "UE-steps/s",
@@ -234,6 +244,42 @@ def run_reference(args):
         "gpu_launches": 0,
     }
     print(json.dumps(line))
+
+
+def d2h_copy_rate(torch, dev, nbytes, barrier, world, dist, reps=20):
+    """Device -> pinned host copies of `nbytes` back to back, no kernels: GB/s of this rank and of all ranks together
+    (time = max over ranks).  What the host side can absorb is the ceiling of the e2e figure."""
+    src = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    dst = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    for _ in range(3):
+        dst.copy_(src, non_blocking=True)
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(reps):
+        dst.copy_(src, non_blocking=True)
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    if world > 1:
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    per = nbytes * reps / (ms * 1e-3) / 1e9
+    return {"gbs_per_gpu": per, "gbs_total": per * world, "bytes_per_copy": nbytes, "copies": reps, "ms_per_copy": ms / reps}
+
+
+def ncu_facts(workload, envs, depth):
+    """What one `ncu --set full` capture of k_ue_env on this workload measured (profiles/ue_env_ncu.json, written by
+    scripts/ncu_to_json.py from the committed captures): warp instructions and DRAM bytes per launch are properties of
+    the launch, not of the run, so they are combined with the LIVE kernel time below."""
+    try:
+        for tj in json.load(open(os.path.join(ROOT, "profiles", "ue_env_ncu.json"))):
+            if tj.get("envs") == envs and tj.get("depth", 0) == depth and tj.get("workload") == workload:
+                return tj
+    except Exception:
+        pass
+    return None
 
 
 def run_b200(args):
@@ -296,6 +342,17 @@ def run_b200(args):
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize(dev)
+
+    surface_bytes = E * (50 * 8 + 95 * 8 + 5 + 25 + 6 * 8 + 1)  # float64 obs0 / obs_i, int8 masks, 6 rewards, done
+    if args.d2h_probe:
+        r = d2h_copy_rate(torch, dev, surface_bytes, barrier, world, dist, reps=50)
+        if rank == 0:
+            print(json.dumps({"probe": "d2h", "n_gpus": world, "envs_per_gpu": E, **r,
+                              "note": "device -> pinned host, no kernels running; aggregate = per-GPU rate x ranks, timed as "
+                                      "the max over ranks", "host_numa_pinned": numa_pinned}))
+        if world > 1:
+            dist.destroy_process_group()
+        return
 
     n_fill = fill_to_steady_state(args, bank, eng, pool)
     for k in range(Wm):
@@ -367,23 +424,38 @@ def run_b200(args):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = ue_bytes / (kms[1] * 1e-3) / 1e9
-    traffic = None
-    try:
-        for tj in json.load(open(os.path.join(ROOT, "profiles", "ue_step_traffic.json"))):  # ncu --set full captures
-            if tj.get("envs") == E and tj.get("depth", 0) == args.depth and tj.get("workload", "mix") == args.workload:
-                traffic = tj["dram_bytes_per_launch"]
-    except Exception:
-        pass
-    roofline = {"bound": "hbm", "kernel": "k_ue_env", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": traffic,
-                "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650 GB/s",
-                "algorithmic_bytes_per_launch": ue_bytes, "kernel_ms": kms[1],
-                "kernel_ms_all": {"k_action": kms[0], "k_ue_env": kms[1], "k_env_tail": kms[2]},
-                "bytes_per_ue_row": ("%d (per-UE records) + ring row: 4 per slot access (expiring slot, the 4-slot look-ahead at the old end, slots the drain changes, the arrivals slot)" % FIXED_ROW_BYTES)
-                + (" + 1080 (SE row) per associated UE" if args.workload == "trace" else ""),
-                "row_paths": {"no_old_packets": path_frac[0], "window_cleared": path_frac[1], "lane_drain": path_frac[2],
-                              "warp_drain": path_frac[3]},
-                "live_slot_fraction": live_frac}
+    facts = ncu_facts(args.workload, E, args.depth)
+    traffic = facts["dram_bytes_per_launch"] if facts else None
+    rows = E * U
+    hbm = {"achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+           "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650 GB/s",
+           "algorithmic_bytes_per_launch": ue_bytes,
+           "bytes_per_ue_row": ("%d (per-UE records) + ring row: 4 per slot access (expiring slot, the 4-slot look-ahead at "
+                                "the old end, slots the drain changes, the arrivals slot)" % FIXED_ROW_BYTES)
+           + (" + 1080 (SE row) per associated UE" if args.workload == "trace" else ""),
+           # what SURVEY 8(d)'s dense age-shift formulation (np.roll of every row, buffer.py:61) would move: stated for
+           # reference, never divided by a time (the ring rows do not move these bytes)
+           "survey_8d_dense_shift_bytes_per_launch": float(sum(8 * int(d) + 136 for d in depth_tab[(np.arange(E) + rank * E) % len(arr)].ravel()))
+           if args.workload != "trace" else None}
+    sm_mhz = (clocks or {}).get("sm_mhz") or float(peaks.get("sm_max_mhz", 1965.0))
+    n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
+    if args.workload != "trace" and facts and facts.get("inst_per_launch"):
+        # With ring rows the kernel moves ~0.45 KB per UE row and draws 135 normals for it: it is bound by instruction
+        # issue (one warp instruction per SM sub-partition and clock), not by HBM.  Achieved = warp instructions of
+        # one launch (ncu smsp__inst_executed.sum of the same launch shape) / the LIVE kernel time.
+        ginst = facts["inst_per_launch"] / (kms[1] * 1e-3) / 1e9
+        peak_i = n_sm * 4 * sm_mhz * 1e6 / 1e9
+        roofline = {"bound": "issue", "kernel": "k_ue_env", "achieved": ginst, "peak": peak_i, "unit": "G warp-inst/s",
+                    "frac": ginst / peak_i, "traffic": traffic,
+                    "peak_source": f"{n_sm} SMs x 4 schedulers x {sm_mhz:.0f} MHz (SM clock sampled during the timed region)",
+                    "inst_per_launch": facts["inst_per_launch"], "ncu_issue_active_pct": facts.get("issue_active_pct"),
+                    "ncu_source": facts.get("source"), "hbm": hbm}
+    else:
+        roofline = dict(hbm, bound="hbm", kernel="k_ue_env")
+    roofline.update({"kernel_ms": kms[1], "kernel_ms_all": {"k_action": kms[0], "k_ue_env": kms[1], "k_env_tail": kms[2]},
+                     "row_paths": {"no_old_packets": path_frac[0], "window_cleared": path_frac[1], "lane_drain": path_frac[2],
+                                   "warp_drain": path_frac[3]},
+                     "live_extent_fraction": live_frac})
 
     # ---- e2e: host actions in, host surface out, through irs_step_host ------------------------
     e2e = e2e_f32 = None
@@ -416,8 +488,12 @@ def run_b200(args):
             return {"value": world * E * U * Ke / (ms * 1e-3), "unit": "UE-steps/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": bytes_out, "steps": Ke, "ms_per_step": ms / Ke}
 
+        probe = d2h_copy_rate(torch, dev, d2h, barrier, world, dist)
         e2e = time_host(surf, d2h)
         e2e["api"] = "irs_step_host (pinned host actions in, float64 obs/masks/rewards/done out, stream drained)"
+        # the ceiling of this figure: the same bytes copied device -> pinned host with no kernels running, all ranks at once
+        e2e["d2h_copy_only"] = {"gbs_per_gpu": probe["gbs_per_gpu"], "gbs_total": probe["gbs_total"],
+                                "ms_per_step": probe["ms_per_copy"], "frac_of_ceiling": probe["ms_per_copy"] / e2e["ms_per_step"]}
         # the same call with the optional binary32 surface (converted on the device): half the bytes over PCIe
         h32 = {"obs0_f32": pin(E, 50, dt=torch.float32), "obsi_f32": pin(E, 5, 19, dt=torch.float32),
                "reward_f32": pin(E, 6, dt=torch.float32)}
@@ -434,7 +510,7 @@ def run_b200(args):
     err = eng.check_errors()
     active = float((torch.from_numpy((arr["ue_slice"][:, :25] >= 0).sum(1)).to(dev)[eng.v["scen"].long()]).double().mean().item())
     from intent_radio_sched_multi_slice_b200 import distributed as D
-    metrics_named = D.all_reduce_metrics(eng.episode_metrics(), dev)  # the path's one collective (NCCL when N > 1)
+    metrics_named = D.all_reduce_metrics(eng.episode_metrics_device(), dev)  # the path's one collective (NCCL when N > 1)
 
     # kernels per irs_step (irs_capi.cu launch_step): k_action[_t], k_ue_env, k_env_tail[_t], and k_rollover after the
     # thread-per-env tail (launches of >= IRS_SERIAL_MIN_ENVS envs, default 49,152)

@@ -147,6 +147,7 @@ typedef struct {
     size_t out_reward;       /* f64 [E][6] */
     size_t out_done;         /* u8  [E] */
     size_t metrics_total;    /* f64 [16] result of irs_episode_metrics */
+    size_t scratch;          /* i32 [64] small device-side results (irs_check_errors: first failing env, its error word) */
     size_t out32;            /* f32 [E][151] staging of the binary32 host surface (obs0 | obsi | reward per env
                                 block: [E][50], then [E][95], then [E][6]) */
 } irs_layout;
@@ -261,8 +262,10 @@ int irs_reset_host(irs_env* env, int32_t initial_episode, const irs_host_surface
  * host_out != NULL, copy them to the host (synchronises).  Replaces Metrics.save
  * (metrics.py:73-100) as the source of episode statistics. */
 int irs_episode_metrics(irs_env* env, double* host_out, void* stream);
-/* debug=True of the reference (comm_env.py:313-319): synchronises, returns IRS_ERR_ENV and the
- * index of the first env with a non-zero error word. */
+/* debug=True of the reference (comm_env.py:313-319): the error words are scanned ON THE DEVICE (first env with a
+ * non-zero word) and two integers come back; synchronises; returns IRS_ERR_ENV, the env index and its error word
+ * (bits: 1 invalid intra-slice action, 2 episode out of range, 4 RB sum, 8 episode outside the SE bank, 16 RB given
+ * to two UEs). */
 int irs_check_errors(irs_env* env, int32_t* first_env, int32_t* code, void* stream);
 /* random_episodes with a GIVEN order (parity runs replay the permutation the reference drew from its np_random):
  * order_dev is i32 [E][n], caller-owned device memory kept alive while in use; env e plays order_dev[e][pos % n].

@@ -32,7 +32,7 @@ class Config(C.Structure):
 _LAYOUT_ARRAYS = [
     "buf", "ue_i", "ue_d", "ring", "rb", "step", "episode", "scen", "win_len",
     "win_head", "err", "visit", "ep_pos", "ep_gen", "ep_base", "wsum", "sorted", "acc", "bank", "cdf", "in_a0", "in_intra", "out_obs0", "out_obsi",
-    "out_mask0", "out_maski", "out_reward", "out_done", "metrics_total", "out32",
+    "out_mask0", "out_maski", "out_reward", "out_done", "metrics_total", "scratch", "out32",
 ]
 UI_FIELDS = ["tot", "sum_sent", "sum_drop", "last_sent", "last_drop", "last_inc", "occ1z", "path"]
 UD_FIELDS = ["occ", "lat", "sebar", "thr"]

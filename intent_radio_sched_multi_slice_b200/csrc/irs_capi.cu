@@ -8,6 +8,8 @@
 
 #include <new>
 
+#include <nvtx3/nvToolsExt.h> // header-only; a no-op unless a profiler is attached
+
 #include "irs_action.cuh"
 #include "irs_env.cuh"
 #include "irs_ue.cuh"
@@ -74,6 +76,7 @@ static void compute_layout(const irs_config& c, int32_t n_lambda, irs_layout* L)
     L->out_reward = take(E * 6 * 8);
     L->out_done = take(E);
     L->metrics_total = take(IRS_NUM_METRICS * 8);
+    L->scratch = take(64 * 4);
     L->out32 = take(E * (IRS_OBS0 + S * IRS_OBSI + 6) * 4);
     L->total_bytes = off;
 }
@@ -214,6 +217,7 @@ int irs_bind(irs_env* env, void* state_dev, size_t bytes, void* stream)
     s.out_mask0 = (int8_t*)(b + L.out_mask0); s.out_maski = (int8_t*)(b + L.out_maski);
     s.out_reward = (double*)(b + L.out_reward); s.out_done = (uint8_t*)(b + L.out_done);
     s.metrics_total = (double*)(b + L.metrics_total);
+    s.scratch = (int32_t*)(b + L.scratch);
     s.row_stride = L.row_stride;
     cudaStream_t st = (cudaStream_t)stream;
     CK(cudaMemsetAsync(b, 0, L.total_bytes, st));
@@ -281,22 +285,33 @@ int irs_reset(irs_env* env, const uint8_t* mask_dev, int32_t initial_episode, co
     return IRS_OK;
 }
 
+struct NvtxRange { // host-side range around the enqueue of one phase (shows the launch sequence on a timeline)
+    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+};
+
 static int launch_step(irs_env* env, const StepArgs& A, cudaStream_t st, bool profile = false)
 {
     const int E = A.env_end - A.env_begin;
     if (E <= 0) return IRS_OK;
+    NvtxRange whole("irs_step");
     if (profile) CK(cudaEventRecord(env->ev[0], st));
     const bool serial = E >= env->serial_min;
+    nvtxRangePushA("action->RB");
     if (A.sched_bits) k_sched_runs<<<(E + 7) / 8, 256, 0, st>>>(A);
     else if (serial) k_action_t<<<(E + SERIAL_THREADS - 1) / SERIAL_THREADS, SERIAL_THREADS, 0, st>>>(A);
     else k_action<<<(E + 7) / 8, 256, 0, st>>>(A);
+    nvtxRangePop();
     if (profile) CK(cudaEventRecord(env->ev[1], st));
+    nvtxRangePushA("channel+traffic+buffers");
     StepArgs B2 = A; // small batches: 2 or 4 warps per env, so that the launch still puts ~32 warps on every SM
     B2.ue_split_log2 = env->ue_split >= 0 ? env->ue_split : (E <= 1184 ? 2 : (E <= 2368 ? 1 : 0));
     const unsigned env_warps = (unsigned)E << B2.ue_split_log2;
     if (A.raw.se_used || A.sched_bits) k_ue_env_raw<<<(env_warps + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(B2);
     else k_ue_env<<<(env_warps + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(B2);
+    nvtxRangePop();
     if (profile) CK(cudaEventRecord(env->ev[2], st));
+    NvtxRange tail("obs+reward+rollover");
     const bool alt = env->cfg.surface != 0; // SchedTWC / SchedColORAN: their surface reads the step's records before
                                             // finished envs roll over, then once more for the reset observation
     const unsigned env_blocks = (E + ENV_WARPS - 1) / ENV_WARPS;
@@ -619,22 +634,19 @@ int irs_check_errors(irs_env* env, int32_t* first_env, int32_t* code, void* stre
     if (!env || !env->bound) return IRS_ERR_UNBOUND;
     cudaStream_t st = (cudaStream_t)stream;
     const int E = env->cfg.num_envs;
-    int32_t* h = new (std::nothrow) int32_t[E];
-    if (!h) return IRS_ERR_ARG;
-    cudaError_t e = cudaMemcpyAsync(h, env->st.err, (size_t)E * 4, cudaMemcpyDeviceToHost, st);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-    if (e != cudaSuccess) { delete[] h; return cuda_fail(env, e, "irs_check_errors"); }
-    int rc = IRS_OK;
-    for (int i = 0; i < E; ++i)
-        if (h[i]) {
-            if (first_env) *first_env = i;
-            if (code) *code = h[i];
-            snprintf(env->err, sizeof(env->err), "env %d error word %d", i, h[i]);
-            rc = IRS_ERR_ENV;
-            break;
-        }
-    delete[] h;
-    return rc;
+    StepArgs A = make_args(env);
+    CK(cudaMemsetAsync(env->st.scratch, 0x7f, 4, st)); // 0x7f7f7f7f: larger than any env index
+    k_err_scan<<<(E + 255) / 256, 256, 0, st>>>(A);
+    k_err_word<<<1, 1, 0, st>>>(A);
+    CK(cudaGetLastError());
+    int32_t h[2] = {0, 0};
+    CK(cudaMemcpyAsync(h, env->st.scratch, 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (h[0] < 0 || h[0] >= E) return IRS_OK;
+    if (first_env) *first_env = h[0];
+    if (code) *code = h[1];
+    snprintf(env->err, sizeof(env->err), "env %d error word %d", h[0], h[1]);
+    return IRS_ERR_ENV;
 }
 
 } // extern "C"

@@ -52,6 +52,7 @@ struct DevState {
     int8_t *out_mask0, *out_maski;
     uint8_t* out_done;
     double* metrics_total;
+    int32_t* scratch;
     int32_t row_stride;
 };
 

@@ -392,6 +392,19 @@ __global__ void __launch_bounds__(256) k_read_buffers(const __grid_constant__ St
         dst[a] = a < up.depth ? row[head - a + (head < a ? up.depth : 0)] : 0;
 }
 
+// irs_check_errors: index of the first env with a non-zero error word into scratch[0] (INT_MAX: none), its word into
+// scratch[1] - two launches on the stream, so that 8 bytes instead of the whole error array cross PCIe.
+__global__ void __launch_bounds__(256) k_err_scan(const __grid_constant__ StepArgs A)
+{
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e < A.cfg.num_envs && A.st.err[e] != 0) atomicMin(&A.st.scratch[0], e);
+}
+__global__ void k_err_word(const __grid_constant__ StepArgs A)
+{
+    const int e = A.st.scratch[0];
+    A.st.scratch[1] = (e >= 0 && e < A.cfg.num_envs) ? A.st.err[e] : 0;
+}
+
 // Sum of the per-env accumulators in a FIXED order (reproducible bits for a given batch size): block k sums
 // metric k; thread t adds its contiguous range of envs serially, then a shared-memory tree over the threads.
 __global__ void __launch_bounds__(256) k_metrics(const __grid_constant__ StepArgs A)

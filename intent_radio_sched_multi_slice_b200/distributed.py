@@ -48,13 +48,14 @@ def init(backend: str | None = None, device: torch.device | None = None):
 
 
 def all_reduce_metrics(local, device=None) -> dict:
-    """Sum the 16 episode-metric accumulators over all ranks.  `local`: array-like [16] (e.g.
-    BatchEngine.episode_metrics()) or a tensor already on the device.  Counters (packets,
-    steps, violations, episodes) are integer-valued float64 < 2^53 and therefore exact in any
-    reduction order; the float sums (rewards, Mbit, distances) agree to rounding."""
-    t = torch.as_tensor(np.asarray(local) if not isinstance(local, torch.Tensor) else local, dtype=torch.float64)
+    """Sum the 16 episode-metric accumulators over all ranks.  `local`: a tensor already on the device - e.g.
+    BatchEngine.episode_metrics_device(), the [16] result of the fixed-order reduction kernel inside the state blob,
+    which NCCL then reduces IN PLACE on the same stream (no host round trip before the collective) - or an
+    array-like [16].  Counters (packets, steps, violations, episodes) are integer-valued float64 < 2^53 and therefore
+    exact in any reduction order; the float sums (rewards, Mbit, distances) agree to rounding."""
+    t = local if isinstance(local, torch.Tensor) else torch.as_tensor(np.asarray(local), dtype=torch.float64)
     if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
-        if dist.get_backend() == "nccl":
+        if dist.get_backend() == "nccl" and not t.is_cuda:
             t = t.to(device if device is not None else torch.device("cuda", torch.cuda.current_device()))
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
     return dict(zip(capi.METRIC_NAMES, t.cpu().tolist()))

@@ -127,6 +127,10 @@ class HistoryRecorder:
             action[k] = a
         if self.flat:
             reward, obs, action = reward.astype(np.float64), np.stack(list(obs)), np.stack(list(action))
+            if self.eng.cfg.policy == 1:  # MARR.step returns integer scores +-1 (agents/marr.py:40-47)
+                action = action.astype(np.int64)
+        from . import scenario as scn
+        req = scn.callable_req(req)  # operators as NumPy ufuncs, like the dicts the reference pickles
         slice_req = np.empty(T, object)
         for k in range(T):
             slice_req[k] = req

@@ -235,3 +235,45 @@ def test_history_file_matches_reference_trace(bank, tmp_path):
             np.testing.assert_allclose([h["reward"][k][f"player_{i}"] for i in range(6)], d["reward"][sl][k], rtol=1e-12)
             assert np.array_equal(h["agent_action"][k]["player_0"], d["a0"][sl][k])
             assert [h["agent_action"][k][f"player_{i + 1}"] for i in range(5)] == d["intra"][sl][k].tolist()
+
+
+@pytest.mark.parametrize("agent,fixture", [("IBSched", "ib_sched"), ("MARR", "marr")])
+def test_history_file_has_the_structure_of_the_reference_file(agent, fixture, bank, tmp_path):
+    """The file history.py writes against the file the UNMODIFIED reference wrote with save_hist=True
+    (tests/golden/hist_ref_*_ep_4.npz, oracle/refharness/gen_hist_fixture.py): same keys in the same order, same
+    dtypes and shapes, same nesting of the pickled dicts (reward / obs / agent_action / slice_req with callable
+    operators) - compared through NumPy, not through this package's own reader."""
+    import os
+
+    from intent_radio_sched_multi_slice_b200 import agents, plugins
+    from intent_radio_sched_multi_slice_b200.env import MARLCommEnv
+    from test_reference_readers_cpu import GOLDEN, history_structure
+
+    env = MARLCommEnv(plugins.MimicQuadriga, plugins.MultSliceTraffic, plugins.SimpleMobility,
+                      plugins.MultSliceAssociation, "mult_slice", fixture, 31, root_path="/nonexistent",
+                      initial_episode_number=4, save_hist=True, debug=True, scenario_bank=bank,
+                      hist_root_path=str(tmp_path), simu_name="fixture")
+    env.max_number_steps = 6
+    ag = getattr(agents, agent)(env, 25, 5, 1, np.array([135]))
+    env.set_agent_functions(ag.obs_space_format, ag.action_format, ag.calculate_reward, ag.get_obs_space(),
+                            ag.get_action_space())
+    obs, _ = env.reset(seed=31, options={"initial_episode": 4})
+    rng = np.random.default_rng(3)
+    for k in range(6):
+        if agent == "IBSched":
+            a = {"player_0": rng.uniform(-1, 1, 5)}
+            a.update({f"player_{i}": int(rng.integers(0, 3)) for i in range(1, 6)})
+        else:
+            a = ag.step(obs)
+        obs, *_ = env.step(a)
+    env.close()
+    mine = os.path.join(str(tmp_path), "hist", "fixture", fixture, "ep_4.npz")
+    keys, st = history_structure(mine)
+    ref_keys, ref_st = history_structure(os.path.join(GOLDEN, f"hist_ref_{fixture}_ep_4.npz"))
+    assert keys == ref_keys
+    for k in ref_keys:
+        assert st[k] == ref_st[k], (k, st[k], ref_st[k])
+    f, g = np.load(mine, allow_pickle=True), np.load(os.path.join(GOLDEN, f"hist_ref_{fixture}_ep_4.npz"), allow_pickle=True)
+    assert f["spectral_efficiencies"].any()              # recorded by default (results/gen_results.py:260-322 reads it)
+    for k in ("slice_ue_assoc", "basestation_slice_assoc", "basestation_ue_assoc", "mobility"):
+        assert np.array_equal(f[k], g[k]), k             # same scenario (episode 4 of the seed-10 associations)
