@@ -246,18 +246,26 @@ def run_reference(args):
     print(json.dumps(line))
 
 
-def d2h_copy_rate(torch, dev, nbytes, barrier, world, dist, reps=20):
-    """Device -> pinned host copies of `nbytes` back to back, no kernels: GB/s of this rank and of all ranks together
-    (time = max over ranks).  What the host side can absorb is the ceiling of the e2e figure."""
+def d2h_copy_rate(torch, dev, nbytes, barrier, world, dist, reps=20, pieces=1):
+    """Device -> pinned host copies of `nbytes` (as `pieces` back-to-back copies of nbytes / pieces) in a loop, no
+    kernels: GB/s of this rank and of all ranks together (time = max over ranks).  What the host side can absorb is the
+    ceiling of the e2e figure."""
     src = torch.empty(nbytes, dtype=torch.uint8, device=dev)
     dst = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    per = (nbytes + pieces - 1) // pieces
+    spans = [(i * per, min(nbytes, (i + 1) * per)) for i in range(pieces)]
+
+    def once():
+        for a, b in spans:
+            dst[a:b].copy_(src[a:b], non_blocking=True)
+
     for _ in range(3):
-        dst.copy_(src, non_blocking=True)
+        once()
     barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
     for _ in range(reps):
-        dst.copy_(src, non_blocking=True)
+        once()
     ev1.record()
     barrier()
     ms = ev0.elapsed_time(ev1)
@@ -265,8 +273,9 @@ def d2h_copy_rate(torch, dev, nbytes, barrier, world, dist, reps=20):
         t = torch.tensor([ms], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
-    per = nbytes * reps / (ms * 1e-3) / 1e9
-    return {"gbs_per_gpu": per, "gbs_total": per * world, "bytes_per_copy": nbytes, "copies": reps, "ms_per_copy": ms / reps}
+    rate = nbytes * reps / (ms * 1e-3) / 1e9
+    return {"gbs_per_gpu": rate, "gbs_total": rate * world, "bytes_per_copy": nbytes, "pieces": pieces, "copies": reps,
+            "ms_per_copy": ms / reps}
 
 
 def ncu_facts(workload, envs, depth):
@@ -304,7 +313,8 @@ def run_b200(args):
         args.envs = 1024
     E, K, Wm = args.envs, args.steps, max(args.warmup, 3)
     bank, wl = make_bank(args.depth)
-    eng = BatchEngine(bank, E, device=dev, depth_cap=max(bank.max_depth(), 101), **engine_kwargs(args, rank))
+    # small batches are launch-bound: the engine replays one captured graph per step (BatchEngine(graph=True))
+    eng = BatchEngine(bank, E, device=dev, depth_cap=max(bank.max_depth(), 101), graph=E <= 4096, **engine_kwargs(args, rank))
     gid = torch.arange(E, device=dev, dtype=torch.int32) + rank * E
     trace_bytes = 0
     if args.workload == "trace":
@@ -346,6 +356,10 @@ def run_b200(args):
     surface_bytes = E * (50 * 8 + 95 * 8 + 5 + 25 + 6 * 8 + 1)  # float64 obs0 / obs_i, int8 masks, 6 rewards, done
     if args.d2h_probe:
         r = d2h_copy_rate(torch, dev, surface_bytes, barrier, world, dist, reps=50)
+        r["by_pieces"] = {str(p_): d2h_copy_rate(torch, dev, surface_bytes, barrier, world, dist, reps=30, pieces=p_)["gbs_per_gpu"]
+                          for p_ in (4, 16, 64)}
+        r["by_size_mb"] = {str(mb): d2h_copy_rate(torch, dev, mb << 20, barrier, world, dist, reps=30)["gbs_per_gpu"]
+                           for mb in (1, 4, 16, 64, 256)}
         if rank == 0:
             print(json.dumps({"probe": "d2h", "n_gpus": world, "envs_per_gpu": E, **r,
                               "note": "device -> pinned host, no kernels running; aggregate = per-GPU rate x ranks, timed as "
@@ -481,6 +495,13 @@ def run_b200(args):
             ev1.record()
             barrier()
             ms = max(ev0.elapsed_time(ev1), (time.perf_counter() - tw) * 1e3)
+            if os.environ.get("IRS_BENCH_DEBUG"):
+                per = []
+                for k in range(10):
+                    tq = time.perf_counter()
+                    eng.step_host(h_pool[k % 4][0], h_pool[k % 4][1], surface)
+                    per.append((time.perf_counter() - tq) * 1e3)
+                print(f"e2e debug: events {ev0.elapsed_time(ev1) / Ke:.3f} ms/step, wall {ms / Ke:.3f}, single calls {sorted(per)}", file=sys.stderr)
             if world > 1:
                 t = torch.tensor([ms], device=dev, dtype=torch.float64)
                 dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -514,7 +535,9 @@ def run_b200(args):
 
     # kernels per irs_step (irs_capi.cu launch_step): k_action[_t], k_ue_env, k_env_tail[_t], and k_rollover after the
     # thread-per-env tail (launches of >= IRS_SERIAL_MIN_ENVS envs, default 49,152)
-    launches_per_step = 4 if E >= int(os.environ.get("IRS_SERIAL_MIN_ENVS", "49152")) else 3
+    # at most IRS_FUSED_MAX_ENVS envs (default 2,368): the whole step is ONE launch (k_env_step)
+    launches_per_step = 1 if E <= int(os.environ.get("IRS_FUSED_MAX_ENVS", "2368")) else \
+        (4 if E >= int(os.environ.get("IRS_SERIAL_MIN_ENVS", "49152")) else 3)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_oracle_run(args, bank, args.cpu_envs, warmup=5, fill=n_fill)
@@ -530,7 +553,7 @@ def run_b200(args):
                        "channel": "SE trace bank in HBM (channel_mode 3)" if args.workload == "trace" else "native mimic_quadriga",
                        "trace_bank_bytes": trace_bytes, "traffic": "native Poisson",
                        "state_bytes_per_gpu": state_bytes, "fill_steps": n_fill, "episode_steps": episode_steps(args),
-                       "host_numa_pinned": numa_pinned,
+                       "host_numa_pinned": numa_pinned, "cuda_graph": bool(eng.graph),
                        "l2": "state larger than L2" if flush is None else "L2 flushed (256 MB fill) between timed steps"},
             "e2e": e2e, "e2e_f32_surface": e2e_f32, "roofline": roofline, "cpu_baseline": cpu, "gpu_launches": launches_per_step * K, "clocks": clocks,
             "active_ue_steps_per_s": value * active / U,  # SURVEY 8(d) secondary figure: only UEs associated to a slice

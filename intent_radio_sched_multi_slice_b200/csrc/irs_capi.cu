@@ -9,6 +9,8 @@
 #include <new>
 
 #include <nvtx3/nvToolsExt.h> // header-only; a no-op unless a profiler is attached
+#include <time.h>
+static double wall_ms() { timespec t; clock_gettime(CLOCK_MONOTONIC, &t); return t.tv_sec * 1e3 + t.tv_nsec * 1e-6; }
 
 #include "irs_action.cuh"
 #include "irs_env.cuh"
@@ -29,12 +31,17 @@ struct irs_env {
     cudaEvent_t ev[4];
     bool have_ev;
     cudaStream_t copy_stream;      // irs_step_host: device->host copies of finished chunks
+    cudaStream_t side_stream;      // irs_step_host: every other chunk computes here, so that the kernels of two chunks overlap
+    cudaEvent_t fork_ev, join_ev;
+    int host_streams;              // IRS_HOST_STREAMS (1 or 2 compute streams; default 1)
 
     cudaEvent_t chunk_ev[IRS_MAX_HOST_CHUNKS];
     bool have_copy;
     int ue_split;                  // IRS_UE_SPLIT: log2 of the warps per env in k_ue_env (-1 = by batch size)
-    int host_chunks;               // IRS_HOST_CHUNKS (0 = whole waves of the row kernel, about five chunks)
-    size_t wave_envs;              // envs one full wave of k_ue_env covers on this device (0 = not queried yet)
+    int host_chunks;               // IRS_HOST_CHUNKS (0 = four equal chunks from 16,384 envs)
+    int fused_max;                 // IRS_FUSED_MAX_ENVS (default 2,368): launches of at most this many envs run the whole
+                                   // step in ONE kernel (k_env_step) - small batches are bound by launch and dependency
+                                   // latency, not by throughput
     int serial_min;                // IRS_SERIAL_MIN_ENVS (default 49,152): launches covering at least this many envs
                                    // use the thread-per-env action / tail kernels (irs_serial.cuh); below that one
                                    // thread per env leaves the SMs too empty to hide its serial latency
@@ -161,6 +168,10 @@ int irs_create(const irs_config* cfg, int32_t n_lambda, irs_env** out)
     if (env->ue_split > 2) env->ue_split = 2;
     const char* hc = getenv("IRS_HOST_CHUNKS");
     env->host_chunks = hc ? atoi(hc) : 0;
+    const char* hs_ = getenv("IRS_HOST_STREAMS");
+    env->host_streams = hs_ ? atoi(hs_) : 1;
+    const char* fm_ = getenv("IRS_FUSED_MAX_ENVS");
+    env->fused_max = fm_ ? atoi(fm_) : 2368;
     const char* sm_ = getenv("IRS_SERIAL_MIN_ENVS");
     env->serial_min = sm_ ? atoi(sm_) : 49152;
     compute_layout(env->cfg, n_lambda, &env->lay);
@@ -175,6 +186,9 @@ int irs_destroy(irs_env* env)
     if (env && env->have_copy) {
         for (int i = 0; i < IRS_MAX_HOST_CHUNKS; ++i) cudaEventDestroy(env->chunk_ev[i]);
         cudaStreamDestroy(env->copy_stream);
+        cudaStreamDestroy(env->side_stream);
+        cudaEventDestroy(env->fork_ev);
+        cudaEventDestroy(env->join_ev);
     }
     delete env;
     return IRS_OK;
@@ -296,6 +310,13 @@ static int launch_step(irs_env* env, const StepArgs& A, cudaStream_t st, bool pr
     if (E <= 0) return IRS_OK;
     NvtxRange whole("irs_step");
     if (profile) CK(cudaEventRecord(env->ev[0], st));
+    if (E <= env->fused_max && env->cfg.surface == 0 && !A.sched_bits && !A.raw.se_used) {
+        if (profile) CK(cudaEventRecord(env->ev[1], st));
+        k_env_step<<<(E + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(A);
+        if (profile) { CK(cudaEventRecord(env->ev[2], st)); CK(cudaEventRecord(env->ev[3], st)); }
+        CK(cudaGetLastError());
+        return IRS_OK;
+    }
     const bool serial = E >= env->serial_min;
     nvtxRangePushA("action->RB");
     if (A.sched_bits) k_sched_runs<<<(E + 7) / 8, 256, 0, st>>>(A);
@@ -499,39 +520,23 @@ static int copy_surface(irs_env* env, const irs_host_surface* o, bool with_rewar
 }
 
 // How irs_step_host splits the batch: the surface of a finished chunk crosses PCIe while the next chunk computes.
-// Chunks are whole WAVES of the row kernel (resident blocks per SM x SMs x envs per block), so that chunking does not
-// add a partly filled last wave to every chunk; about five chunks per step.
-// Small batches stay whole (launch latency dominates).  IRS_HOST_CHUNKS=n forces n equal chunks.
+// Measured on B200 (profiles/r2_notes.md): the float64 surface of 65,536 envs needs 1.42 ms on the wire (57 GB/s),
+// the unchunked step 0.71 ms - but a chunk is three dependent kernels that each end in a partly filled wave and run the
+// warp-per-env action / tail kernels, 17-20 ns per env against 10.8 unchunked, so chunked compute (1.26 ms in four
+// chunks) only just keeps ahead of the copy (21.7 ns per env).  The call is then copy-bound at
+// (first chunk's kernels) + (whole copy): FOUR equal chunks measured best (1.82 ms; 3, 5, 6, 8, 12, 16 chunks, a small
+// first chunk with doubling sizes, and two alternating compute streams all measured 1.87-2.1 ms: fewer chunks start the
+// copy later, more chunks compute slower than the wire).  Small batches stay whole (launch latency dominates).
+// IRS_HOST_CHUNKS=n forces n equal chunks, IRS_HOST_STREAMS=2 alternates the chunks between two compute streams.
 static int host_chunk_plan(irs_env* env, size_t* bounds /* [IRS_MAX_HOST_CHUNKS + 1] */)
 {
     const size_t E = (size_t)env->cfg.num_envs;
-    int chunks;
-    size_t per;
-    if (env->host_chunks > 0) {
-        chunks = env->host_chunks > IRS_MAX_HOST_CHUNKS ? IRS_MAX_HOST_CHUNKS : env->host_chunks;
-        per = (E + chunks - 1) / chunks;
-    } else if (E < 16384) {
-        chunks = 1;
-        per = E;
-    } else {
-        if (env->wave_envs == 0) {
-            int dev = 0, sms = 0, nb = 0;
-            if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
-                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_ue_env, FUSED_WARPS * 32, 0) != cudaSuccess || sms <= 0 || nb <= 0) {
-                sms = 148; nb = UE_ENV_MINB;
-            }
-            env->wave_envs = (size_t)sms * nb * FUSED_WARPS;
-        }
-        // Equal chunks: measured timelines (IRS_HOST_TRACE=1, profiles/r1_notes.md) show the sweep compute-bound with only the
-        // last chunk's copy exposed, the mix balanced between chunked kernels and PCIe; a one-wave first chunk and a
-        // partial-wave last chunk (1 + 4 + 4 + 4 + rest) measured 4-10 % slower on both.
-        const size_t waves = (E + env->wave_envs - 1) / env->wave_envs;
-        const size_t wpc = (waves + 4) / 5; // waves per chunk: about five chunks
-        per = wpc * env->wave_envs;
-        chunks = (int)((E + per - 1) / per);
-        if (chunks > IRS_MAX_HOST_CHUNKS) { chunks = IRS_MAX_HOST_CHUNKS; per = (E + chunks - 1) / chunks; }
-    }
-    for (int c = 0; c <= chunks; ++c) bounds[c] = (size_t)c * per < E ? (size_t)c * per : E;
+    int chunks = env->host_chunks > 0 ? env->host_chunks : (E < 16384 ? 1 : 4);
+    if (chunks > IRS_MAX_HOST_CHUNKS) chunks = IRS_MAX_HOST_CHUNKS;
+    size_t per = (E + chunks - 1) / chunks;
+    if (env->host_chunks <= 0 && chunks > 1) per = (per + 31) / 32 * 32; // whole blocks of every kernel
+    bounds[0] = 0;
+    for (int c = 1; c <= chunks; ++c) bounds[c] = (size_t)c * per < E ? (size_t)c * per : E;
     return chunks;
 }
 
@@ -547,30 +552,48 @@ int irs_step_host(irs_env* env, const irs_actions* actions_host, const irs_host_
     const bool given = actions_host && actions_host->a0;
     if (env->cfg.policy == 0 && !given) return fail(env, IRS_ERR_ARG, "policy 0 needs actions.a0");
     if (given) {
-        CK(cudaMemcpyAsync(env->st.in_a0, actions_host->a0, E * S * 8, cudaMemcpyHostToDevice, st));
         A.a0 = env->st.in_a0;
         A.cfg.policy = 0;
-        if (actions_host->intra) {
-            CK(cudaMemcpyAsync(env->st.in_intra, actions_host->intra, E * S * 4, cudaMemcpyHostToDevice, st));
-            A.intra = env->st.in_intra;
-        } else if (env->cfg.fixed_intra < 0) return fail(env, IRS_ERR_ARG, "fixed_intra -1 needs actions.intra");
+        if (actions_host->intra) A.intra = env->st.in_intra;
+        else if (env->cfg.fixed_intra < 0) return fail(env, IRS_ERR_ARG, "fixed_intra -1 needs actions.intra");
     }
+    // the actions of envs [e0, e1) to the device, right before the kernels that read them (a chunk's slice is small,
+    // so the first kernel does not wait for the whole batch's actions)
+    auto upload_actions = [&](size_t e0, size_t e1, cudaStream_t s_) -> cudaError_t {
+        if (!given) return cudaSuccess;
+        cudaError_t rc_ = cudaMemcpyAsync(env->st.in_a0 + e0 * S, actions_host->a0 + e0 * S, (e1 - e0) * S * 8, cudaMemcpyHostToDevice, s_);
+        if (rc_ == cudaSuccess && actions_host->intra)
+            rc_ = cudaMemcpyAsync(env->st.in_intra + e0 * S, actions_host->intra + e0 * S, (e1 - e0) * S * 4, cudaMemcpyHostToDevice, s_);
+        return rc_;
+    };
     size_t bounds[IRS_MAX_HOST_CHUNKS + 1];
     const int chunks = host_chunk_plan(env, bounds);
     if (chunks == 1) {
+        CK(upload_actions(0, E, st));
         rc = launch_step(env, A, st);
         if (rc) return rc;
         return copy_surface(env, out_host, true, st);
     }
     if (!env->have_copy) {
         CK(cudaStreamCreateWithFlags(&env->copy_stream, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&env->side_stream, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&env->fork_ev, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&env->join_ev, cudaEventDisableTiming));
         for (int i = 0; i < IRS_MAX_HOST_CHUNKS; ++i) CK(cudaEventCreateWithFlags(&env->chunk_ev[i], cudaEventDisableTiming));
         env->have_copy = true;
     }
-    // One compute stream: a chunk must FINISH early for its copy to start early (two alternating compute
-    // streams were measured slower - both chunks then finish late, profiles/r1_notes.md).
+    // IRS_HOST_STREAMS=2: chunks alternate between two compute streams, so that the partly filled last waves of one
+    // chunk's kernels are filled by the next chunk's (chunks touch disjoint env ranges: no hazard).  Measured no better
+    // than one stream (a chunk must FINISH early for its copy to start early), kept as an option.
+    const bool two = env->host_streams >= 2;
+    if (two) { // the side stream starts after everything the caller queued on `st`
+        CK(cudaEventRecord(env->fork_ev, st));
+        CK(cudaStreamWaitEvent(env->side_stream, env->fork_ev, 0));
+    }
     // IRS_HOST_TRACE=1: timeline of one call on stderr (ms since the call's first enqueue) - a debugging aid
     static const bool trace = getenv("IRS_HOST_TRACE") != nullptr;
+    static double last_return = 0;
+    const double w_entry = wall_ms();
     cudaEvent_t t0 = nullptr, tk[IRS_MAX_HOST_CHUNKS] = {}, tc[IRS_MAX_HOST_CHUNKS] = {};
     if (trace) {
         CK(cudaEventCreate(&t0));
@@ -582,18 +605,27 @@ int irs_step_host(irs_env* env, const irs_actions* actions_host, const irs_host_
         if (e0 >= e1) break;
         A.env_begin = (int32_t)e0;
         A.env_end = (int32_t)e1;
-        rc = launch_step(env, A, st);
+        const cudaStream_t cs = (two && (c & 1)) ? env->side_stream : st;
+        CK(upload_actions(e0, e1, cs));
+        rc = launch_step(env, A, cs);
         if (rc) return rc;
-        CK(cudaEventRecord(env->chunk_ev[c], st));
-        if (trace) CK(cudaEventRecord(tk[c], st));
+        CK(cudaEventRecord(env->chunk_ev[c], cs));
+        if (trace) CK(cudaEventRecord(tk[c], cs));
         CK(cudaStreamWaitEvent(env->copy_stream, env->chunk_ev[c], 0));
         rc = copy_surface_range(env, out_host, true, e0, e1, env->copy_stream);
         if (rc) return rc;
         if (trace) CK(cudaEventRecord(tc[c], env->copy_stream));
     }
+    if (two) { // the caller's stream continues after both compute streams
+        CK(cudaEventRecord(env->join_ev, env->side_stream));
+        CK(cudaStreamWaitEvent(st, env->join_ev, 0));
+    }
+    const double w_enq = wall_ms();
     CK(cudaStreamSynchronize(env->copy_stream));
+    const double w_sync = wall_ms();
     if (trace) {
-        fprintf(stderr, "irs_step_host trace:");
+        fprintf(stderr, "irs_step_host trace: host [since last return %.3f, enqueue %.3f, wait %.3f]", last_return ? w_entry - last_return : 0.0,
+                w_enq - w_entry, w_sync - w_enq);
         for (int c = 0; c < chunks; ++c) {
             float a = 0, b = 0;
             cudaEventElapsedTime(&a, t0, tk[c]);
@@ -603,6 +635,7 @@ int irs_step_host(irs_env* env, const irs_actions* actions_host, const irs_host_
         }
         fprintf(stderr, "\n");
         cudaEventDestroy(t0);
+        last_return = wall_ms();
     }
     return IRS_OK;
 }

@@ -46,14 +46,19 @@ __device__ __forceinline__ T sel4(const T (&a)[GRP], int j)
     return v;
 }
 
-template <bool RAWSE>
+// FULL_STEP = false: the per-UE middle of the step, between k_action and k_env_tail (large batches: every warp of the
+//                    GPU runs the same small code region).
+// FULL_STEP = true : the whole step of the env in this warp - action -> RB runs before, observation / reward /
+//                    rollover after, on the registers the middle leaves behind.  For SMALL batches (BASELINE config 2:
+//                    1,024 envs) the step is bound by launch and dependency latency, and one launch replaces three.
+template <bool FULL_STEP, bool RAWSE>
 __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP][136], const float2* __restrict__ ntab)
 {
     const DevState& st = A.st;
     const irs_config& cfg = A.cfg;
     const int lane = lane_id();
     const int wib = threadIdx.x >> 5;
-    const int split = A.ue_split_log2, gmask = (1 << split) - 1;
+    const int split = FULL_STEP ? 0 : A.ue_split_log2, gmask = (1 << split) - 1;
     const int wglob = blockIdx.x * FUSED_WARPS + wib;
     const int e = A.env_begin + (wglob >> split), grp = wglob & gmask; // this warp serves the UEs u with (u & gmask) == grp
     if (e >= A.env_end) { normal_tab_wait(); return; } // every warp of the block meets the table barrier exactly once
@@ -89,8 +94,13 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
         const int q = p_old + k;
         look[k] = (ue_lane && a_old - k >= 1) ? row[q >= up.depth ? q - up.depth : q] : 0;
     }
-    const short2 run = st.rb[eu];
-    const int rb_s = run.x, rb_c = run.y;
+    int rb_s, rb_c;
+    if (FULL_STEP) { // ib_sched.py:223-349 on this lane's previous frame (occupancy, mean SE, window sum of sent packets)
+        action_to_rb_core(A, e, sc, rec_d0.x, st.ue_d[eu * UD_N + UD_SEBAR], rec_a.y, win_len, step, episode, rb_s, rb_c);
+    } else {
+        const short2 run = st.rb[eu];
+        rb_s = run.x; rb_c = run.y;
+    }
 
     normal_tab_wait(); // the generators' table, requested at kernel entry, is in shared memory from here on
     // ---- phase 2: channel + traffic of this frame, and the two row sums per UE --------------
@@ -422,7 +432,15 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
         if (A.raw.occ) A.raw.occ[eu] = occ;
         if (A.raw.lat) A.raw.lat[eu] = lat;
         if (A.raw.traffic_used) A.raw.traffic_used[eu] = traffic;
+        if (FULL_STEP) st.rb[eu] = make_short2((short)rb_s, (short)rb_c);
     }
+    if (!FULL_STEP) return;
+    // ---- phase 6: observation, reward, metrics, done, rollover (comm_env.py:339-373) ----------
+    UeFrame f;
+    f.occ = occ; f.lat = lat; f.sebar = sebar; f.sent = sent; f.sum_sent = sum_sent; f.sum_drop = sum_drop;
+    f.rb_count = rb_c; f.occ1z = occ1z;
+    __syncwarp();
+    env_tail_core(A, e, sc, f, dropped, (int)inc, win_len, head_w, step, sm[wib][0]);
 }
 
 #ifndef UE_ENV_MINB
@@ -433,7 +451,7 @@ __global__ void __launch_bounds__(FUSED_WARPS * 32, UE_ENV_MINB) k_ue_env(const 
     __shared__ __align__(16) double sm[FUSED_WARPS][GRP][136];
     __shared__ __align__(16) float2 ntab[IRS_NORMAL_TAB_N];
     normal_tab_request(ntab);
-    ue_env_body<false>(A, sm, ntab);
+    ue_env_body<false, false>(A, sm, ntab);
 }
 // same kernel with the optional per-RB SE output (irs_raw_outputs.se_used; tests and trace dumps)
 __global__ void __launch_bounds__(FUSED_WARPS * 32, UE_ENV_MINB) k_ue_env_raw(const __grid_constant__ StepArgs A)
@@ -441,5 +459,17 @@ __global__ void __launch_bounds__(FUSED_WARPS * 32, UE_ENV_MINB) k_ue_env_raw(co
     __shared__ __align__(16) double sm[FUSED_WARPS][GRP][136];
     __shared__ __align__(16) float2 ntab[IRS_NORMAL_TAB_N];
     normal_tab_request(ntab);
-    ue_env_body<true>(A, sm, ntab);
+    ue_env_body<false, true>(A, sm, ntab);
+}
+
+// the whole step in one launch (small batches; IBSched-family surface, no per-RB raw output)
+#ifndef ENV_STEP_MINB
+#define ENV_STEP_MINB 4
+#endif
+__global__ void __launch_bounds__(FUSED_WARPS * 32, ENV_STEP_MINB) k_env_step(const __grid_constant__ StepArgs A)
+{
+    __shared__ __align__(16) double sm[FUSED_WARPS][GRP][136];
+    __shared__ __align__(16) float2 ntab[IRS_NORMAL_TAB_N];
+    normal_tab_request(ntab);
+    ue_env_body<true, false>(A, sm, ntab);
 }

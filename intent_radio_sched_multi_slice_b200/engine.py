@@ -47,7 +47,8 @@ class BatchEngine:
     def __init__(self, bank: ScenarioBank, num_envs: int, *, device="cuda:0", depth_cap=None,
                  channel_mode=2, traffic_mode=1, sort_slices=1, fixed_intra=-1, policy=0, assoc_mode=0,
                  scen_mod=200, scen_div=100, max_steps=1000, max_episodes=10000, initial_episode=0,
-                 auto_reset=0, env_id_base=0, seed=10, bandwidth=1e8, surface=0, random_episodes=0):
+                 auto_reset=0, env_id_base=0, seed=10, bandwidth=1e8, surface=0, random_episodes=0,
+                 graph=False):
         if not torch.cuda.is_available():
             raise RuntimeError("intent_radio_sched_multi_slice_b200 needs a CUDA device (there is no CPU path)")
         self.lib = capi.load()
@@ -86,6 +87,12 @@ class BatchEngine:
         self._raw = None
         self._raw_struct = None
         self._keep = None
+        # graph=True: step() replays ONE captured CUDA graph of irs_step (its launches are fixed-pointer and allocate
+        # nothing).  Actions are staged into the blob's in_a0 / in_intra arrays, which the captured launch reads.
+        # For small batches (BASELINE config 2: 1,024 envs) the step is launch-bound, and a replay costs one launch.
+        self.graph = bool(graph)
+        self._graph = None
+        self._graph_key = None
 
     # -- plumbing ---------------------------------------------------------------------------
     def _stream(self):
@@ -196,9 +203,35 @@ class BatchEngine:
                 self.h, m.data_ptr() if m is not None else None, int(initial_episode),
                 ie.data_ptr() if ie is not None else None, C.byref(inj), self._raw_ref(), self._stream()))
 
+    def _step_graph(self, a0, intra):
+        """One step as a replay of the captured graph (native generators / device channel only: nothing is injected)."""
+        key = (a0 is not None, intra is not None, self._raw_struct is not None)
+        if a0 is not None:
+            self.v["in_a0"].copy_(a0 if isinstance(a0, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(a0, np.float64)),
+                                  non_blocking=True)
+        if intra is not None:
+            self.v["in_intra"].copy_(intra if isinstance(intra, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(intra, np.int32)),
+                                     non_blocking=True)
+        if self._graph is None or self._graph_key != key:
+            act = capi.Actions(self.v["in_a0"].data_ptr() if a0 is not None else None,
+                               self.v["in_intra"].data_ptr() if intra is not None else None)
+            inj = capi.Inject(None, None)
+            cur = torch.cuda.current_stream(self.device)
+            side = torch.cuda.Stream(self.device)
+            side.wait_stream(cur)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.device(self.device), torch.cuda.graph(g, stream=side):
+                capi.check(self.h, self.lib.irs_step(self.h, C.byref(act), C.byref(inj), self._raw_ref(),
+                                                     torch.cuda.current_stream(self.device).cuda_stream))
+            cur.wait_stream(side)
+            self._graph, self._graph_key, self._graph_keep = g, key, (act, inj)
+        self._graph.replay()
+
     def step(self, a0=None, intra=None, se=None, traffic=None, sched_bits=None):
         """CommunicationEnv.step for every env (comm_env.py:271-373).  Asynchronous.  `sched_bits` (int32/uint32
         [E, 25, 5], bit r of a UE's 135-bit row = RB r) gives the scheduling matrix directly instead of an action."""
+        if self.graph and se is None and traffic is None and sched_bits is None:
+            return self._step_graph(a0, intra)
         a0_t, in_t = self._dev(a0, torch.float64), self._dev(intra, torch.int32)
         se_t, tr_t = self._dev(se, torch.float64), self._dev(traffic, torch.float64)
         sb_t = None

@@ -368,7 +368,9 @@ class BatchedMARLCommEnv:
         if self._surface.flat or not isinstance(action, dict):
             # array actions -> scalar reward and plain bools (marl_comm_env.py:60-66)
             return obs, float(r[0]), done, done, {}
-        reward = {f"player_{i}": float(r[i]) for i in range(6)}
+        # calculate_reward_no_mask iterates over the formatted observation (common.py:396-439): the reward dict has the
+        # observation's key order - player_0, then the slices in sorted order
+        reward = {k: float(r[int(k.split("_")[1])]) for k in obs}
         term = {f"player_{i}": done for i in range(6)}
         term["__all__"] = done
         return obs, reward, term, dict(term), {}

@@ -117,7 +117,8 @@ class HistoryRecorder:
             if self.flat:
                 reward[k], obs[k], action[k] = float(h["reward"][k, 0]), h["obs0"][k], h["a0"][k]
                 continue
-            reward[k] = {f"player_{p}": float(h["reward"][k, p]) for p in range(6)}
+            order = [0] + [int(sl) + 1 for sl in h["order"][k]]  # common.py:396-439: the observation's key order
+            reward[k] = {f"player_{p}": h["reward"][k, p] for p in order}  # np.float64 values, like the reference
             o = {"player_0": {"observations": h["obs0"][k], "action_mask": h["mask0"][k]}}
             for sl in h["order"][k]:  # insertion order = sorted slices (ib_sched.py:91,186-200)
                 o[f"player_{int(sl) + 1}"] = {"observations": h["obsi"][k, sl], "action_mask": h["maski"][k, sl]}

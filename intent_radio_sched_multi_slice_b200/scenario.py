@@ -40,6 +40,9 @@ SLICE_TYPES = [
     ("video_streaming_4k", 0, None, None, 30, 10240, 100, 65536, 30, 2, 5),
 ]
 SLICE_TYPE_NAMES = [t[0] for t in SLICE_TYPES]
+# "mobility" (km/h) of the UEs of each type: carried in the slice_req dicts (history files, agent callbacks) for
+# fidelity with the reference's files; nothing on the path reads it (mobilities/simple.py is constant)
+SLICE_MOBILITY = [0, 72, 0, 0, 0, 30, 30, 0, 0, 0]
 
 SLICE_DTYPE = np.dtype(
     [
@@ -64,8 +67,8 @@ def slice_req_from_type(type_id: int) -> dict:
         params[f"par{len(params)+1}"] = {"name": "throughput", "value": thr, "unit": "Mbps", "operator": "at_least"}
     return {
         "name": name, "priority": prio, "parameters": params,
-        "ues": {"buffer_size": bsz, "buffer_latency": blat, "message_size": msg, "traffic": traffic,
-                "min_number_ues": umin, "max_number_ues": umax},
+        "ues": {"buffer_size": bsz, "buffer_latency": blat, "message_size": msg, "mobility": SLICE_MOBILITY[type_id],
+                "traffic": traffic, "min_number_ues": umin, "max_number_ues": umax},
     }
 
 

@@ -92,7 +92,7 @@ def test_env_api_replays_reference_trace(name, agent, n, bank):
         check_obs(obs, d["obs0"][k], d["mask0"][k], d["obs_i"][k], d["mask_i"][k], d["order"][k], f"step {k}")
         done = bool(d["done"][k])
         if agent == "IBSched":
-            assert list(reward.keys()) == [f"player_{i}" for i in range(6)]
+            assert list(reward.keys()) == list(obs.keys())  # common.py:396-439 iterates over the formatted observation
             np.testing.assert_allclose([reward[f"player_{i}"] for i in range(6)], d["reward"][k], rtol=1e-5, atol=1e-300)
             assert term["__all__"] == done and trunc["__all__"] == done and term["player_3"] == done
         else:
