@@ -533,11 +533,9 @@ def run_b200(args):
     from intent_radio_sched_multi_slice_b200 import distributed as D
     metrics_named = D.all_reduce_metrics(eng.episode_metrics_device(), dev)  # the path's one collective (NCCL when N > 1)
 
-    # kernels per irs_step (irs_capi.cu launch_step): k_action[_t], k_ue_env, k_env_tail[_t], and k_rollover after the
-    # thread-per-env tail (launches of >= IRS_SERIAL_MIN_ENVS envs, default 49,152)
-    # at most IRS_FUSED_MAX_ENVS envs (default 2,368): the whole step is ONE launch (k_env_step)
-    launches_per_step = 1 if E <= int(os.environ.get("IRS_FUSED_MAX_ENVS", "2368")) else \
-        (4 if E >= int(os.environ.get("IRS_SERIAL_MIN_ENVS", "49152")) else 3)
+    # kernels per irs_step (irs_capi.cu launch_step): ONE (k_env_step) up to IRS_FUSED_MAX_ENVS envs (default 2,368), else
+    # k_action_8 | k_action_t, k_ue_env, k_env_tail_8 | k_env_tail_t and k_rollover (auto-reset)
+    launches_per_step = 1 if E <= int(os.environ.get("IRS_FUSED_MAX_ENVS", "2368")) else 4
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_oracle_run(args, bank, args.cpu_envs, warmup=5, fill=n_fill)

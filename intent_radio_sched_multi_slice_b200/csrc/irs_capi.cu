@@ -17,6 +17,7 @@ static double wall_ms() { timespec t; clock_gettime(CLOCK_MONOTONIC, &t); return
 #include "irs_ue.cuh"
 #include "irs_fused.cuh"
 #include "irs_serial.cuh"
+#include "irs_lane8.cuh"
 #include "irs_alt.cuh"
 
 #define IRS_MAX_HOST_CHUNKS 16
@@ -42,6 +43,9 @@ struct irs_env {
     int fused_max;                 // IRS_FUSED_MAX_ENVS (default 2,368): launches of at most this many envs run the whole
                                    // step in ONE kernel (k_env_step) - small batches are bound by launch and dependency
                                    // latency, not by throughput
+    int per_env;                   // IRS_PER_ENV: how the per-env stages of a launch above fused_max run - 0 / "lane8": eight
+                                   // lanes per env (measured fastest from 2,368 to 65,536 envs per launch), "warp": one warp
+                                   // per env, "thread": one thread per env
     int serial_min;                // IRS_SERIAL_MIN_ENVS (default 49,152): launches covering at least this many envs
                                    // use the thread-per-env action / tail kernels (irs_serial.cuh); below that one
                                    // thread per env leaves the SMs too empty to hide its serial latency
@@ -172,6 +176,8 @@ int irs_create(const irs_config* cfg, int32_t n_lambda, irs_env** out)
     env->host_streams = hs_ ? atoi(hs_) : 1;
     const char* fm_ = getenv("IRS_FUSED_MAX_ENVS");
     env->fused_max = fm_ ? atoi(fm_) : 2368;
+    const char* pe_ = getenv("IRS_PER_ENV");
+    env->per_env = !pe_ ? 0 : (!strcmp(pe_, "warp") ? 1 : (!strcmp(pe_, "lane8") ? 2 : (!strcmp(pe_, "thread") ? 3 : 0)));
     const char* sm_ = getenv("IRS_SERIAL_MIN_ENVS");
     env->serial_min = sm_ ? atoi(sm_) : 49152;
     compute_layout(env->cfg, n_lambda, &env->lay);
@@ -317,9 +323,12 @@ static int launch_step(irs_env* env, const StepArgs& A, cudaStream_t st, bool pr
         CK(cudaGetLastError());
         return IRS_OK;
     }
-    const bool serial = E >= env->serial_min;
+    const int per_env = env->per_env ? env->per_env : 2;
+    const bool serial = per_env == 3, lane8 = per_env == 2;
+    const unsigned l8_blocks = (unsigned)(((size_t)E * 8 + L8_THREADS - 1) / L8_THREADS);
     nvtxRangePushA("action->RB");
     if (A.sched_bits) k_sched_runs<<<(E + 7) / 8, 256, 0, st>>>(A);
+    else if (lane8) k_action_8<<<l8_blocks, L8_THREADS, 0, st>>>(A);
     else if (serial) k_action_t<<<(E + SERIAL_THREADS - 1) / SERIAL_THREADS, SERIAL_THREADS, 0, st>>>(A);
     else k_action<<<(E + 7) / 8, 256, 0, st>>>(A);
     nvtxRangePop();
@@ -336,7 +345,9 @@ static int launch_step(irs_env* env, const StepArgs& A, cudaStream_t st, bool pr
     const bool alt = env->cfg.surface != 0; // SchedTWC / SchedColORAN: their surface reads the step's records before
                                             // finished envs roll over, then once more for the reset observation
     const unsigned env_blocks = (E + ENV_WARPS - 1) / ENV_WARPS;
-    if (serial) {
+    if (lane8) {
+        k_env_tail_8<<<l8_blocks, L8_THREADS, 0, st>>>(A);
+    } else if (serial) {
         k_env_tail_t<<<(E + SERIAL_THREADS - 1) / SERIAL_THREADS, SERIAL_THREADS, 0, st>>>(A);
     } else {
         StepArgs B = A;
@@ -344,7 +355,7 @@ static int launch_step(irs_env* env, const StepArgs& A, cudaStream_t st, bool pr
         k_env_tail<<<env_blocks, ENV_WARPS * 32, 0, st>>>(B);
     }
     if (alt) k_surface_alt<<<env_blocks, ENV_WARPS * 32, 0, st>>>(A, 0);
-    if ((serial || alt) && env->cfg.auto_reset) {
+    if ((serial || lane8 || alt) && env->cfg.auto_reset) {
         k_rollover<<<(E + ENV_WARPS * ROLL_ENVS - 1) / (ENV_WARPS * ROLL_ENVS), ENV_WARPS * 32, 0, st>>>(A);
         if (alt) k_surface_alt<<<env_blocks, ENV_WARPS * 32, 0, st>>>(A, 1);
     }

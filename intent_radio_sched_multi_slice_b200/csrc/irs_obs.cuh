@@ -30,8 +30,15 @@ struct SliceView { // valid on lanes 0..4 (slice = lane)
 // common.py:9-65 + 68-340 for one UE; r = intent_overfulfillment_rate 0.2 (ib_sched.py:53)
 // `mul` = 2 when the agent pushes every frame twice into the window (win[1] is then the newest frame again and
 // every window sum counts each kept frame twice), else 1.
+// Each metric ends in ONE division: the reference's two alternatives (intent met: distance over the over-fulfilment
+// band; intent violated: distance over the requirement) are a choice of numerator and denominator, so neighbouring
+// lanes that take different sides still share the division (float64 division is ~35 instructions and these were
+// two thirds of the per-UE cost of the tail kernels).  Same operands, same operation: bit-identical results.
+// reliability target t = (100 - v) / 100 of a slice (common.py:188-233): a per-slice constant that a caller looping over
+// UEs computes once per slice
+__device__ __forceinline__ double rel_target(const irs_slice* sl) { return (100 - __ldg(&sl->rel_value)) / 100; }
 __device__ __forceinline__ void intent_drift_ue(const irs_slice* sl, int flags, const UeFrame& f, int win_len, int mul,
-                                                double (&drift)[3])
+                                                double (&drift)[3], const double* rel_t = nullptr)
 {
     const double r = 0.2;
     drift[0] = drift[1] = drift[2] = 0;
@@ -41,34 +48,27 @@ __device__ __forceinline__ void intent_drift_ue(const irs_slice* sl, int flags, 
         bool zero = isclose0(f.occ);                                                        // :104-107
         if (win_len * mul > 1) zero = zero || (mul == 2 ? isclose0(f.occ) : f.occ1z);          // :108-116
         if (zero) m = v * (1.1 + r);                                                        // :117-119
-        if (m >= v) {
-            if (m > v * (1 + r)) drift[0] += 1;        // :164-168
-            else drift[0] += (m - v) / (v * r);        // :154-162
-        } else {
-            drift[0] -= (v - m) / v;                   // :172-181
-        }
+        const bool ok = m >= v;
+        const double q = (ok ? m - v : v - m) / (ok ? v * r : v); // :154-162 (m - v) / (v r) | :172-181 (v - m) / v
+        drift[0] = ok ? (m > v * (1 + r) ? 1.0 : 0.0 + q) : 0.0 - q; // :164-168 capped at 1 (0 +- q: the reference's own signed zeros)
     }
     if (flags & IRS_F_REL) {
         const double v = __ldg(&sl->rel_value);
         const double den = (f.occ * __ldg(&sl->buffer_size) + (double)(f.sum_drop * mul)) + (double)(f.sum_sent * mul); // :40-47
         const double m = den != 0 ? (double)(f.sum_drop * mul) / den : 0.0;                                      // :48-53
-        const double t = (100 - v) / 100;
-        if (100 * (1 - m) >= v) {                      // :124-126
-            if (m < t * (1 - r)) drift[1] += 1;        // :188-220
-            else drift[1] += (t - m) / (t * r);
-        } else {
-            drift[1] -= (m - t) / (v / 100);           // :223-233
-        }
+        const double t = rel_t ? *rel_t : rel_target(sl);
+        const bool ok = 100 * (1 - m) >= v;                        // :124-126
+        double den2 = t * r;
+        if (!ok) den2 = v / 100;                                   // violated (rare): the other denominator
+        const double q = (ok ? t - m : m - t) / den2; // :188-220 (t - m) / (t r) | :223-233 (m - t) / (v / 100)
+        drift[1] = ok ? (m < t * (1 - r) ? 1.0 : 0.0 + q) : 0.0 - q;
     }
     if (flags & IRS_F_LAT) {
         const double v = __ldg(&sl->lat_value);
         const double m = f.lat;
-        if (m <= v) {
-            if (m < v * (1 - r)) drift[2] += 1;        // :290-319
-            else drift[2] += (v - m) / (v * r);
-        } else {
-            drift[2] -= (m - v) / (__ldg(&sl->buffer_latency) - v); // :322-335
-        }
+        const bool ok = m <= v;
+        const double q = (ok ? v - m : m - v) / (ok ? v * r : __ldg(&sl->buffer_latency) - v); // :290-319 | :322-335
+        drift[2] = ok ? (m < v * (1 - r) ? 1.0 : 0.0 + q) : 0.0 - q;
     }
 }
 

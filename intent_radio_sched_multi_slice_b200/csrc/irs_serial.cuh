@@ -303,6 +303,9 @@ __global__ void __launch_bounds__(SERIAL_THREADS, TAIL_T_MINB) k_env_tail_t(cons
         snt[s] = 0; n_s[s] = 0; rbs_alloc[s] = 0;
         flags[s] = __ldg(&sc->sl[s].flags);
     }
+    double rel_t[S]; // the reliability target of each slice: one division per slice instead of per UE
+#pragma unroll
+    for (int s = 0; s < S; ++s) rel_t[s] = rel_target(&sc->sl[s]);
     long long t_sent = 0, t_drop = 0, t_inc = 0;
     IRS_UNROLL(TAIL_UNROLL)
     for (int u = 0; u < U; ++u) {
@@ -320,7 +323,8 @@ __global__ void __launch_bounds__(SERIAL_THREADS, TAIL_T_MINB) k_env_tail_t(cons
         f.occ = d0.x; f.lat = d0.y; f.sebar = sebar; f.sent = lo.w; f.sum_sent = lo.y; f.sum_drop = lo.z;
         f.rb_count = st.rb[eu].y; f.occ1z = hi.z != 0;
         double drift[3] = {0, 0, 0};
-        if (fl & IRS_F_REQ) intent_drift_ue(sl, fl, f, win_len, A.win_mul, drift);
+        const double rt = sel5(rel_t, s);
+        if (fl & IRS_F_REQ) intent_drift_ue(sl, fl, f, win_len, A.win_mul, drift, &rt);
         int j = 0;
 #pragma unroll
         for (int ss = 0; ss < S; ++ss) {

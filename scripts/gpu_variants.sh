@@ -1,11 +1,8 @@
 #!/bin/bash
-# a short bench per library variant under build_variants/ (IRS_LIB_PATH) plus the default build; WL="sweep mix" picks workloads
+# build variants (build_variants/lib_<tag>.so) against the default library: default sweep, device-timed
 mkdir -p gpurun_out
-for w in ${WL:-sweep}; do
-  python bench.py --workload $w --steps 100 --warmup 10 --no-cpu-baseline --no-e2e > gpurun_out/var_default_$w.json 2> gpurun_out/var_default_$w.err
-  for f in build_variants/*.so; do
-    [ -f "$f" ] || continue
-    n=$(basename $f .so)
-    IRS_LIB_PATH=$PWD/$f python bench.py --workload $w --steps 100 --warmup 10 --no-cpu-baseline --no-e2e > gpurun_out/var_${n}_$w.json 2> gpurun_out/var_${n}_$w.err
-  done
+python bench.py --steps 60 --no-cpu-baseline --no-e2e > gpurun_out/bench_var_default.json 2> gpurun_out/bench_var_default.err
+for f in build_variants/lib_*.so; do
+  tag=$(basename $f .so); tag=${tag#lib_}
+  IRS_LIB_PATH=$PWD/$f python bench.py --steps 60 --no-cpu-baseline --no-e2e > gpurun_out/bench_var_$tag.json 2> gpurun_out/bench_var_$tag.err
 done

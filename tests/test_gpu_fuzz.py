@@ -48,14 +48,14 @@ def _random_bank(rng, n):
     return bank
 
 
-@pytest.mark.parametrize("family", ["one_launch", "warp_per_env", "thread_per_env"])
+@pytest.mark.parametrize("family", ["one_launch", "warp_per_env", "lane8", "thread_per_env"])
 @pytest.mark.parametrize("seed", [0, 1])
 def test_fuzzed_scenarios_match_oracle(seed, family, monkeypatch):
     from oracle import oracle
 
     if family != "one_launch":  # k_env_step (default for small batches) / warp-per-env / thread-per-env kernels
         monkeypatch.setenv("IRS_FUSED_MAX_ENVS", "0")
-        monkeypatch.setenv("IRS_SERIAL_MIN_ENVS", "1" if family == "thread_per_env" else str(1 << 30))
+        monkeypatch.setenv("IRS_PER_ENV", {"warp_per_env": "warp", "lane8": "lane8", "thread_per_env": "thread"}[family])
     rng = np.random.default_rng(100 + seed)
     n_scen, E, steps = 48, 192, 45
     bank = _random_bank(rng, n_scen)

@@ -16,15 +16,16 @@ from gpu_adapter import OUT_KEYS, CudaEnv, compare_outputs
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(autouse=True, params=["one_launch", "warp_per_env", "thread_per_env"])
+@pytest.fixture(autouse=True, params=["one_launch", "warp_per_env", "lane8", "thread_per_env"])
 def per_env_kernels(request, monkeypatch):
-    """Every test of this file runs with the three ways a step is launched: k_env_step (the whole step of an env in one
-    warp and ONE launch; the default up to 2,368 envs per launch), k_action / k_ue_env / k_env_tail (one warp per env;
-    mid-size batches and the chunks of irs_step_host), and k_action_t / k_env_tail_t + k_rollover around k_ue_env (one
-    thread per env, the default from 49,152 envs per launch; irs_serial.cuh)."""
+    """Every test of this file runs with the four ways a step is launched: k_env_step (the whole step of an env in one
+    warp and ONE launch; the default up to 2,368 envs per launch), and k_ue_env between the per-env stages as one warp
+    per env (k_action / k_env_tail), eight lanes per env (k_action_8 / k_env_tail_8; the default for mid-size launches
+    and the chunks of irs_step_host) or one thread per env (k_action_t / k_env_tail_t, the default from 49,152 envs per
+    launch)."""
     if request.param != "one_launch":
         monkeypatch.setenv("IRS_FUSED_MAX_ENVS", "0")
-        monkeypatch.setenv("IRS_SERIAL_MIN_ENVS", "1" if request.param == "thread_per_env" else str(1 << 30))
+        monkeypatch.setenv("IRS_PER_ENV", {"warp_per_env": "warp", "lane8": "lane8", "thread_per_env": "thread"}[request.param])
 
 TRACES = ["cfg1_marr", "mapf", "ibsched_mimic", "ibsched_fixed", "seq_mimic", "seq_fixed", "sweep_scen", "twc", "colran",
           "random_eps"]
