@@ -318,7 +318,7 @@ static int launch_step(irs_env* env, const StepArgs& A, cudaStream_t st, bool pr
     if (profile) CK(cudaEventRecord(env->ev[0], st));
     if (E <= env->fused_max && env->cfg.surface == 0 && !A.sched_bits && !A.raw.se_used) {
         if (profile) CK(cudaEventRecord(env->ev[1], st));
-        k_env_step<<<(E + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(A);
+        k_env_step<<<E, STEP_WARPS * 32, 0, st>>>(A); // one block per env
         if (profile) { CK(cudaEventRecord(env->ev[2], st)); CK(cudaEventRecord(env->ev[3], st)); }
         CK(cudaGetLastError());
         return IRS_OK;
@@ -542,6 +542,15 @@ static int copy_surface(irs_env* env, const irs_host_surface* o, bool with_rewar
 static int host_chunk_plan(irs_env* env, size_t* bounds /* [IRS_MAX_HOST_CHUNKS + 1] */)
 {
     const size_t E = (size_t)env->cfg.num_envs;
+    static const char* plan = getenv("IRS_HOST_PLAN");
+    if (env->host_chunks <= 0 && E >= 16384 && plan && !strcmp(plan, "geom")) { // small first chunk, doubling sizes
+        size_t s = env->fused_max >= 1024 ? (size_t)env->fused_max : 2368, done = 0;
+        int n = 0;
+        bounds[0] = 0;
+        while (E - done > 2 * s && n < IRS_MAX_HOST_CHUNKS - 1) { done += s; bounds[++n] = done; s *= 2; }
+        bounds[++n] = E;
+        return n;
+    }
     int chunks = env->host_chunks > 0 ? env->host_chunks : (E < 16384 ? 1 : 4);
     if (chunks > IRS_MAX_HOST_CHUNKS) chunks = IRS_MAX_HOST_CHUNKS;
     size_t per = (E + chunks - 1) / chunks;

@@ -48,18 +48,26 @@ __device__ __forceinline__ T sel4(const T (&a)[GRP], int j)
 
 // FULL_STEP = false: the per-UE middle of the step, between k_action and k_env_tail (large batches: every warp of the
 //                    GPU runs the same small code region).
-// FULL_STEP = true : the whole step of the env in this warp - action -> RB runs before, observation / reward /
-//                    rollover after, on the registers the middle leaves behind.  For SMALL batches (BASELINE config 2:
-//                    1,024 envs) the step is bound by launch and dependency latency, and one launch replaces three.
-template <bool FULL_STEP, bool RAWSE>
-__device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP][136], const float2* __restrict__ ntab)
+// FULL_STEP = true : the whole step of ONE env in ONE block of four warps and one launch - for SMALL batches
+//                    (BASELINE config 2: 1,024 envs), where the step is bound by launch and dependency latency.
+//                    Warp 0 turns the action into RB runs (lane = UE) and hands them over through shared memory; the
+//                    four warps share the env's UEs (u mod 4) for the middle; the per-UE frames go back through shared
+//                    memory and warp 0 finishes with observation / reward / rollover.
+struct StepXchg { // hand-over between the warps of a k_env_step block
+    short2 rb[32];
+    double occ[32], lat[32], sebar[32];
+    int sent[32], sum_sent[32], sum_drop[32], dropped[32], inc[32], occ1z[32];
+};
+template <bool FULL_STEP, bool RAWSE, int NW>
+__device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP][136], const float2* __restrict__ ntab,
+                                            StepXchg* xc = nullptr)
 {
     const DevState& st = A.st;
     const irs_config& cfg = A.cfg;
     const int lane = lane_id();
     const int wib = threadIdx.x >> 5;
-    const int split = FULL_STEP ? 0 : A.ue_split_log2, gmask = (1 << split) - 1;
-    const int wglob = blockIdx.x * FUSED_WARPS + wib;
+    const int split = FULL_STEP ? (NW == 4 ? 2 : (NW == 2 ? 1 : 0)) : A.ue_split_log2, gmask = (1 << split) - 1;
+    const int wglob = blockIdx.x * NW + wib;
     const int e = A.env_begin + (wglob >> split), grp = wglob & gmask; // this warp serves the UEs u with (u & gmask) == grp
     if (e >= A.env_end) { normal_tab_wait(); return; } // every warp of the block meets the table barrier exactly once
 
@@ -95,8 +103,16 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
         look[k] = (ue_lane && a_old - k >= 1) ? row[q >= up.depth ? q - up.depth : q] : 0;
     }
     int rb_s, rb_c;
-    if (FULL_STEP) { // ib_sched.py:223-349 on this lane's previous frame (occupancy, mean SE, window sum of sent packets)
-        action_to_rb_core(A, e, sc, rec_d0.x, st.ue_d[eu * UD_N + UD_SEBAR], rec_a.y, win_len, step, episode, rb_s, rb_c);
+    if (FULL_STEP) { // ib_sched.py:223-349 on every UE's previous frame (occupancy, mean SE, window sum of sent packets)
+        if (wib == 0) {
+            const size_t ea = (size_t)e * U + (lane < U ? lane : 0);
+            int rs_a, rc_a;
+            action_to_rb_core(A, e, sc, st.ue_d[ea * UD_N + UD_OCC], st.ue_d[ea * UD_N + UD_SEBAR],
+                              st.ue_i[ea * UI_N + UI_SUM_SENT], win_len, step, episode, rs_a, rc_a);
+            xc->rb[lane] = make_short2((short)rs_a, (short)rc_a);
+        }
+        __syncthreads();
+        rb_s = xc->rb[lane].x; rb_c = xc->rb[lane].y;
     } else {
         const short2 run = st.rb[eu];
         rb_s = run.x; rb_c = run.y;
@@ -435,12 +451,19 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
         if (FULL_STEP) st.rb[eu] = make_short2((short)rb_s, (short)rb_c);
     }
     if (!FULL_STEP) return;
-    // ---- phase 6: observation, reward, metrics, done, rollover (comm_env.py:339-373) ----------
+    // ---- phase 6: observation, reward, metrics, done, rollover (comm_env.py:339-373), by warp 0 on every UE's frame
+    if (ue_lane) {
+        xc->occ[lane] = occ; xc->lat[lane] = lat; xc->sebar[lane] = sebar;
+        xc->sent[lane] = sent; xc->sum_sent[lane] = sum_sent; xc->sum_drop[lane] = sum_drop;
+        xc->dropped[lane] = dropped; xc->inc[lane] = (int)inc; xc->occ1z[lane] = occ1z ? 1 : 0;
+    }
+    __syncthreads();
+    if (wib != 0) return;
     UeFrame f;
-    f.occ = occ; f.lat = lat; f.sebar = sebar; f.sent = sent; f.sum_sent = sum_sent; f.sum_drop = sum_drop;
-    f.rb_count = rb_c; f.occ1z = occ1z;
-    __syncwarp();
-    env_tail_core(A, e, sc, f, dropped, (int)inc, win_len, head_w, step, sm[wib][0]);
+    const int lu = lane < U ? lane : 0;
+    f.occ = xc->occ[lu]; f.lat = xc->lat[lu]; f.sebar = xc->sebar[lu]; f.sent = xc->sent[lu];
+    f.sum_sent = xc->sum_sent[lu]; f.sum_drop = xc->sum_drop[lu]; f.rb_count = xc->rb[lu].y; f.occ1z = xc->occ1z[lu] != 0;
+    env_tail_core(A, e, sc, f, xc->dropped[lu], xc->inc[lu], win_len, head_w, step, sm[0][0]);
 }
 
 #ifndef UE_ENV_MINB
@@ -451,7 +474,7 @@ __global__ void __launch_bounds__(FUSED_WARPS * 32, UE_ENV_MINB) k_ue_env(const 
     __shared__ __align__(16) double sm[FUSED_WARPS][GRP][136];
     __shared__ __align__(16) float2 ntab[IRS_NORMAL_TAB_N];
     normal_tab_request(ntab);
-    ue_env_body<false, false>(A, sm, ntab);
+    ue_env_body<false, false, FUSED_WARPS>(A, sm, ntab);
 }
 // same kernel with the optional per-RB SE output (irs_raw_outputs.se_used; tests and trace dumps)
 __global__ void __launch_bounds__(FUSED_WARPS * 32, UE_ENV_MINB) k_ue_env_raw(const __grid_constant__ StepArgs A)
@@ -459,17 +482,22 @@ __global__ void __launch_bounds__(FUSED_WARPS * 32, UE_ENV_MINB) k_ue_env_raw(co
     __shared__ __align__(16) double sm[FUSED_WARPS][GRP][136];
     __shared__ __align__(16) float2 ntab[IRS_NORMAL_TAB_N];
     normal_tab_request(ntab);
-    ue_env_body<false, true>(A, sm, ntab);
+    ue_env_body<false, true, FUSED_WARPS>(A, sm, ntab);
 }
 
-// the whole step in one launch (small batches; IBSched-family surface, no per-RB raw output)
-#ifndef ENV_STEP_MINB
-#define ENV_STEP_MINB 4
+// the whole step in one launch, one block of STEP_WARPS warps per env (small batches; IBSched-family surface, no per-RB
+// raw output)
+#ifndef STEP_WARPS
+#define STEP_WARPS 2
 #endif
-__global__ void __launch_bounds__(FUSED_WARPS * 32, ENV_STEP_MINB) k_env_step(const __grid_constant__ StepArgs A)
+#ifndef ENV_STEP_MINB
+#define ENV_STEP_MINB 8
+#endif
+__global__ void __launch_bounds__(STEP_WARPS * 32, ENV_STEP_MINB) k_env_step(const __grid_constant__ StepArgs A)
 {
-    __shared__ __align__(16) double sm[FUSED_WARPS][GRP][136];
+    __shared__ __align__(16) double sm[STEP_WARPS][GRP][136];
     __shared__ __align__(16) float2 ntab[IRS_NORMAL_TAB_N];
+    __shared__ StepXchg xc;
     normal_tab_request(ntab);
-    ue_env_body<true, false>(A, sm, ntab);
+    ue_env_body<true, false, STEP_WARPS>(A, sm, ntab, &xc);
 }

@@ -17,7 +17,7 @@
 
 #define L8_THREADS 128 /* 16 envs per block */
 #ifndef L8_TAIL_MINB
-#define L8_TAIL_MINB 4 /* resident blocks per SM the tail's register budget is set for */
+#define L8_TAIL_MINB 6 /* 80 registers: measured fastest (4: 0.128 ms, 6: 0.111, 8: 0.120 at 65,536 envs) */
 #endif
 #ifndef L8_ACTION_MINB
 #define L8_ACTION_MINB 8

@@ -25,6 +25,6 @@ ncu --set full --clock-control none --import-source on -k regex:k_ue_env -s 518 
     python bench.py --workload trace --fill 512 --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu_full_trace.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:k_ue_env -s 1670 -c 1 -f -o gpurun_out/k_ue_env_d401 \
     python bench.py --depth 401 --fill 1664 --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu_full_d401.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:"k_action_t|k_env_tail_t" -s 1030 -c 2 -f -o gpurun_out/k_per_env_mix \
+ncu --set full --clock-control none --import-source on -k regex:"k_action_8|k_env_tail_8" -s 1030 -c 2 -f -o gpurun_out/k_per_env_mix \
     python bench.py --workload mix --fill 512 --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu_full_perenv.log 2>&1
 ls -la gpurun_out | tail -30
