@@ -203,8 +203,25 @@ class BatchedMARLCommEnv:
                 tr[e] = self._tf[e].step(sua, req, int(step[e]), int(episode[e]))
         return se, tr
 
-    def _predict_episode(self, step, ep, initial_episode):
-        """comm_env.py:415-433 for one env (host mirror, used only by the host hook path)."""
+    def _predict_episode(self, step, ep, initial_episode, e=0, cycle=None):
+        """comm_env.py:415-444 for one env (host mirror, used only by the host hook path: a host Channel plugin is
+        asked for the reset frame of the NEXT episode before the device has moved to it).  `cycle` = this env's
+        (position, permutation number, first episode) when enable_random_episodes."""
+        if self.enable_random_episodes:
+            from . import scenario as scn
+            pos, gen, base = cycle
+            moved = False
+            if initial_episode != -1:
+                base, gen, pos, moved = initial_episode, gen + 1, 0, True
+            if step == self.max_number_steps:
+                pos, moved = pos + 1, True
+            n = self.max_number_episodes - base
+            if n <= 0:
+                raise Exception("Episode number received is greater than the maximum number of episodes")
+            if self.eng is not None and getattr(self.eng, "_order", None) is not None:
+                order = self.eng._order[e].cpu().numpy()
+                return int(order[pos % len(order)]) if moved else ep
+            return scn.shuffled_episode(int(self.seed), self.env_id_base + e, gen, base, n, pos % n) if moved else ep
         init = initial_episode if initial_episode != -1 else self.initial_episode_number
         last = self.max_number_episodes - 1
         if (step == 0 and ep == 0) or (step == self.max_number_steps and ep == last) or initial_episode != -1:
@@ -231,9 +248,11 @@ class BatchedMARLCommEnv:
             st, ep = eng.v["step"].cpu().numpy(), eng.v["episode"].cpu().numpy()
             m = np.ones(self.num_envs, bool) if mask is None else np.asarray(mask, bool)
             saved = (st.copy(), ep.copy())
+            cyc = [eng.v[k].cpu().numpy() for k in ("ep_pos", "ep_gen", "ep_base")] if self.enable_random_episodes else None
             for e in np.flatnonzero(m):  # the channel's reset frame belongs to the NEW episode, step 0
                 ie = int(initial_episodes[e]) if initial_episodes is not None else initial_episode
-                ep[e], st[e] = self._predict_episode(int(st[e]), int(ep[e]), ie), 0
+                cy = (int(cyc[0][e]), int(cyc[1][e]), int(cyc[2][e])) if cyc is not None else None
+                ep[e], st[e] = self._predict_episode(int(st[e]), int(ep[e]), ie, int(e), cy), 0
             eng.v["step"].copy_(torch.from_numpy(st)); eng.v["episode"].copy_(torch.from_numpy(ep))
             se, _ = self._hook_frames(reset_mask=m)
             eng.v["step"].copy_(torch.from_numpy(saved[0])); eng.v["episode"].copy_(torch.from_numpy(saved[1]))

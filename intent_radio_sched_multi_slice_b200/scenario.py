@@ -78,6 +78,51 @@ def _operator_name(op) -> str:
     return {"greater_equal": "at_least", "less_equal": "at_most"}.get(getattr(op, "__name__", ""), "unsupported")
 
 
+def _philox4x32_7(counter, k0, k1):
+    """Philox4x32-7 on Python ints (csrc/irs_rng.cuh philox4x32_7): host mirror for the few places that must predict
+    a device draw (the shuffled episode order below)."""
+    c = [int(x) & 0xFFFFFFFF for x in counter]
+    k0, k1 = int(k0) & 0xFFFFFFFF, int(k1) & 0xFFFFFFFF
+    for _ in range(7):
+        p0, p1 = 0xD2511F53 * c[0], 0xCD9E8D57 * c[2]
+        c = [((p1 >> 32) ^ c[1] ^ k0) & 0xFFFFFFFF, p1 & 0xFFFFFFFF, ((p0 >> 32) ^ c[3] ^ k1) & 0xFFFFFFFF, p0 & 0xFFFFFFFF]
+        k0, k1 = (k0 + 0x9E3779B9) & 0xFFFFFFFF, (k1 + 0xBB67AE85) & 0xFFFFFFFF
+    return c
+
+
+def _mix32(x):
+    x &= 0xFFFFFFFF
+    x ^= x >> 16
+    x = (x * 0x7FEB352D) & 0xFFFFFFFF
+    x ^= x >> 15
+    x = (x * 0x846CA68B) & 0xFFFFFFFF
+    x ^= x >> 16
+    return x
+
+
+def shuffled_episode(seed: int, gid: int, gen: int, base: int, n: int, pos: int) -> int:
+    """Element `pos` of the episode permutation an env plays with enable_random_episodes (comm_env.py:219-226,
+    434-444) - the host mirror of csrc/irs_rng.cuh shuffled_episode (8-round Feistel network, cycle walking)."""
+    K_PERM = 5
+    k = _philox4x32_7([K_PERM << 16, gen, 0, gid], seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
+    if n <= 1:
+        return base
+    bits = 1
+    while (1 << bits) < n:
+        bits += 1
+    bits += bits & 1
+    half = bits >> 1
+    mask = (1 << half) - 1
+    x = pos
+    while True:
+        l, r = x >> half, x & mask
+        for j in range(8):
+            l, r = r, l ^ (_mix32(r ^ k[j & 3] ^ ((j * 0x9E3779B9) & 0xFFFFFFFF)) & mask)
+        x = (l << half) | r
+        if x < n:
+            return base + x
+
+
 _OPERATORS = {"at_least": np.greater_equal, "at_most": np.less_equal}
 
 

@@ -81,3 +81,22 @@ def test_random_episode_cycle_in_the_oracle(bank):
     again = np.array(again)
     for e in range(E):
         assert sorted(again[:3, e]) == [8, 9, 10] and again[3, e] == again[0, e]
+
+
+def test_host_mirror_of_the_episode_permutation(bank):
+    """scenario.shuffled_episode (used by the env when a HOST channel plugin must be asked for the next episode's reset
+    frame before the device has moved on) equals the permutation the oracle / the kernels play."""
+    from intent_radio_sched_multi_slice_b200 import scenario as scn
+
+    for c, k0, k1 in [([1, 2, 3, 4], 5, 6), ([0xFFFFFFFF, 0, 7, 99], 0x12345678, 0x9ABCDEF0)]:
+        assert scn._philox4x32_7(c, k0, k1) == [int(x) for x in oracle.philox(c, k0, k1)]
+    E, seed = 5, (7 << 32) + 11
+    env = oracle.OracleEnv(bank.array(), bank.poisson_cdf(), E, channel_mode=1, traffic_mode=1, policy=1, fixed_intra=0,
+                           sort_slices=0, max_steps=1, max_episodes=23, initial_episode=4, auto_reset=1, random_episodes=1,
+                           seed=seed, env_id_base=40)
+    env.reset()
+    for k in range(25):
+        ep = env.state()["episode"]
+        for e in range(E):
+            assert ep[e] == scn.shuffled_episode(seed, 40 + e, 0, 4, 19, k % 19), (k, e)
+        env.step()

@@ -41,7 +41,8 @@ def _trace_plugins(rse, sse, stf):
 @pytest.mark.parametrize("name,agent,n", [("ibsched_mimic", "IBSched", 150), ("seq_fixed", "IBSched", 100),
                                           ("cfg1_marr", "MARR", 120), ("mapf", "MAPF", 120),
                                           ("quadriga", "IBSched", 100), ("quadriga_seq", "IBSched", 100),
-                                          ("twc", "SchedTWC", 220), ("colran", "SchedColORAN", 220)])
+                                          ("twc", "SchedTWC", 220), ("colran", "SchedColORAN", 220),
+                                          ("random_eps", "IBSched", 375)])
 def test_env_api_replays_reference_trace(name, agent, n, bank):
     from intent_radio_sched_multi_slice_b200 import agents, plugins
     from intent_radio_sched_multi_slice_b200.env import MARLCommEnv
@@ -56,11 +57,16 @@ def test_env_api_replays_reference_trace(name, agent, n, bank):
     Assoc = plugins.MultSliceAssociation if meta["assoc"] == "mult_slice" else plugins.MultSliceAssociationSeq
     env = MARLCommEnv(Ch, Tr, plugins.SimpleMobility, Assoc, "mult_slice", agent.lower(), int(meta["seed"]),
                       root_path="/nonexistent", initial_episode_number=int(meta["initial_episode"]),
-                      max_episode_number=int(meta["max_episodes"]), save_hist=False, debug=True, scenario_bank=bank)
+                      max_episode_number=int(meta["max_episodes"]), save_hist=False, debug=True, scenario_bank=bank,
+                      enable_random_episodes=bool(int(meta.get("random_episodes", 0))))
     env.max_number_steps = int(meta["max_steps"])
     ag = getattr(agents, agent)(env, 25, 5, 1, np.array([135]))
     env.set_agent_functions(ag.obs_space_format, ag.action_format, ag.calculate_reward, ag.get_obs_space(),
                             ag.get_action_space())
+    random_eps, n_perm = bool(int(meta.get("random_episodes", 0))), 0
+    if random_eps:  # the permutation the reference drew from its np_random (comm_env.py:435-442)
+        env._engine().set_episode_order(d["reset_order_0"][None])
+        n_perm = 1
     obs, info = env.reset(seed=int(meta["seed"]), options={"initial_episode": int(meta["initial_episode"])})
     assert info == {}
 
@@ -101,7 +107,14 @@ def test_env_api_replays_reference_trace(name, agent, n, bank):
         assert info == {}
         if done:
             ri += 1
-            obs, _ = env.reset()
+            if random_eps and int(d["reset_initial"][ri]) != -1:
+                env.eng.set_episode_order(d[f"reset_order_{n_perm}"][None])
+                n_perm += 1
+                obs, _ = env.reset(options={"initial_episode": int(d["reset_initial"][ri])})
+            else:
+                obs, _ = env.reset()
+            if random_eps:
+                assert env.episode_number == int(d["reset_episode"][ri]), ri
             check_obs(obs, d["reset_obs0"][ri], d["reset_mask0"][ri], d["reset_obs_i"][ri], d["reset_mask_i"][ri],
                       d["reset_order"][ri], f"reset {ri}")
     env.close()
