@@ -124,15 +124,6 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
     const int fl_mine = s_mine >= 0 ? __ldg(&sc->sl[s_mine].flags) : 0;
     const bool has_traffic = (fl_mine & IRS_F_REQ) != 0;
     const int lam_idx = has_traffic ? __ldg(&sc->sl[s_mine].lam_idx) : 0;
-    if (FULL_STEP && cfg.traffic_mode == 1 && wib == 0) {
-        // small batches: the Poisson table rows of the env's slices into L2 now (4 KB = 32 lines each, one line per
-        // lane) - the nine dependent probes of the table inversion then do not each wait on HBM when the caches are cold
-#pragma unroll
-        for (int sl_ = 0; sl_ < S; ++sl_)
-            if (__ldg(&sc->sl[sl_].flags) & IRS_F_REQ)
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char*>(
-                    st.cdf + (size_t)__ldg(&sc->sl[sl_].lam_idx) * IRS_POISSON_K) + 128 * lane));
-    }
     double sum_t = 0.0, sum_se = 0.0, traffic = 0.0, mu_l = 0.0;
     if (!native) {
         if (cfg.traffic_mode == 0) traffic = ue_lane ? A.traffic[eu] : 0.0;

@@ -23,14 +23,23 @@
 #define L8_ACTION_MINB 8
 #endif
 
-// UE indices of slice s (ascending, <= 5), 5 bits each; n = how many
+// UE indices of slice s (ascending, <= 5), 5 bits each; n = how many.  The 25 slice ids are compared four at a time
+// (per-byte SIMD compare), the matches gathered into a 25-bit mask and its lowest five bits listed.
 __device__ __forceinline__ uint32_t slice_ue_list(const uint32_t (&us)[8], int s, int& n)
 {
+    const uint32_t pat = (uint32_t)(s & 0xff) * 0x01010101u;
+    uint32_t bits = 0;
+#pragma unroll
+    for (int w = 0; w < 7; ++w) {
+        const uint32_t m = __vcmpeq4(us[w], pat) & 0x01010101u;       // byte b of the word = UE 4w + b
+        bits |= (((m * 0x00204081u) >> 21) & 0xfu) << (4 * w);        // one bit per byte, in order
+    }
+    bits &= 0x01ffffffu;
     uint32_t list = 0;
     n = 0;
 #pragma unroll
-    for (int u = 0; u < U; ++u)
-        if (ue_slice_of(us, u) == s && n < NS) { list |= (uint32_t)u << (5 * n); ++n; }
+    for (int i = 0; i < NS; ++i)
+        if (bits) { list |= (uint32_t)(__ffs(bits) - 1) << (5 * i); bits &= bits - 1; ++n; }
     return list;
 }
 __device__ __forceinline__ int group_sum8(int v)
@@ -70,9 +79,14 @@ __global__ void __launch_bounds__(L8_THREADS, L8_ACTION_MINB) k_action_8(const _
     const bool mine = g < S;
     const int s = mine ? g : 0;
     bool active[S];
+    int active_i[S];
     int nact = 0;
 #pragma unroll
-    for (int j = 0; j < S; ++j) { active[j] = (__ldg(&sc->sl[j].flags) & IRS_F_ACTIVE) != 0; nact += active[j]; }
+    for (int j = 0; j < S; ++j) {
+        active[j] = (__ldg(&sc->sl[j].flags) & IRS_F_ACTIVE) != 0;
+        active_i[j] = active[j];
+        nact += active[j];
+    }
     int n;
     const uint32_t list = slice_ue_list(us, mine ? g : -2, n);
 
@@ -147,17 +161,54 @@ __global__ void __launch_bounds__(L8_THREADS, L8_ACTION_MINB) k_action_8(const _
         }
     __syncwarp(); // the zeroes above are written by other lanes than the runs below
     int total = 0, expect = 0;
-    if (nact != 0) {
+    // scores -> RBGs (common.py:442-505 scores_to_rbs + round_int_equal_sum), one score per lane: the serial sums are
+    // evaluated by every lane in the reference's order, each of the two divisions per score by the score's own lane, the
+    // five results shared by width-8 shuffles.  Outside the nact branch: the four envs of a warp shuffle together.
+    int rbs_per_slice[S];
+    {
         double a0[S];
-        {
-            int srt[S];
+        int srt[S];
 #pragma unroll
-            for (int j = 0; j < S; ++j) srt[j] = st.sorted[(size_t)e * S + j];
+        for (int j = 0; j < S; ++j) srt[j] = st.sorted[(size_t)e * S + j];
 #pragma unroll
-            for (int j = 0; j < S; ++j) a0[j] = active[j] ? sel5(a0_in, srt[j]) : -1.0; // :247 (quirk Q3), :248-255
+        for (int j = 0; j < S; ++j) a0[j] = active[j] ? sel5(a0_in, srt[j]) : -1.0; // :247 (quirk Q3), :248-255
+        const int target = R / IRS_RBS_PER_RBG;
+        double res = 0.;
+#pragma unroll
+        for (int j = 0; j < S; ++j) res += a0[j] + 1;
+        const double sum = 0. + res;
+        double x_mine;
+        if (sum != 0) {
+            x_mine = ((double)target * (sel5(a0, s) + 1)) / sum;
+        } else {
+            double sa = 0.;
+#pragma unroll
+            for (int j = 0; j < S; ++j) sa += active[j] ? 1.0 : 0.0;
+            sa = 0. + sa;
+            x_mine = ((double)target / sa) * (sel5i(active_i, s) ? 1.0 : 0.0);
         }
-        int rbs_per_slice[S];
-        scores_to_rbs5(a0, R / IRS_RBS_PER_RBG, active, rbs_per_slice);
+        double xs[S];
+        double res2 = 0.;
+        int cnt = 0;
+#pragma unroll
+        for (int j = 0; j < S; ++j) {
+            xs[j] = __shfl_sync(FULL, x_mine, j, 8);
+            if (xs[j] != 0) { res2 += xs[j]; ++cnt; }
+        }
+        const double sum2 = 0. + res2;
+        int out_mine = (x_mine != 0) ? (int)floor(((double)target * x_mine) / sum2) : 0;
+        int tot = 0, rank = 0; // rank: descending value, ties -> higher index first (stable argsort reversed)
+#pragma unroll
+        for (int j = 0; j < S; ++j) {
+            tot += __shfl_sync(FULL, out_mine, j, 8);
+            if (xs[j] != 0 && (xs[j] > x_mine || (xs[j] == x_mine && j > s))) ++rank;
+        }
+        const int adj = target - tot;
+        if (x_mine != 0 && adj > rank) out_mine += (adj - rank - 1) / cnt + 1;
+#pragma unroll
+        for (int j = 0; j < S; ++j) rbs_per_slice[j] = __shfl_sync(FULL, out_mine, j, 8);
+    }
+    if (nact != 0) {
         int base = 0;
 #pragma unroll
         for (int j = 0; j < S; ++j)
