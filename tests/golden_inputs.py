@@ -205,13 +205,13 @@ def load_config2():
 
 
 class Config2Frames:
-    """SE / traffic frames of the config-2 fixture, regenerated env by env from the recipe (env e: seed 10 + e,
-    episode e mod 200; oracle/refharness/gen_config2.py) and verified against the stored checksums."""
+    """SE / traffic frames of a batch fixture, regenerated env by env from the recipe (env e: seed seed_base + e;
+    oracle/refharness/gen_config2.py, gen_batch_fixtures.py) and verified against the stored checksums."""
 
-    def __init__(self, d, envs):
+    def __init__(self, d, envs, seed_base=10, channel="mimic"):
         st, us = load_scenarios()
         self.d, self.envs = d, list(envs)
-        self.src = [FrameSource(10 + e, "mimic", st, us) for e in self.envs]
+        self.src = [FrameSource(seed_base + e, channel, st, us) for e in self.envs]
         self.k = 0
         self.n_reset = 0
 
@@ -283,3 +283,68 @@ def replay_config2(env, d, envs, n_steps=None, rtol=1e-5):
                     assert np.array_equal(buf[i, u, :dep], d["ckpt_buf"][e, ck, u, :dep]), f"buffer env {e} UE {u} step {k}"
             ck += 1
     return ck
+
+
+def load_batch(name):
+    f = np.load(os.path.join(GOLDEN, f"batch_{name}.npz"), allow_pickle=False)
+    d = {k: f[k] for k in f.files}
+    meta = {k[5:]: (v.item() if v.shape == () else v) for k, v in d.items() if k.startswith("meta_")}
+    return meta, d
+
+
+def replay_batch(env, meta, d, rtol=1e-5):
+    """Replay one of the 16-env fixtures of oracle/refharness/gen_batch_fixtures.py as ONE batch: injected frames, the
+    recorded actions, every episode end followed by a reset of the whole batch (the envs run in lockstep).  `env`:
+    reset(initial_episodes | None, se) / step(a0, intra, se, traffic) / buffers()."""
+    E, n, every = int(meta["n_envs"]), int(meta["n_steps"]), int(meta["obs_every"])
+    envs = list(range(E))
+    frames = Config2Frames(d, envs, seed_base=int(meta["seed_base"]), channel=str(meta["channel"]))
+    flat = np.isnan(d["reward"][0, 0, 1])
+
+    def close(tag, got, want, k):
+        np.testing.assert_allclose(np.asarray(got, np.float64), np.asarray(want, np.float64), rtol=rtol, atol=1e-30,
+                                   err_msg=f"batch {meta['agent']}: {tag} at step {k}")
+
+    def exact(tag, got, want, k):
+        assert np.array_equal(np.asarray(got).astype(np.int64), np.asarray(want).astype(np.int64)), \
+            f"batch {meta['agent']}: {tag} differs at step {k}"
+
+    def check_reset(out, ri, k):
+        close("reset obs0", out["obs0"], d["reset_obs0"][:, ri], k)
+        for key in ("mask0", "mask_i", "sorted_slices"):
+            exact("reset " + key, out[key], d["reset_" + key][:, ri], k)
+
+    ri = 0
+    out = env.reset(initial_episodes=d["reset_episode"][:, 0].astype(np.int32), se=frames.reset_frames())
+    check_reset(out, 0, -1)
+    ck = n_done = 0
+    for k in range(n):
+        se, tr = frames.step_frames()
+        out = env.step(d["a0"][:, k], np.maximum(d["intra"][:, k], 0), se, tr)
+        for key, gold in (("rb_start", "rb_start"), ("rb_count", "rb_count"), ("pkt_incoming", "pkt_incoming"),
+                          ("pkt_throughputs", "pkt_throughputs"), ("sent", "pkt_effective_thr"),
+                          ("dropped", "dropped_pkts"), ("mask0", "mask0"), ("mask_i", "mask_i"),
+                          ("sorted_slices", "sorted_slices"), ("done", "done")):
+            exact(key, out[key], d[gold][:, k], k)
+        close("reward", out["reward"][:, 0] if flat else out["reward"], d["reward"][:, k, 0] if flat else d["reward"][:, k], k)
+        if k % every == every - 1:
+            j = k // every
+            close("obs0", out["obs0"], d["obs0"][:, j], k)
+            if "obs_i" in d:
+                close("obs_i", out["obs_i"], d["obs_i"][:, j], k)
+            close("occ", out["occ"], d["buffer_occupancies"][:, j], k)
+            close("lat", out["lat"], d["buffer_latencies"][:, j], k)
+        if ck < d["ckpt_at_step"].shape[1] and d["ckpt_at_step"][0, ck] == k:
+            buf = np.asarray(env.buffers())
+            for e in range(E):
+                for u in range(U):
+                    dep = int(d["ckpt_depth"][e, ck, u])
+                    assert np.array_equal(buf[e, u, :dep], d["ckpt_buf"][e, ck, u, :dep]), f"buffer env {e} UE {u} step {k}"
+            ck += 1
+        if d["done"][0, k]:
+            assert d["done"][:, k].all()
+            n_done += 1
+            ri += 1
+            out = env.reset(initial_episodes=None, se=frames.reset_frames())
+            check_reset(out, ri, k)
+    return n_done

@@ -350,6 +350,33 @@ def test_config2_batch_fixture_from_the_reference(bank):
     assert bool(gpu.eng.v["out_done"].all())
 
 
+@pytest.mark.parametrize("name", ["mapf", "marr", "twc", "colran", "ibsched_fixed"])
+def test_batch_fixtures_from_the_reference(name, bank):
+    """16 envs x 300 steps (three 100-step episodes per env) of MAPF / MARR / SchedTWC / SchedColORAN / IBSched over
+    fixed_se recorded from the unmodified reference (oracle/refharness/gen_batch_fixtures.py), each replayed as ONE CUDA
+    batch with the recorded frames injected: integers bit-exact at every step, rewards every step, the agent's
+    observation every 4th step, buffers at the checkpoints, every rollover's reset observation."""
+    meta, d = golden_inputs.load_batch(name)
+    m = {"agent": str(meta["agent"])}
+    sort, fixed = trace_replay.agent_config(m)
+    gpu = CudaEnv(bank, int(meta["n_envs"]), channel_mode=0, traffic_mode=0, sort_slices=sort, fixed_intra=fixed,
+                  surface=trace_replay.agent_surface(m), max_steps=int(meta["max_steps"]))
+
+    class Env:
+        def reset(self, initial_episodes, se):
+            if initial_episodes is None:
+                return gpu.reset(initial_episode=-1, se=se)
+            return gpu.reset(initial_episodes=initial_episodes, initial_episode=0, se=se)
+
+        def step(self, a0, intra, se, tr):
+            return gpu.step(a0, intra, se, tr)
+
+        def buffers(self):
+            return gpu.buffers()
+
+    assert golden_inputs.replay_batch(Env(), meta, d) == 3
+
+
 def test_random_episodes_native_matches_oracle(bank):
     """enable_random_episodes with the built-in (Feistel) permutation: CUDA and oracle play the same shuffled cycles,
     per env, across wrap-arounds and a mid-run reset that draws a new permutation (comm_env.py:219-226, 434-444)."""
