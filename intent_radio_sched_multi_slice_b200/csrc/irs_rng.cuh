@@ -78,8 +78,8 @@ __device__ __align__(16) const uint32_t g_normal_tab[2 * IRS_NORMAL_TAB_N] = { I
 __device__ __forceinline__ float normal_from(uint32_t m, uint32_t signbit, const float2* __restrict__ tab)
 {
     const uint32_t bits = __float_as_uint((float)(int)(32768u - m)); // tail count t in [1, 32768], exact in binary32
-    const float2 c = tab[(bits >> 18) - (127u << 5)];                // octave * 32 + top 5 mantissa bits
-    const float g = __uint_as_float(((bits & 0x3FFFFu) << 5) | 0x3F800000u); // position inside the segment, [1, 2)
+    const float2 c = tab[(bits >> (23 - IRS_NORMAL_SUB_BITS)) - (127u << IRS_NORMAL_SUB_BITS)]; // octave, top mantissa bits
+    const float g = __uint_as_float(((bits & ((1u << (23 - IRS_NORMAL_SUB_BITS)) - 1u)) << IRS_NORMAL_SUB_BITS) | 0x3F800000u); // position inside the segment, [1, 2)
     return __uint_as_float(__float_as_uint(__fmaf_rn(c.y, g, c.x)) ^ signbit);
 }
 // half-word k (0 = low) of word w

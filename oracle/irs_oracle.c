@@ -160,9 +160,9 @@ static float normal16(uint32_t h)
 {
     uint32_t m = h & 0x7FFFu, signbit = (h & 0x8000u) << 16;
     uint32_t bits = float_to_bits((float)(int)(32768u - m));
-    uint32_t idx = (bits >> 18) - (127u << 5);
+    uint32_t idx = (bits >> (23 - IRS_NORMAL_SUB_BITS)) - (127u << IRS_NORMAL_SUB_BITS);
     float c0 = bits_to_float(normal_tab[2 * idx]), c1 = bits_to_float(normal_tab[2 * idx + 1]);
-    float g = bits_to_float(((bits & 0x3FFFFu) << 5) | 0x3F800000u);
+    float g = bits_to_float(((bits & ((1u << (23 - IRS_NORMAL_SUB_BITS)) - 1u)) << IRS_NORMAL_SUB_BITS) | 0x3F800000u);
     return bits_to_float(float_to_bits(fmaf(c1, g, c0)) ^ signbit);
 }
 static float normal_half(const uint32_t w[4], int k) { return normal16((w[k >> 1] >> (16 * (k & 1))) & 0xFFFFu); }
