@@ -136,8 +136,8 @@ __device__ __forceinline__ void action_to_rb_core(const StepArgs& A, int e, cons
             double sm = __shfl_sync(FULL, snt_mean, src);
             if (!smask[s]) { om = 0.0 / 0.0; sm = 0.0 / 0.0; } // np.mean of an empty selection
             const double bsz = __ldg(&sc->sl[s].buffer_size), msg = __ldg(&sc->sl[s].message_size);
-            occ_mbps[s] = active[s] ? ((om * bsz) * msg) / 1e6 : 0.0;
-            sent_mbps[s] = active[s] ? (sm * msg) / 1e6 : 0.0;
+            occ_mbps[s] = active[s] ? DIVC((om * bsz) * msg, 1e6) : 0.0;
+            sent_mbps[s] = active[s] ? DIVC(sm * msg, 1e6) : 0.0;
             mx = (s == 0 || occ_mbps[s] > mx) ? occ_mbps[s] : mx;
         }
         double res = 0.;
@@ -199,7 +199,7 @@ __device__ __forceinline__ void action_to_rb_core(const StepArgs& A, int e, cons
         const int rr_buf = rr_share(elmask, rbs_s);
         const int rr_all = rr_share(gmask, rbs_s); // fallback: account_buffer=False
         // throughput each UE could use - common.py:567-583, 648-664
-        const double ta_a = (sebar * (((double)rbs_s * cfg.bandwidth) / (double)R)) / (double)n;
+        const double ta_a = (sebar * DIVC((double)rbs_s * cfg.bandwidth, R)) / (double)n;
         const double ta_b = (occ * (double)up.max_pkts) * up.pkt_bits;
         const double ta = ta_a < ta_b ? ta_a : ta_b;
         const double tamax = group_max(ta, gmask);

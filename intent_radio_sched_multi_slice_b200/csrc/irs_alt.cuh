@@ -61,8 +61,8 @@ __global__ void __launch_bounds__(ENV_WARPS * 32) k_surface_alt(const __grid_con
             ++n;
             sum_se += f.sebar;
             sum_thr += thr;
-            sum_thr_mbps += (thr * pkt) / 1e6;                               // pkts_to_mbps, sched_twc.py:430-431
-            sum_eff += ((double)((long long)f.sent * (long long)pkt)) / 1e6;
+            sum_thr_mbps += DIVC(thr * pkt, 1e6);                               // pkts_to_mbps, sched_twc.py:430-431
+            sum_eff += DIVC((double)((long long)f.sent * (long long)pkt), 1e6);
             sum_occ += f.occ;
             sum_lat += f.lat;
             const double dw = (double)(f.sum_drop * A.win_mul), tw = (double)(f.sum_sent * A.win_mul);

@@ -135,7 +135,7 @@ __device__ __noinline__ void reset_env_warp(const StepArgs& A, int e, int initia
         if (A.raw.se_used)
             for (int r = lane; r < R; r += 32) A.raw.se_used[((size_t)e * U + u) * R + r] = se_row[r];
         const double sum = __shfl_sync(FULL, np_sum135_pair(se_row, se_row), 0);
-        if (lane == u) sebar = sum / (double)R;
+        if (lane == u) sebar = DIVC(sum, R);
         __syncwarp();
     }
     // push the all-zero metrics frame (comm_env.py:474-478)
@@ -259,7 +259,7 @@ __device__ __forceinline__ void env_tail_core(const StepArgs& A, int e, const ir
         const bool vi = __shfl_sync(FULL, (int)viol, sl);
         const double mn = __shfl_sync(FULL, vmn, sl);
         if (!act_s) continue;
-        a9 += ((double)snt * msg) / 1e6;
+        a9 += DIVC((double)snt * msg, 1e6);
         if (vi) {
             add10 += 1; a12 += mn;
             if (pr != 0) { add11 += 1; a13 += mn; }

@@ -350,7 +350,7 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
     // ---- phase 3: throughput, arrivals, closed-form buffer arithmetic - one UE per lane -------
     const double thr = floor(sum_t / up.pkt_bits);   // ues.py:108-116
     const double inc = floor(traffic / up.pkt_bits); // ues.py:199
-    const double sebar = sum_se / (double)R;         // np.mean(SE[0,u,:])
+    const double sebar = DIVC(sum_se, R);         // np.mean(SE[0,u,:])
     const int thr_i = (int)fmin(fmax(thr, 0.0), 2147483647.0);
     const int total = tot_prev - expired;            // occupancy after the age shift (buffer.py:60-62)
     int dropped = expired, kept;

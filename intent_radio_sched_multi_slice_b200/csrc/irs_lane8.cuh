@@ -112,8 +112,8 @@ __global__ void __launch_bounds__(L8_THREADS, L8_ACTION_MINB) k_action_8(const _
         }
         const double om = (0. + so) / (double)n, sm = (0. + ss) / (double)n; // n == 0: 0/0 = nan like np.mean([])
         const double bsz = __ldg(&sc->sl[s].buffer_size), msg = __ldg(&sc->sl[s].message_size);
-        const double occ_m = active[s] ? ((om * bsz) * msg) / 1e6 : 0.0;
-        const double sent_m = active[s] ? (sm * msg) / 1e6 : 0.0;
+        const double occ_m = active[s] ? DIVC((om * bsz) * msg, 1e6) : 0.0;
+        const double sent_m = active[s] ? DIVC(sm * msg, 1e6) : 0.0;
         double occ_mbps[S], sent_mbps[S], w[S];
         double mx = 0;
 #pragma unroll
@@ -246,7 +246,7 @@ __global__ void __launch_bounds__(L8_THREADS, L8_ACTION_MINB) k_action_8(const _
                     if (i < n) {
                         const int u = (list >> (5 * i)) & 31;
                         const double sebar = st.ue_d[(eu0 + u) * UD_N + UD_SEBAR];
-                        const double ta_a = (sebar * (((double)rbs_s * cfg.bandwidth) / (double)R)) / (double)n;
+                        const double ta_a = (sebar * DIVC((double)rbs_s * cfg.bandwidth, R)) / (double)n;
                         const double ta_b = (occ[i] * max_pkts) * pkt_bits;
                         ta[i] = ta_a < ta_b ? ta_a : ta_b;
                         tamax = (i == 0 || ta[i] > tamax) ? ta[i] : tamax;
@@ -377,7 +377,7 @@ __global__ void __launch_bounds__(L8_THREADS, L8_TAIL_MINB) k_env_tail_8(const _
         snt += f.sent;
         if (live) { // per-UE tail of player_{s+1}'s observation (ib_sched.py:186-200)
             pi[9 + j] = f.occ;
-            pi[14 + j] = sebar / 40.0;
+            pi[14 + j] = DIVC(sebar, 40.0);
         }
     }
     double dsl[3], act[3];
@@ -418,10 +418,10 @@ __global__ void __launch_bounds__(L8_THREADS, L8_TAIL_MINB) k_env_tail_8(const _
         double* p0 = st.out_obs0 + (size_t)e * IRS_OBS0 + pos * 10; // :160-173
         p0[0] = dsl[0]; p0[1] = dsl[1]; p0[2] = dsl[2];
         p0[3] = act[0]; p0[4] = act[1]; p0[5] = act[2];
-        p0[6] = prio; p0[7] = traffic / 120.0; p0[8] = (double)n / 5.0; p0[9] = se_slice / 40.0;
+        p0[6] = prio; p0[7] = DIVC(traffic, 120.0); p0[8] = DIVC((double)n, 5.0); p0[9] = DIVC(se_slice, 40.0);
         pi[0] = dsl[0]; pi[1] = dsl[1]; pi[2] = dsl[2]; // :186-200
         pi[3] = act[0]; pi[4] = act[1]; pi[5] = act[2];
-        pi[6] = (double)rbs_alloc / (double)R; pi[7] = traffic / 120.0; pi[8] = (double)n / 5.0;
+        pi[6] = DIVC((double)rbs_alloc, R); pi[7] = DIVC(traffic, 120.0); pi[8] = DIVC((double)n, 5.0);
         st.out_mask0[(size_t)e * S + s] = is_active ? 1 : 0; // :76-81 (unsorted order)
 #pragma unroll
         for (int j = 0; j < NS; ++j) st.out_maski[((size_t)e * S + s) * NS + j] = j < n ? 1 : 0;
@@ -470,7 +470,7 @@ __global__ void __launch_bounds__(L8_THREADS, L8_TAIL_MINB) k_env_tail_8(const _
 
     // ---- episode metrics (metrics.py:62-71 as running sums; results/gen_results.py:791-809, 874-1022): lane 0 walks
     //      the slices in sorted order, like the observation vector -----------------------------------------------
-    const double mbit = ((double)snt * msg) / 1e6;
+    const double mbit = DIVC((double)snt * msg, 1e6);
     const bool act_s = mine && (fl & IRS_F_ACTIVE);
     double* acc = st.acc + (size_t)e * IRS_NUM_METRICS;
     double a9 = acc[9], a12 = acc[12], a13 = acc[13], add10 = 0, add11 = 0;

@@ -36,7 +36,7 @@ struct SliceView { // valid on lanes 0..4 (slice = lane)
 // two thirds of the per-UE cost of the tail kernels).  Same operands, same operation: bit-identical results.
 // reliability target t = (100 - v) / 100 of a slice (common.py:188-233): a per-slice constant that a caller looping over
 // UEs computes once per slice
-__device__ __forceinline__ double rel_target(const irs_slice* sl) { return (100 - __ldg(&sl->rel_value)) / 100; }
+__device__ __forceinline__ double rel_target(const irs_slice* sl) { return DIVC(100 - __ldg(&sl->rel_value), 100); }
 __device__ __forceinline__ void intent_drift_ue(const irs_slice* sl, int flags, const UeFrame& f, int win_len, int mul,
                                                 double (&drift)[3], const double* rel_t = nullptr)
 {
@@ -44,7 +44,7 @@ __device__ __forceinline__ void intent_drift_ue(const irs_slice* sl, int flags, 
     drift[0] = drift[1] = drift[2] = 0;
     if (flags & IRS_F_THR) {
         const double v = __ldg(&sl->thr_value);
-        double m = (double)((long long)f.sent * (long long)__ldg(&sl->message_size)) / 1e6; // :26-31
+        double m = DIVC((double)((long long)f.sent * (long long)__ldg(&sl->message_size)), 1e6); // :26-31
         bool zero = isclose0(f.occ);                                                        // :104-107
         if (win_len * mul > 1) zero = zero || (mul == 2 ? isclose0(f.occ) : f.occ1z);          // :108-116
         if (zero) m = v * (1.1 + r);                                                        // :117-119
@@ -59,7 +59,7 @@ __device__ __forceinline__ void intent_drift_ue(const irs_slice* sl, int flags, 
         const double t = rel_t ? *rel_t : rel_target(sl);
         const bool ok = 100 * (1 - m) >= v;                        // :124-126
         double den2 = t * r;
-        if (!ok) den2 = v / 100;                                   // violated (rare): the other denominator
+        if (!ok) den2 = DIVC(v, 100);                                   // violated (rare): the other denominator
         const double q = (ok ? t - m : m - t) / den2; // :188-220 (t - m) / (t r) | :223-233 (m - t) / (v / 100)
         drift[1] = ok ? (m < t * (1 - r) ? 1.0 : 0.0 + q) : 0.0 - q;
     }
@@ -157,11 +157,11 @@ __device__ __noinline__ SliceView format_obs_warp(const StepArgs& A, int e, cons
         double* p0 = st.out_obs0 + (size_t)e * IRS_OBS0 + pos * 10; // :160-173
         p0[0] = v.dsl[0]; p0[1] = v.dsl[1]; p0[2] = v.dsl[2];
         p0[3] = v.act[0]; p0[4] = v.act[1]; p0[5] = v.act[2];
-        p0[6] = v.prio; p0[7] = traffic / 120.0; p0[8] = (double)v.n / 5.0; p0[9] = se_slice / 40.0;
+        p0[6] = v.prio; p0[7] = DIVC(traffic, 120.0); p0[8] = DIVC((double)v.n, 5.0); p0[9] = DIVC(se_slice, 40.0);
         double* pi = st.out_obsi + ((size_t)e * S + lane) * IRS_OBSI; // :186-200
         pi[0] = v.dsl[0]; pi[1] = v.dsl[1]; pi[2] = v.dsl[2];
         pi[3] = v.act[0]; pi[4] = v.act[1]; pi[5] = v.act[2];
-        pi[6] = (double)rbs_alloc / (double)R; pi[7] = traffic / 120.0; pi[8] = (double)v.n / 5.0;
+        pi[6] = DIVC((double)rbs_alloc, R); pi[7] = DIVC(traffic, 120.0); pi[8] = DIVC((double)v.n, 5.0);
         for (int j = v.n; j < NS; ++j) { pi[9 + j] = 0; pi[14 + j] = 0; }
         st.out_mask0[(size_t)e * S + lane] = v.active ? 1 : 0; // :76-81 (unsorted order)
         for (int j = 0; j < NS; ++j) st.out_maski[((size_t)e * S + lane) * NS + j] = j < v.n ? 1 : 0;
@@ -171,7 +171,7 @@ __device__ __noinline__ SliceView format_obs_warp(const StepArgs& A, int e, cons
         const int j = __popc(gmask & ((1u << lane) - 1u));
         double* pi = st.out_obsi + ((size_t)e * S + s_mine) * IRS_OBSI;
         pi[9 + j] = f.occ;
-        pi[14 + j] = f.sebar / 40.0;
+        pi[14 + j] = DIVC(f.sebar, 40.0);
     }
     return v;
 }

@@ -101,8 +101,8 @@ __global__ void __launch_bounds__(SERIAL_THREADS) k_action_t(const __grid_consta
             }
             double om = (0. + so) / (double)n, sm = (0. + ss) / (double)n; // n == 0: 0/0 = nan like np.mean([])
             const double bsz = __ldg(&sc->sl[s].buffer_size), msg = __ldg(&sc->sl[s].message_size);
-            occ_mbps[s] = active[s] ? ((om * bsz) * msg) / 1e6 : 0.0;
-            sent_mbps[s] = active[s] ? (sm * msg) / 1e6 : 0.0;
+            occ_mbps[s] = active[s] ? DIVC((om * bsz) * msg, 1e6) : 0.0;
+            sent_mbps[s] = active[s] ? DIVC(sm * msg, 1e6) : 0.0;
             mx = (s == 0 || occ_mbps[s] > mx) ? occ_mbps[s] : mx;
         }
         double res = 0.;
@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(SERIAL_THREADS) k_action_t(const __grid_consta
                     ta[i] = 0;
                     if (i < n) {
                         const double sebar = st.ue_d[(eu0 + g.u[i]) * UD_N + UD_SEBAR];
-                        const double ta_a = (sebar * (((double)rbs_s * cfg.bandwidth) / (double)R)) / (double)n;
+                        const double ta_a = (sebar * DIVC((double)rbs_s * cfg.bandwidth, R)) / (double)n;
                         const double ta_b = (occ[i] * max_pkts) * pkt_bits;
                         ta[i] = ta_a < ta_b ? ta_a : ta_b;
                         tamax = (i == 0 || ta[i] > tamax) ? ta[i] : tamax;
@@ -339,7 +339,7 @@ __global__ void __launch_bounds__(SERIAL_THREADS, TAIL_T_MINB) k_env_tail_t(cons
         if (j < NS) { // per-UE tail of player_{s+1}'s observation (ib_sched.py:186-200)
             double* pi = st.out_obsi + ((size_t)e * S + s) * IRS_OBSI;
             pi[9 + j] = f.occ;
-            pi[14 + j] = sebar / 40.0;
+            pi[14 + j] = DIVC(sebar, 40.0);
         }
     }
     double dsl[S][3], act[S][3], se_slice[S], prio[S], traffic[S], msg[S];
@@ -397,11 +397,11 @@ __global__ void __launch_bounds__(SERIAL_THREADS, TAIL_T_MINB) k_env_tail_t(cons
         double* p0 = st.out_obs0 + (size_t)e * IRS_OBS0 + pos[s] * 10; // :160-173
         p0[0] = dsl[s][0]; p0[1] = dsl[s][1]; p0[2] = dsl[s][2];
         p0[3] = act[s][0]; p0[4] = act[s][1]; p0[5] = act[s][2];
-        p0[6] = prio[s]; p0[7] = traffic[s] / 120.0; p0[8] = (double)n_s[s] / 5.0; p0[9] = se_slice[s] / 40.0;
+        p0[6] = prio[s]; p0[7] = DIVC(traffic[s], 120.0); p0[8] = DIVC((double)n_s[s], 5.0); p0[9] = DIVC(se_slice[s], 40.0);
         double* pi = st.out_obsi + ((size_t)e * S + s) * IRS_OBSI; // :186-200
         pi[0] = dsl[s][0]; pi[1] = dsl[s][1]; pi[2] = dsl[s][2];
         pi[3] = act[s][0]; pi[4] = act[s][1]; pi[5] = act[s][2];
-        pi[6] = (double)rbs_alloc[s] / (double)R; pi[7] = traffic[s] / 120.0; pi[8] = (double)n_s[s] / 5.0;
+        pi[6] = DIVC((double)rbs_alloc[s], R); pi[7] = DIVC(traffic[s], 120.0); pi[8] = DIVC((double)n_s[s], 5.0);
         st.out_mask0[(size_t)e * S + s] = active ? 1 : 0; // :76-81 (unsorted order)
 #pragma unroll
         for (int j = 0; j < NS; ++j) st.out_maski[((size_t)e * S + s) * NS + j] = j < n_s[s] ? 1 : 0;
@@ -457,7 +457,7 @@ __global__ void __launch_bounds__(SERIAL_THREADS, TAIL_T_MINB) k_env_tail_t(cons
 #pragma unroll
         for (int s = 0; s < S; ++s) {
             if (pos[s] != p || !(flags[s] & IRS_F_ACTIVE)) continue;
-            a9 += ((double)snt[s] * msg[s]) / 1e6;
+            a9 += DIVC((double)snt[s] * msg[s], 1e6);
             if (viol[s]) {
                 add10 += 1; a12 += vmn[s];
                 if (__ldg(&sc->sl[s].priority) != 0) { add11 += 1; a13 += vmn[s]; }
