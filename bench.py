@@ -481,6 +481,9 @@ def run_b200(args):
               "mask0": pin(E, 5, dt=torch.int8), "maski": pin(E, 5, 5, dt=torch.int8),
               "reward": pin(E, 6, dt=torch.float64), "done": pin(E, dt=torch.uint8)}
         surf = capi.HostSurface(*[hs[n].data_ptr() for n in capi.SURFACE_FIELDS])
+        if os.environ.get("IRS_BENCH_SURF"):  # experiment: only the first k surface arrays (per-copy overhead of the chunked D2H)
+            keep = int(os.environ["IRS_BENCH_SURF"])
+            surf = capi.HostSurface(*[hs[n].data_ptr() if i < keep else None for i, n in enumerate(capi.SURFACE_FIELDS)])
         h2d = sum(a.numel() * a.element_size() + b.numel() * b.element_size() for a, b in h_pool[:1])
         d2h = sum(t.numel() * t.element_size() for t in hs.values())
         def time_host(surface, bytes_out):
