@@ -205,7 +205,7 @@ class BatchEngine:
 
     def _step_graph(self, a0, intra):
         """One step as a replay of the captured graph (native generators / device channel only: nothing is injected)."""
-        key = (a0 is not None, intra is not None, self._raw_struct is not None)
+        key = (a0 is not None, intra is not None, id(self._raw_struct))  # the capture holds the raw-output pointers
         if a0 is not None:
             self.v["in_a0"].copy_(a0 if isinstance(a0, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(a0, np.float64)),
                                   non_blocking=True)

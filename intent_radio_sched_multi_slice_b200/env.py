@@ -122,6 +122,9 @@ class BatchedMARLCommEnv:
                 raise ValueError("set_agent_functions needs three callables (comm_env.py:484-512)")
             self._callbacks = (obs_space_format, action_format, calculate_reward)
             self._surface = agents_mod.IBSched  # still written by the tail kernel; not returned on this path
+            # the callbacks see the raw frame of the step that just ran, so a finished env must not be rolled over
+            # inside that step (its SE frame would already be the next episode's): reset with reset(mask=done)
+            self.auto_reset = False
             self.observation_space, self.action_space = obs_space, action_space
         if self.eng is not None:
             self.eng.close()
