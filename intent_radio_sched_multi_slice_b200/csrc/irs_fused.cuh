@@ -1,16 +1,16 @@
 // irs_fused.cuh - k_ue_env: the per-UE middle of CommunicationEnv.step (channel, traffic, throughput,
-// buffers, per-UE window push; comm_env.py:302-326, ues.py:149-243) of one env in ONE warp, between k_action
-// and k_env_tail.
+// buffers, per-UE window push; comm_env.py:302-326, ues.py:149-243) of one env in ONE warp, between the
+// action and the tail kernels; and k_env_step: the whole step of a small batch in one launch.
 //
 // Lane u = UE u for everything that is per-UE scalar work (closed-form buffer arithmetic, ring-row
-// update, window push).  The one warp-wide stage is the generators: (UE, Philox quad) tasks of up to 4
-// associated UEs are packed over the 32 lanes - pair passes (lanes 0..15 one UE, lanes 16..31 another;
-// a lane adds up the 8 elements of one accumulator of NumPy's pairwise sum in registers) + 1 auxiliary
-// pass that serves all 4 UEs at once (6 lanes per UE: 4 half-quads for RBs 128..134, the per-episode
-// mean, the Poisson arrival).  Unassociated UEs are skipped entirely.  Buffer rows are rings
-// (irs_ue.cuh): a UE lane loads the expiring slot and its 4 oldest slots in the prologue, before the
-// generators run, and resolves the step's drain on them after the closed form; only a drain that
-// reaches further, or a window of more than 4 slots that empties, is handed to the whole warp.
+// update, window push, and - native generators - the per-episode mean, the serial tail of the SE row and
+// the Poisson arrival).  The warp-wide stage is the 128 leading SE values of every associated UE: pair
+// passes (lanes 0..15 one UE, lanes 16..31 another; a lane draws one Philox quad = eight table normals =
+// the 8 elements of one accumulator of NumPy's pairwise sum, and adds them up in registers).
+// Unassociated UEs are skipped entirely.  Buffer rows are rings (irs_ue.cuh): a UE lane loads the expiring
+// slot and its 4 oldest slots in the prologue, before the generators run, and resolves the step's drain on
+// them after the closed form; only a drain that reaches further, or a window of more than 4 slots that
+// empties, is handed to the whole warp.
 #pragma once
 #include "irs_action.cuh"
 #include "irs_env.cuh"
@@ -48,11 +48,11 @@ __device__ __forceinline__ T sel4(const T (&a)[GRP], int j)
 
 // FULL_STEP = false: the per-UE middle of the step, between k_action and k_env_tail (large batches: every warp of the
 //                    GPU runs the same small code region).
-// FULL_STEP = true : the whole step of ONE env in ONE block of four warps and one launch - for SMALL batches
+// FULL_STEP = true : the whole step of ONE env in ONE block of NW warps and one launch - for SMALL batches
 //                    (BASELINE config 2: 1,024 envs), where the step is bound by launch and dependency latency.
 //                    Warp 0 turns the action into RB runs (lane = UE) and hands them over through shared memory; the
-//                    four warps share the env's UEs (u mod 4) for the middle; the per-UE frames go back through shared
-//                    memory and warp 0 finishes with observation / reward / rollover.
+//                    block's warps share the env's UEs (u mod NW) for the middle; the per-UE frames go back through
+//                    shared memory and warp 0 finishes with observation / reward / rollover.
 struct StepXchg { // hand-over between the warps of a k_env_step block
     short2 rb[32];
     double occ[32], lat[32], sebar[32];
