@@ -46,9 +46,6 @@ struct irs_env {
     int per_env;                   // IRS_PER_ENV: how the per-env stages of a launch above fused_max run - 0 / "lane8": eight
                                    // lanes per env (measured fastest from 2,368 to 65,536 envs per launch), "warp": one warp
                                    // per env, "thread": one thread per env
-    int serial_min;                // IRS_SERIAL_MIN_ENVS (default 49,152): launches covering at least this many envs
-                                   // use the thread-per-env action / tail kernels (irs_serial.cuh); below that one
-                                   // thread per env leaves the SMs too empty to hide its serial latency
     const double* se_bank;         // channel_mode 3 (irs_set_se_trace)
     int32_t bank_eps, bank_steps, bank_first, bank_wrap;
     const int32_t* ep_order;       // random_episodes with a given order (irs_set_episode_order)
@@ -178,8 +175,6 @@ int irs_create(const irs_config* cfg, int32_t n_lambda, irs_env** out)
     env->fused_max = fm_ ? atoi(fm_) : 2368;
     const char* pe_ = getenv("IRS_PER_ENV");
     env->per_env = !pe_ ? 0 : (!strcmp(pe_, "warp") ? 1 : (!strcmp(pe_, "lane8") ? 2 : (!strcmp(pe_, "thread") ? 3 : 0)));
-    const char* sm_ = getenv("IRS_SERIAL_MIN_ENVS");
-    env->serial_min = sm_ ? atoi(sm_) : 49152;
     compute_layout(env->cfg, n_lambda, &env->lay);
     *out = env;
     return IRS_OK;

@@ -5,8 +5,10 @@
 // With tens of thousands of envs there is enough parallelism to give every env its own THREAD:
 // the code becomes the plain serial algorithm (NumPy's serial sums are just loops), a warp
 // advances 32 envs at once, and the issue slots per env drop by ~10x.  Same reference symbols,
-// same arithmetic order, same state layout as irs_action.cuh; selected by the launcher when the
-// launch covers >= IRS_SERIAL_MIN_ENVS envs (env var, default 49,152).
+// same arithmetic order, same state layout as irs_action.cuh.  Round 1's default for launches of
+// >= 49,152 envs; since round 2 the eight-lanes-per-env kernels (irs_lane8.cuh) are faster at every
+// size (0.078 + 0.101 ms against 0.099 + 0.192 at 65,536 envs) and these are selected with
+// IRS_PER_ENV=thread (every parity test runs them too).
 #pragma once
 #include "irs_action.cuh"
 
