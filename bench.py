@@ -50,6 +50,7 @@ def parse():
     p.add_argument("--d2h-probe", action="store_true",
                    help="no kernels: every rank copies one step's float64 surface (81.2 MB at 65,536 envs) device->pinned "
                         "host in a loop; prints the aggregate GB/s, the ceiling of the e2e figure at N GPUs")
+    p.add_argument("--no-graph", action="store_true", help="small batches: eager launches instead of the graph replay (profiling)")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
     a = p.parse_args()
@@ -314,7 +315,7 @@ def run_b200(args):
     E, K, Wm = args.envs, args.steps, max(args.warmup, 3)
     bank, wl = make_bank(args.depth)
     # small batches are launch-bound: the engine replays one captured graph per step (BatchEngine(graph=True))
-    eng = BatchEngine(bank, E, device=dev, depth_cap=max(bank.max_depth(), 101), graph=E <= 4096, **engine_kwargs(args, rank))
+    eng = BatchEngine(bank, E, device=dev, depth_cap=max(bank.max_depth(), 101), graph=E <= 4096 and not args.no_graph, **engine_kwargs(args, rank))
     gid = torch.arange(E, device=dev, dtype=torch.int32) + rank * E
     trace_bytes = 0
     if args.workload == "trace":

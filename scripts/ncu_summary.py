@@ -35,3 +35,6 @@ print("== warp instructions (all profiled launches):", tot)
 for f in byfile: print(f"  {f}: {100*byfile[f]/tot:.1f}% inst, {100*sf[f]/ts:.1f}% stall samples")
 for k, v in agg.most_common(topn):
     print(f"  {k[0][:16]:16s} {k[1]:4d} {100*v/tot:5.1f}% inst {100*stall[k]/ts:5.1f}% stall | {text[k]}")
+print("== source lines by stall samples")
+for k, v in stall.most_common(topn):
+    print(f"  {k[0][:16]:16s} {k[1]:4d} {100*agg[k]/tot:5.1f}% inst {100*v/ts:5.1f}% stall | {text[k]}")
