@@ -10,7 +10,8 @@
 #include "irs_common.cuh"
 #include "irs_rng.cuh"
 
-// agents/common.py:481-505 on 5 values held by every lane (uniform, fully unrolled).
+// agents/common.py:481-505 on 5 values held by one thread (fully unrolled): the per-slice rounding of the thread- and
+// lane8-per-env stages.
 __device__ __forceinline__ void round_int_equal_sum5(const double (&x)[S], int target, int (&out)[S])
 {
     double res = 0.;
@@ -37,7 +38,7 @@ __device__ __forceinline__ void round_int_equal_sum5(const double (&x)[S], int t
     }
 }
 
-// agents/common.py:442-461
+// agents/common.py:442-461 by one thread (the thread-per-env stage)
 __device__ __forceinline__ void scores_to_rbs5(const double (&action)[S], int total, const bool (&active)[S],
                                                int (&out)[S])
 {
@@ -58,6 +59,56 @@ __device__ __forceinline__ void scores_to_rbs5(const double (&action)[S], int to
         for (int i = 0; i < S; ++i) x[i] = ((double)total / sa) * (active[i] ? 1.0 : 0.0);
     }
     round_int_equal_sum5(x, total, out);
+}
+
+// agents/common.py:442-461 scores_to_rbs + :481-505 round_int_equal_sum on the five scores every lane holds.  The serial
+// sums are evaluated by every lane in the reference's order; each of the two float64 divisions per score runs on the
+// score's own lane (lane s = slice s, lanes >= 5 shadow slice 0) and the five results are shared by shuffles: two
+// dependent divisions on the warp's critical path instead of ten.
+__device__ __forceinline__ void scores_to_rbs5_lanes(const double (&action)[S], int total, const bool (&active)[S],
+                                                     int (&out)[S])
+{
+    const int lane = lane_id();
+    const int s = lane < S ? lane : 0;
+    double a1_mine = 0, act_mine = 0;
+    double res = 0.;
+#pragma unroll
+    for (int i = 0; i < S; ++i) {
+        const double a1 = action[i] + 1;
+        res += a1;
+        if (i == s) { a1_mine = a1; act_mine = active[i] ? 1.0 : 0.0; }
+    }
+    const double sum = 0. + res;
+    double x_mine;
+    if (sum != 0) {
+        x_mine = ((double)total * a1_mine) / sum;
+    } else {
+        double sa = 0.;
+#pragma unroll
+        for (int i = 0; i < S; ++i) sa += active[i] ? 1.0 : 0.0;
+        sa = 0. + sa;
+        x_mine = ((double)total / sa) * act_mine;
+    }
+    double x[S];
+    double res2 = 0.;
+    int cnt = 0;
+#pragma unroll
+    for (int i = 0; i < S; ++i) {
+        x[i] = __shfl_sync(FULL, x_mine, i);
+        if (x[i] != 0) { res2 += x[i]; ++cnt; }
+    }
+    const double sum2 = 0. + res2;
+    int out_mine = (x_mine != 0) ? (int)floor(((double)total * x_mine) / sum2) : 0;
+    int tot = 0, rank = 0; // rank: descending value, ties -> higher index first (stable argsort reversed)
+#pragma unroll
+    for (int i = 0; i < S; ++i) {
+        tot += __shfl_sync(FULL, out_mine, i);
+        if (x[i] != 0 && (x[i] > x_mine || (x[i] == x_mine && i > s))) ++rank;
+    }
+    const int adj = total - tot;
+    if (x_mine != 0 && adj > rank) out_mine += (adj - rank - 1) / cnt + 1;
+#pragma unroll
+    for (int i = 0; i < S; ++i) out[i] = __shfl_sync(FULL, out_mine, i);
 }
 
 // agents/common.py:508-555: share of this lane when `rbs_s` RBs go round-robin to `elmask`.
@@ -96,6 +147,7 @@ __device__ __forceinline__ void action_to_rb_core(const StepArgs& A, int e, cons
     const DevState& st = A.st;
     const irs_config& cfg = A.cfg;
     const int lane = lane_id();
+    PHASE_STAMP(2, 0);
     const int s_mine = lane < U ? (int)sc->ue_slice[lane] : -1;
     uint32_t smask[S], gmask = 0;
 #pragma unroll
@@ -103,6 +155,7 @@ __device__ __forceinline__ void action_to_rb_core(const StepArgs& A, int e, cons
         smask[s] = __ballot_sync(FULL, s_mine == s);
         if (s_mine == s) gmask = smask[s];
     }
+    const GroupIdx G = group_index(gmask);
     bool active[S];
     int nact = 0;
 #pragma unroll
@@ -124,9 +177,9 @@ __device__ __forceinline__ void action_to_rb_core(const StepArgs& A, int e, cons
 #pragma unroll
         for (int s = 0; s < S; ++s) a0_in[s] = __ldg(&sc->sl[s].n_ues) > 0 ? 1.0 : -1.0;
     } else if (cfg.policy == 2) { // agents/mapf.py:41-111
-        const int n = __popc(gmask);
-        const double occ_mean = group_sum_ordered(occ, gmask) / (double)n;
-        const double snt_mean = group_sum_ordered((double)sum_sent / (double)win_len, gmask) / (double)n;
+        const int n = G.n;
+        const double occ_mean = group_sum_ordered(occ, G) / (double)n;
+        const double snt_mean = group_sum_ordered((double)sum_sent / (double)win_len, G) / (double)n;
         double occ_mbps[S], sent_mbps[S], w[S];
         double mx = 0;
 #pragma unroll
@@ -171,6 +224,7 @@ __device__ __forceinline__ void action_to_rb_core(const StepArgs& A, int e, cons
 
     // ---- ib_sched.py:223-349 -----------------------------------------------------------
     int count = 0, start = 0;
+    PHASE_STAMP(2, 1);
     if (nact != 0) { // warp-uniform
         double a0[S];
 #pragma unroll
@@ -179,7 +233,8 @@ __device__ __forceinline__ void action_to_rb_core(const StepArgs& A, int e, cons
             a0[s] = active[s] ? sel5(a0_in, src) : -1.0; // :247 (quirk Q3), :248-255
         }
         int rbs_per_slice[S];
-        scores_to_rbs5(a0, R / IRS_RBS_PER_RBG, active, rbs_per_slice);
+        scores_to_rbs5_lanes(a0, R / IRS_RBS_PER_RBG, active, rbs_per_slice);
+        PHASE_STAMP(2, 2);
         int base_s = 0, rbs_s = 0, algo = 0;
         {
             int run = 0;
@@ -192,34 +247,40 @@ __device__ __forceinline__ void action_to_rb_core(const StepArgs& A, int e, cons
         }
         if (cfg.fixed_intra >= 0) algo = cfg.fixed_intra;
         const bool member = s_mine >= 0;
-        const int n = __popc(gmask);
+        const int n = G.n;
         // round robin over UEs with a non-empty buffer (all of them if none) - common.py:517-524
         uint32_t elmask = gmask & __ballot_sync(FULL, member && !isclose0(occ));
         if (elmask == 0) elmask = gmask;
         const int rr_buf = rr_share(elmask, rbs_s);
         const int rr_all = rr_share(gmask, rbs_s); // fallback: account_buffer=False
         // throughput each UE could use - common.py:567-583, 648-664
-        const double ta_a = (sebar * DIVC((double)rbs_s * cfg.bandwidth, R)) / (double)n;
+        const double ta_a = div_small(sebar * DIVC((double)rbs_s * cfg.bandwidth, R), n);
         const double ta_b = (occ * (double)up.max_pkts) * up.pkt_bits;
         const double ta = ta_a < ta_b ? ta_a : ta_b;
-        const double tamax = group_max(ta, gmask);
-        double snt = ((double)sum_sent / (double)win_len) * up.pkt_bits;
-        if (isclose0(ta)) snt = 1;
-        const double w = !isclose0(snt) ? ta / snt : 2 * tamax;
-        const double sw = group_sum_ordered(w, gmask);
-        const int pf_r = group_round_int_equal_sum(((double)rbs_s * w) / sw, gmask, rbs_s);
-        const int pf = sw != 0 ? pf_r : rr_all;
-        const double stt = group_sum_ordered(ta, gmask);
-        const int mt_r = group_round_int_equal_sum(((double)rbs_s * ta) / stt, gmask, rbs_s);
-        const int mt = stt != 0 ? mt_r : rr_all;
+        PHASE_STAMP(2, 3);
+        // proportional fairness (common.py:558-636) weighs by ta / mean sent throughput, max throughput (:639-701) by ta:
+        // the same normalise-and-round over the slice's UEs.  A slice runs ONE of the two, so each lane feeds the value
+        // of its own slice's algorithm through a single pass.
+        double val = ta;
+        if (__any_sync(FULL, member && algo == 1)) {
+            const double tamax = group_max(ta, G);
+            double snt = ((double)sum_sent / (double)win_len) * up.pkt_bits;
+            if (isclose0(ta)) snt = 1;
+            const double w = !isclose0(snt) ? ta / snt : 2 * tamax;
+            if (algo == 1) val = w;
+        }
+        PHASE_STAMP(2, 4);
+        const double sv = group_sum_ordered(val, G);
+        const int share_r = group_round_int_equal_sum(((double)rbs_s * val) / sv, G, rbs_s);
+        const int share = sv != 0 ? share_r : rr_all;
+        PHASE_STAMP(2, 5);
         if (member) {
             if (algo == 0) count = rr_buf;
-            else if (algo == 1) count = pf;
-            else if (algo == 2) count = mt;
+            else if (algo == 1 || algo == 2) count = share;
             else atomicOr(&st.err[e], ERR_INTRA_ACTION); // ValueError, ib_sched.py:341-344
         }
         // common.py:464-478 distribute_rbs_ues: consecutive runs inside the slice's block
-        start = base_s + group_prefix_excl(count, gmask);
+        start = base_s + group_prefix_excl(count, G);
         if (count <= 0) start = 0;
         // ib_sched.py:345-347 assert sum == 135
         int total = count;
@@ -230,6 +291,7 @@ __device__ __forceinline__ void action_to_rb_core(const StepArgs& A, int e, cons
         for (int s = 0; s < S; ++s) expect += smask[s] ? rbs_per_slice[s] : 0;
         if (lane == 0 && total != expect) atomicOr(&st.err[e], ERR_RB_SUM);
     }
+    PHASE_STAMP(2, 6);
     start_out = start;
     count_out = count;
     if (lane < U) {

@@ -706,4 +706,13 @@ int irs_check_errors(irs_env* env, int32_t* first_env, int32_t* code, void* stre
     return IRS_ERR_ENV;
 }
 
+#ifdef IRS_PHASE_CLOCK
+// debug builds only: the SM-clock stamps of the last k_env_step launch, [block][warp][stamp] (scripts/phase_clock.py)
+int irs_debug_phase_clock(long long* out_host, int n_blocks)
+{
+    cudaDeviceSynchronize();
+    return (int)cudaMemcpyFromSymbol(out_host, g_phase_clock, sizeof(long long) * 32 * (size_t)n_blocks);
+}
+#endif
+
 } // extern "C"

@@ -104,117 +104,128 @@ __device__ __forceinline__ double div_const(double x, double c, double y)
     return __fma_rn(__fma_rn(-q1, c, x), y, q1);
 }
 #define DIVC(x, c) div_const((x), (double)(c), 1.0 / (double)(c))
+// x / n for a member count n = 1..5 (UEs of a slice, slices of a reward term) the same way, the reciprocal picked from
+// constants.  A float64 division is ~500 cycles of dependent latency on the one-warp-per-env critical paths, this is
+// ~50.  n = 0 (np.mean of an empty selection; only ever computed on lanes whose result is not used) gives nan.
+__device__ __forceinline__ double div_small(double x, int n)
+{
+    double y = 1.0;
+    y = n == 2 ? 0.5 : y;
+    y = n == 3 ? 1.0 / 3.0 : y;
+    y = n == 4 ? 0.25 : y;
+    y = n == 5 ? 0.2 : y;
+    const double q = div_const(x, (double)n, y);
+    return n >= 1 ? q : __longlong_as_double(0x7ff8000000000000ll);
+}
+
+#ifdef IRS_PHASE_CLOCK /* debug builds only (scripts/phase_clock.py): SM clock at the phase boundaries of k_env_step */
+__device__ long long g_phase_clock[4096][4][8]; // [block][warp 0 | warp 1 | action core | tail core][stamp]
+#define PHASE_STAMP(row, i) do { if (blockDim.x == 64 && (threadIdx.x & 31) == 0 && blockIdx.x < 4096) { long long t_; \
+    asm volatile("mov.u64 %0, %%clock64;" : "=l"(t_) :: "memory"); g_phase_clock[blockIdx.x][row][i] = t_; } } while (0)
+#define PHASE_CLOCK(i) do { if (FULL_STEP) PHASE_STAMP(wib, i); } while (0)
+#else
+#define PHASE_STAMP(row, i) do { } while (0)
+#define PHASE_CLOCK(i) do { } while (0)
+#endif
 
 // ---- ordered reductions over a group of lanes --------------------------------------------
-// `mask` is the set of lanes that belong to the calling lane's group (0 for idle lanes); all 32
-// lanes must call.  Members are visited in ascending lane order, which is the ascending UE /
-// slice index order NumPy iterates in.  For n < 8 np.add.reduce is a serial sum starting
-// from 0. (numpy/_core/src/umath/loops_utils.h.src, DOUBLE_pairwise_sum), then added to the
-// reduction identity: 0. + res.
-__device__ __noinline__ double group_sum_ordered(double x, uint32_t mask)
+// A group = the UE lanes of one slice (at most NS = 5, agents/ib_sched.py:50).  Its members are listed ONCE per core
+// (GroupIdx: src[k] = lane of the k-th member in ascending lane order, the calling lane itself past the end; all-own
+// for idle lanes, whose mask is 0), so that every reduction below is five shuffles plus its arithmetic instead of a
+// find-first-set chain per call; all 32 lanes must call.  Members are visited in ascending lane order, which is the
+// ascending UE / slice index order NumPy iterates in.  For n < 8 np.add.reduce is a serial sum starting from 0.
+// (numpy/_core/src/umath/loops_utils.h.src, DOUBLE_pairwise_sum), then added to the reduction identity: 0. + res.
+struct GroupIdx {
+    int src[NS];
+    int n, rank; // members; how many of them sit on lower lanes than the caller
+    uint32_t mask;
+};
+__device__ __forceinline__ GroupIdx group_index(uint32_t mask)
 {
-    double res = 0.;
-    uint32_t m = mask;
+    GroupIdx G;
     const int lane = lane_id();
+    G.mask = mask;
+    G.n = __popc(mask);
+    G.rank = __popc(mask & ((1u << lane) - 1u));
+    uint32_t m = mask;
 #pragma unroll
     for (int k = 0; k < NS; ++k) {
-        const bool valid = m != 0;
-        const int src = valid ? (__ffs(m) - 1) : lane;
+        G.src[k] = m ? (__ffs(m) - 1) : lane;
         m &= m - 1;
-        const double v = __shfl_sync(FULL, x, src);
-        if (valid) res += v;
+    }
+    return G;
+}
+__device__ __forceinline__ double group_sum_ordered(double x, const GroupIdx& G)
+{
+    double res = 0.;
+#pragma unroll
+    for (int k = 0; k < NS; ++k) {
+        const double v = __shfl_sync(FULL, x, G.src[k]);
+        if (k < G.n) res += v;
     }
     return 0. + res;
 }
-__device__ __noinline__ int group_sum_int(int x, uint32_t mask)
+__device__ __forceinline__ int group_sum_int(int x, const GroupIdx& G)
 {
     int res = 0;
-    uint32_t m = mask;
-    const int lane = lane_id();
 #pragma unroll
     for (int k = 0; k < NS; ++k) {
-        const bool valid = m != 0;
-        const int src = valid ? (__ffs(m) - 1) : lane;
-        m &= m - 1;
-        const int v = __shfl_sync(FULL, x, src);
-        if (valid) res += v;
+        const int v = __shfl_sync(FULL, x, G.src[k]);
+        if (k < G.n) res += v;
     }
     return res;
 }
-__device__ __noinline__ double group_max(double x, uint32_t mask)
+__device__ __forceinline__ double group_max(double x, const GroupIdx& G)
 {
     double res = x;
-    uint32_t m = mask;
-    const int lane = lane_id();
 #pragma unroll
     for (int k = 0; k < NS; ++k) {
-        const bool valid = m != 0;
-        const int src = valid ? (__ffs(m) - 1) : lane;
-        m &= m - 1;
-        const double v = __shfl_sync(FULL, x, src);
-        if (valid && v > res) res = v;
+        const double v = __shfl_sync(FULL, x, G.src[k]);
+        if (k < G.n && v > res) res = v;
     }
     return res;
 }
 
-// agents/common.py:481-505 round_int_equal_sum over the members of `mask` (one value per
+// agents/common.py:481-505 round_int_equal_sum over the members of G (one value per
 // lane).  np.argsort pinned to kind="stable" (SURVEY 7.1): the +1s go to entries in
 // descending value order, ties -> higher index first, cyclically.  Returns this lane's
 // integer share (0 for non-members and for x == 0).
-__device__ __noinline__ int group_round_int_equal_sum(double x, uint32_t mask, int target)
+__device__ __forceinline__ int group_round_int_equal_sum(double x, const GroupIdx& G, int target)
 {
     const int lane = lane_id();
-    const bool member = (mask >> lane) & 1u;
+    const bool member = (G.mask >> lane) & 1u;
     const bool nz = member && x != 0;
-    // the set of nonzero members of my group
-    uint32_t nzmask = 0;
-    {
-        uint32_t m = mask;
+    const uint32_t nzb = __ballot_sync(FULL, nz) & G.mask; // the nonzero members of my group
+    double v[NS];
+    bool use[NS];
+    double res = 0.;
 #pragma unroll
-        for (int k = 0; k < NS; ++k) {
-            const bool valid = m != 0;
-            const int src = valid ? (__ffs(m) - 1) : lane;
-            m &= m - 1;
-            const int f = __shfl_sync(FULL, (int)nz, src);
-            if (valid && f) nzmask |= 1u << src;
-        }
+    for (int k = 0; k < NS; ++k) {
+        v[k] = __shfl_sync(FULL, x, G.src[k]);
+        use[k] = k < G.n && ((nzb >> G.src[k]) & 1u);
+        if (use[k]) res += v[k];
     }
-    const double sum = group_sum_ordered(x, nzmask);
-    const int cnt = __popc(nzmask);
+    const double sum = 0. + res;
+    const int cnt = __popc(nzb);
     int p = 0;
     if (nz) p = (int)floor(((double)target * x) / sum);
-    const int tot = group_sum_int(p, nzmask);
-    const int adj = target - tot;
-    // rank in descending order, ties -> higher index first
-    int rank = 0;
-    {
-        uint32_t m = nzmask;
+    const int adj = target - group_sum_int(p, G); // p is 0 on the zero members
+    int rank = 0; // rank in descending order, ties -> higher index first
 #pragma unroll
-        for (int k = 0; k < NS; ++k) {
-            const bool valid = m != 0;
-            const int src = valid ? (__ffs(m) - 1) : lane;
-            m &= m - 1;
-            const double v = __shfl_sync(FULL, x, src);
-            if (valid && (v > x || (v == x && src > lane))) ++rank;
-        }
-    }
+    for (int k = 0; k < NS; ++k)
+        if (use[k] && (v[k] > x || (v[k] == x && G.src[k] > lane))) ++rank;
     if (nz && adj > rank) p += (adj - rank - 1) / cnt + 1;
     return p;
 }
 
-// Exclusive prefix (ascending lane order) of an int over the members of `mask`.
-__device__ __noinline__ int group_prefix_excl(int x, uint32_t mask)
+// Exclusive prefix (ascending lane order) of an int over the members of G.
+__device__ __forceinline__ int group_prefix_excl(int x, const GroupIdx& G)
 {
-    const int lane = lane_id();
     int res = 0;
-    uint32_t m = mask;
 #pragma unroll
     for (int k = 0; k < NS; ++k) {
-        const bool valid = m != 0;
-        const int src = valid ? (__ffs(m) - 1) : lane;
-        m &= m - 1;
-        const int v = __shfl_sync(FULL, x, src);
-        if (valid && src < lane) res += v;
+        const int v = __shfl_sync(FULL, x, G.src[k]);
+        if (k < G.rank) res += v;
     }
     return res;
 }

@@ -175,6 +175,7 @@ __device__ __forceinline__ void env_tail_core(const StepArgs& A, int e, const ir
     const DevState& st = A.st;
     const irs_config& c = A.cfg;
     const int lane = lane_id();
+    PHASE_STAMP(3, 0);
     if (lane >= U) { f.sent = 0; f.rb_count = 0; dropped = 0; inc = 0; }
     const int win_len = win_len_old < A.win_cap ? win_len_old + 1 : A.win_cap;
     const int head = (head_old + 1) % A.win_cap;
@@ -183,6 +184,7 @@ __device__ __forceinline__ void env_tail_core(const StepArgs& A, int e, const ir
     if (lane == 0) { st.win_len[e] = win_len; st.win_head[e] = head; st.step[e] = step; }
 
     const SliceView v = format_obs_warp(A, e, sc, f, win_len); // comm_env.py:340
+    PHASE_STAMP(3, 4);
 
     if (block_sync) __syncthreads(); // keeps the block's warps in the same code region (I-cache)
     // ---- calculate_reward (ib_sched.py:206-221, common.py:381-439) ----------------------
@@ -213,7 +215,7 @@ __device__ __forceinline__ void env_tail_core(const StepArgs& A, int e, const ir
             const bool sel = nneg == 0 ? true : (npneg ? (Aa[s] * Pp[s] < 0) : (Aa[s] < 0));
             if (sel) { res += Aa[s]; ++m; }
         }
-        r0 = (0. + res) / (double)m - ((nneg != 0 && npneg) ? 1 : 0); // common.py:410-426
+        r0 = div_small(0. + res, m) - ((nneg != 0 && npneg) ? 1 : 0); // common.py:410-426
     }
     double r_intra = 0; // common.py:428-437
     {
@@ -227,6 +229,7 @@ __device__ __forceinline__ void env_tail_core(const StepArgs& A, int e, const ir
     if (lane == 0) st.out_reward[(size_t)e * 6] = r0;
     if (lane < S) st.out_reward[(size_t)e * 6 + 1 + lane] = r_intra;
 
+    PHASE_STAMP(3, 5);
     if (block_sync) __syncthreads();
     // ---- episode metrics (metrics.py:62-71 as running sums; definitions from
     //      results/gen_results.py:791-809, 874-970, 973-1022) -----------------------------
@@ -276,6 +279,7 @@ __device__ __forceinline__ void env_tail_core(const StepArgs& A, int e, const ir
         if (done) acc[15] += 1;
         st.out_done[e] = done ? 1 : 0;
     }
+    PHASE_STAMP(3, 6);
     if (done && c.auto_reset && !A.defer_rollover) {
         __syncwarp();
         reset_env_warp(A, e, -1, se_row);

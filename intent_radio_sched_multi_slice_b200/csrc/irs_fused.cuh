@@ -70,6 +70,7 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
     const int wglob = blockIdx.x * NW + wib;
     const int e = A.env_begin + (wglob >> split), grp = wglob & gmask; // this warp serves the UEs u with (u & gmask) == grp
     if (e >= A.env_end) { normal_tab_wait(); return; } // every warp of the block meets the table barrier exactly once
+    PHASE_CLOCK(0);
 
     // ---- phase 0: env scalars, this lane's UE record, and the ring slots the step can touch -------
     const int step = st.step[e], episode = st.episode[e];
@@ -118,7 +119,9 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
         rb_s = run.x; rb_c = run.y;
     }
 
+    PHASE_CLOCK(1);
     normal_tab_wait(); // the generators' table, requested at kernel entry, is in shared memory from here on
+    PHASE_CLOCK(2);
     // ---- phase 2: channel + traffic of this frame, and the two row sums per UE --------------
     const bool native = cfg.channel_mode == 2 && cfg.traffic_mode == 1;
     const int fl_mine = s_mine >= 0 ? __ldg(&sc->sl[s_mine].flags) : 0;
@@ -163,6 +166,7 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
             }
         }
         __syncwarp();
+        PHASE_CLOCK(3);
         // pair passes: lanes 0..15 serve one associated UE, lanes 16..31 the next.  Lane m of a side generates
         // SE quad m = the 8 elements accumulator m & 7 of row half m >> 3 visits (se_index), and adds them up in
         // registers in NumPy's order: both 135-term sums (ues.py:108-116 throughput terms, np.mean(SE)) without a
@@ -347,6 +351,7 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
     }
 
 
+    PHASE_CLOCK(4);
     // ---- phase 3: throughput, arrivals, closed-form buffer arithmetic - one UE per lane -------
     const double thr = floor(sum_t / up.pkt_bits);   // ues.py:108-116
     const double inc = floor(traffic / up.pkt_bits); // ues.py:199
@@ -458,12 +463,14 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
         xc->dropped[lane] = dropped; xc->inc[lane] = (int)inc; xc->occ1z[lane] = occ1z ? 1 : 0;
     }
     __syncthreads();
+    PHASE_CLOCK(5);
     if (wib != 0) return;
     UeFrame f;
     const int lu = lane < U ? lane : 0;
     f.occ = xc->occ[lu]; f.lat = xc->lat[lu]; f.sebar = xc->sebar[lu]; f.sent = xc->sent[lu];
     f.sum_sent = xc->sum_sent[lu]; f.sum_drop = xc->sum_drop[lu]; f.rb_count = xc->rb[lu].y; f.occ1z = xc->occ1z[lu] != 0;
     env_tail_core(A, e, sc, f, xc->dropped[lu], xc->inc[lu], win_len, head_w, step, sm[0][0]);
+    PHASE_CLOCK(6);
 }
 
 #ifndef UE_ENV_MINB

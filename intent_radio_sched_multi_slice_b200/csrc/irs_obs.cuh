@@ -87,24 +87,27 @@ __device__ __noinline__ SliceView format_obs_warp(const StepArgs& A, int e, cons
         if (s_mine == s) gmask = smask[s];
     }
     const bool member = s_mine >= 0;
-    const int n_mine = __popc(gmask);
+    const GroupIdx G = group_index(gmask);
+    const int n_mine = G.n;
     const irs_slice* sl_u = &sc->sl[member ? s_mine : 0];
     const int fl_u = member ? __ldg(&sl_u->flags) : 0;
 
     // per-UE drift, then the slice means (common.py:371-373 np.mean over the slice's UEs)
     double drift[3] = {0, 0, 0};
     if (member && (fl_u & IRS_F_REQ)) intent_drift_ue(sl_u, fl_u, f, win_len, A.win_mul, drift);
+    PHASE_STAMP(3, 1);
     double dsl_u[3];
     const int fbit[3] = {IRS_F_THR, IRS_F_REL, IRS_F_LAT};
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-        const double mean = group_sum_ordered(drift[k], gmask) / (double)n_mine;
+        const double mean = div_small(group_sum_ordered(drift[k], G), n_mine);
         dsl_u[k] = ((fl_u & IRS_F_REQ) && (fl_u & fbit[k])) ? mean : -2.0;
     }
-    const double se_slice_u = group_sum_ordered(f.sebar, gmask) / (double)n_mine; // ib_sched.py:146-157
-    const int rbs_alloc_u = group_sum_int(f.rb_count, gmask);                      // :176-181
-    const int snt_u = group_sum_int(f.sent, gmask);
+    const double se_slice_u = div_small(group_sum_ordered(f.sebar, G), n_mine); // ib_sched.py:146-157
+    const int rbs_alloc_u = group_sum_int(f.rb_count, G);                      // :176-181
+    const int snt_u = group_sum_int(f.sent, G);
 
+    PHASE_STAMP(3, 2);
     // ---- slice lanes: fetch the slice-level values from the slice's first UE lane -------
     const int sl_id = lane < S ? lane : 0;
     const uint32_t my_smask = lane < S ? smask[0] * (lane == 0) + smask[1] * (lane == 1) + smask[2] * (lane == 2) +
@@ -152,6 +155,7 @@ __device__ __noinline__ SliceView format_obs_warp(const StepArgs& A, int e, cons
             if (st.sorted[(size_t)e * S + j] == lane) pos = j;
     }
     v.pos = pos;
+    PHASE_STAMP(3, 3);
 
     if (lane < S) {
         double* p0 = st.out_obs0 + (size_t)e * IRS_OBS0 + pos * 10; // :160-173
