@@ -57,6 +57,7 @@ struct StepXchg { // hand-over between the warps of a k_env_step block
     short2 rb[32];
     double occ[32], lat[32], sebar[32];
     int sent[32], sum_sent[32], sum_drop[32], dropped[32], inc[32], occ1z[32];
+    double mu[32], traffic[32]; // pass A of every UE, by the block's last warp
 };
 template <bool FULL_STEP, bool RAWSE, int NW>
 __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP][136], const float2* __restrict__ ntab,
@@ -72,26 +73,82 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
     if (e >= A.env_end) { normal_tab_wait(); return; } // every warp of the block meets the table barrier exactly once
     PHASE_CLOCK(0);
 
-    // ---- phase 0: env scalars, this lane's UE record, and the ring slots the step can touch -------
+    // ---- phase 0: env scalars and this lane's UE record -----------------------------------------
     const int step = st.step[e], episode = st.episode[e];
     const int win_len = st.win_len[e], head_w = st.win_head[e];
     const int p = (head_w + 1) % A.win_cap; // window slot of this frame (deque.appendleft)
     const uint64_t key = env_key(cfg.seed, st.visit[e]);
     const irs_scenario* sc = st.bank + st.scen[e];
     const bool ue_lane = lane < U && (lane & gmask) == grp;
-    const int s_mine = ue_lane ? (int)sc->ue_slice[lane] : -1;
-    UeParams up = ue_params(sc, s_mine);
-    if (up.depth > st.row_stride) up.depth = st.row_stride;
+    const int s_lane = lane < U ? (int)sc->ue_slice[lane] : -1; // this lane's UE, whichever warp serves it
+    const int s_mine = ue_lane ? s_lane : -1;
     const size_t eu = (size_t)e * U + (ue_lane ? lane : 0);
     const int4 rec_a = *reinterpret_cast<const int4*>(st.ue_i + eu * UI_N); // tot, sum_sent, sum_drop, sent
     const double2 rec_d0 = *reinterpret_cast<const double2*>(st.ue_d + eu * UD_N); // occ, lat
     int2 evict = make_int2(0, 0);
     if (ue_lane && win_len == A.win_cap) evict = st.ring[eu * W + p];
     const int tot_prev = ue_lane ? rec_a.x : 0;
+    const int frame = step + 1, gid = cfg.env_id_base + e;
+    const bool native = cfg.channel_mode == 2 && cfg.traffic_mode == 1;
+    // In the one-launch step the generators' per-UE pass (pass A below) does not wait for the action: the block's last
+    // warp runs it for ALL of the env's UEs while warp 0 turns the action into RB runs.
+    constexpr bool SPLIT_A = FULL_STEP && NW > 1;
+    double mu_l = 0.0, traffic = 0.0;
+    int rb_s = 0, rb_c = 0;
+
+    // pass A, lane = UE: the per-episode mean (mimic_quadriga.py:37-41), the serial tail of the row (RBs 128..134, SE
+    // quad 16) into the serving warp's scratch at ws[14 u ..] - (SE, throughput term) pairs, or just the seven SE values
+    // when the RB runs are not known yet (SPLIT_A) - and the Poisson arrival (traffics/mult_slice.py:28-31)
+    auto pass_a = [&](int s_a, double* ws_a) {
+        const int fl_a = __ldg(&sc->sl[s_a].flags);
+        const uint4 wm = rng_quad(key, K_MU, lane, 0, 0, episode, gid);
+        mu_l = fabs(__fma_rn(7.5, (double)normal_lo(wm.x, ntab), 10.0));
+        const uint4 wt = rng_quad(key, K_SE, lane, 16, frame, episode, gid);
+        const uint32_t ww[4] = {wt.x, wt.y, wt.z, wt.w};
+        double* tp = ws_a + 14 * lane;
+        const uint32_t* sb = (RAWSE && A.sched_bits) ? A.sched_bits + ((size_t)e * U + lane) * 5 : nullptr;
+#pragma unroll
+        for (int k = 0; k < 7; ++k) {
+            const float z = (k & 1) ? normal_hi(ww[k >> 1], ntab) : normal_lo(ww[k >> 1], ntab);
+            const double x = fabs(__fma_rn(1.5, (double)z, mu_l));
+            if (SPLIT_A) tp[k] = x;
+            else reinterpret_cast<double2*>(tp)[k] = make_double2(x, sched_at(sb, rb_s, rb_c, 128 + k) ? A.bw_rb * x : 0.0);
+            if (RAWSE && A.raw.se_used) A.raw.se_used[((size_t)e * U + lane) * R + 128 + k] = x;
+        }
+        if (fl_a & IRS_F_REQ) {
+            const int lam_a = __ldg(&sc->sl[s_a].lam_idx);
+            const uint4 wq = rng_quad(key, K_TRAFFIC, lane, 0, frame, episode, gid);
+            const double u01 = ((double)(wq.x >> 5) * 67108864.0 + (double)(wq.y >> 6)) * (1.0 / 9007199254740992.0);
+            const double* cdf = st.cdf + (size_t)lam_a * IRS_POISSON_K;
+            int lo = 0;
+#pragma unroll
+            for (int stp = IRS_POISSON_K / 2; stp > 0; stp >>= 1)
+                if (__ldg(&cdf[lo + stp - 1]) <= u01) lo += stp;
+            if (__ldg(&cdf[lo]) <= u01) lo += 1;
+            traffic = (double)lo * 1e6;
+        }
+    };
+
+    if (FULL_STEP) { // ib_sched.py:223-349 on every UE's previous frame (occupancy, mean SE, window sum of sent packets)
+        if (SPLIT_A) normal_tab_wait();
+        if (wib == 0) {
+            const size_t ea = (size_t)e * U + (lane < U ? lane : 0);
+            int rs_a, rc_a;
+            action_to_rb_core(A, e, sc, st.ue_d[ea * UD_N + UD_OCC], st.ue_d[ea * UD_N + UD_SEBAR],
+                              st.ue_i[ea * UI_N + UI_SUM_SENT], win_len, step, episode, rs_a, rc_a);
+            xc->rb[lane] = make_short2((short)rs_a, (short)rc_a);
+        } else if (SPLIT_A && wib == NW - 1 && native) {
+            if (s_lane >= 0) pass_a(s_lane, &sm[lane & gmask][0][0]); // an unassociated UE has SE 0 and no traffic
+            xc->mu[lane] = mu_l; xc->traffic[lane] = traffic;
+        }
+    }
+    // ---- the ring slots the step can touch (after the action on warp 0: the loads hang on a chain of three dependent
+    //      loads - scenario, slice, depth - that the action must not wait for) -----------------------------------------
+    UeParams up = ue_params(sc, s_mine);
+    if (up.depth > st.row_stride) up.depth = st.row_stride;
     int* row = st.buf + eu * (size_t)st.row_stride;
     const int live_prev = ue_lane ? ROW_LIVE(st.ue_i[eu * UI_N + UI_PATH]) : 0; // ages [0, live_prev) may hold packets
     const long long wsum_prev = ue_lane ? st.wsum[eu] : 0;
-    const int frame = step + 1, gid = cfg.env_id_base + e;
     const int head = frame % up.depth;                 // slot of age 0 after this step
     const int a_old = min(live_prev, up.depth - 1);    // oldest age that may hold packets after the shift (0: none)
     // buffer.py:60: the packets that reach age `depth` now sit in the slot the new arrivals will take
@@ -103,68 +160,33 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
         const int q = p_old + k;
         look[k] = (ue_lane && a_old - k >= 1) ? row[q >= up.depth ? q - up.depth : q] : 0;
     }
-    int rb_s, rb_c;
-    if (FULL_STEP) { // ib_sched.py:223-349 on every UE's previous frame (occupancy, mean SE, window sum of sent packets)
-        if (wib == 0) {
-            const size_t ea = (size_t)e * U + (lane < U ? lane : 0);
-            int rs_a, rc_a;
-            action_to_rb_core(A, e, sc, st.ue_d[ea * UD_N + UD_OCC], st.ue_d[ea * UD_N + UD_SEBAR],
-                              st.ue_i[ea * UI_N + UI_SUM_SENT], win_len, step, episode, rs_a, rc_a);
-            xc->rb[lane] = make_short2((short)rs_a, (short)rc_a);
-        }
+    if (FULL_STEP) {
         __syncthreads();
         rb_s = xc->rb[lane].x; rb_c = xc->rb[lane].y;
+        if (SPLIT_A && native) { mu_l = xc->mu[lane]; traffic = xc->traffic[lane]; }
     } else {
         const short2 run = st.rb[eu];
         rb_s = run.x; rb_c = run.y;
     }
 
     PHASE_CLOCK(1);
-    normal_tab_wait(); // the generators' table, requested at kernel entry, is in shared memory from here on
+    if (!SPLIT_A) normal_tab_wait(); // the generators' table, requested at kernel entry, is in shared memory from here on
     PHASE_CLOCK(2);
     // ---- phase 2: channel + traffic of this frame, and the two row sums per UE --------------
-    const bool native = cfg.channel_mode == 2 && cfg.traffic_mode == 1;
     const int fl_mine = s_mine >= 0 ? __ldg(&sc->sl[s_mine].flags) : 0;
     const bool has_traffic = (fl_mine & IRS_F_REQ) != 0;
     const int lam_idx = has_traffic ? __ldg(&sc->sl[s_mine].lam_idx) : 0;
-    double sum_t = 0.0, sum_se = 0.0, traffic = 0.0, mu_l = 0.0;
+    double sum_t = 0.0, sum_se = 0.0;
     if (!native) {
         if (cfg.traffic_mode == 0) traffic = ue_lane ? A.traffic[eu] : 0.0;
         else if (has_traffic) traffic = native_traffic(key, st.cdf, lane, lam_idx, frame, episode, gid);
     }
     if (native) {
-        // Per-warp scratch in shared memory: tail (SE, throughput term) pairs of UE u at ws[14 u .. 14 u + 13],
-        // per-UE results (sum_t, sum_se) at ws[352 + 4 u ..].
+        // Per-warp scratch in shared memory: the tail of UE u at ws[14 u .. 14 u + 13], per-UE results
+        // (sum_t, sum_se) at ws[352 + 4 u ..].
         double* ws = &sm[wib][0][0];
         const bool gen = ue_lane && s_mine >= 0; // an unassociated UE has SE 0 and no traffic in native mode
-        // pass A, lane = UE: the per-episode mean (mimic_quadriga.py:37-41), the serial tail of the row (RBs 128..134,
-        // SE quad 16) with its throughput terms, and the Poisson arrival (traffics/mult_slice.py:28-31)
-        if (gen) {
-            const uint4 wm = rng_quad(key, K_MU, lane, 0, 0, episode, gid);
-            mu_l = fabs(__fma_rn(7.5, (double)normal_lo(wm.x, ntab), 10.0));
-            const uint4 wt = rng_quad(key, K_SE, lane, 16, frame, episode, gid);
-            const uint32_t ww[4] = {wt.x, wt.y, wt.z, wt.w};
-            const uint32_t* sb = (RAWSE && A.sched_bits) ? A.sched_bits + eu * 5 : nullptr;
-            double2* tp = reinterpret_cast<double2*>(ws + 14 * lane);
-#pragma unroll
-            for (int k = 0; k < 7; ++k) {
-                const float z = (k & 1) ? normal_hi(ww[k >> 1], ntab) : normal_lo(ww[k >> 1], ntab);
-                const double x = fabs(__fma_rn(1.5, (double)z, mu_l));
-                tp[k] = make_double2(x, sched_at(sb, rb_s, rb_c, 128 + k) ? A.bw_rb * x : 0.0);
-                if (RAWSE && A.raw.se_used) A.raw.se_used[eu * R + 128 + k] = x;
-            }
-            if (has_traffic) {
-                const uint4 wq = rng_quad(key, K_TRAFFIC, lane, 0, frame, episode, gid);
-                const double u01 = ((double)(wq.x >> 5) * 67108864.0 + (double)(wq.y >> 6)) * (1.0 / 9007199254740992.0);
-                const double* cdf = st.cdf + (size_t)lam_idx * IRS_POISSON_K;
-                int lo = 0;
-#pragma unroll
-                for (int stp = IRS_POISSON_K / 2; stp > 0; stp >>= 1)
-                    if (__ldg(&cdf[lo + stp - 1]) <= u01) lo += stp;
-                if (__ldg(&cdf[lo]) <= u01) lo += 1;
-                traffic = (double)lo * 1e6;
-            }
-        }
+        if (!SPLIT_A && gen) pass_a(s_mine, ws);
         __syncwarp();
         PHASE_CLOCK(3);
         // pair passes: lanes 0..15 serve one associated UE, lanes 16..31 the next.  Lane m of a side generates
@@ -208,12 +230,18 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
             acc_se = acc_se + __shfl_down_sync(FULL, acc_se, 4);
             acc_t = acc_t + __shfl_down_sync(FULL, acc_t, 4);
             if (l16 == 8) { // second half: the 7-element tail is added serially after the tree
-                const double2* tp = reinterpret_cast<const double2*>(ws + 14 * uj);
+                const double* tp = ws + 14 * uj;
 #pragma unroll
                 for (int k = 0; k < 7; ++k) {
-                    const double2 xt = tp[k];
-                    acc_se += xt.x;
-                    acc_t += xt.y;
+                    if (SPLIT_A) {
+                        const double xt = tp[k];
+                        acc_se += xt;
+                        acc_t += sched_at(sb, rs, rc, 128 + k) ? A.bw_rb * xt : 0.0;
+                    } else {
+                        const double2 xt = reinterpret_cast<const double2*>(tp)[k];
+                        acc_se += xt.x;
+                        acc_t += xt.y;
+                    }
                 }
             }
             const double res_se = 0. + (acc_se + __shfl_down_sync(FULL, acc_se, 8)); // valid on lanes 0, 16
