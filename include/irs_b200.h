@@ -38,6 +38,7 @@ extern "C" {
 #define IRS_NUM_RBS 135       /* env_config/mult_slice.yml:5 */
 #define IRS_WINDOW 10         /* agents/ib_sched.py:49 max_obs_memory */
 #define IRS_MAX_UES_SLICE 5   /* agents/ib_sched.py:50 */
+#define IRS_NOALLOC_MAX_ENVS 1048576 /* irs_check_errors_noalloc: 4,096 scratch slots (16 KB) x 256 envs */
 #define IRS_RBS_PER_RBG 5     /* agents/ib_sched.py:56 */
 #define IRS_OBS0 50           /* agents/ib_sched.py:413-470: player_0 observations */
 #define IRS_OBSI 19           /* player_{s+1} observations */
@@ -276,6 +277,19 @@ int irs_set_episode_order(irs_env* env, const int32_t* order_dev, int32_t n, voi
 /* Buffer.buffer of every UE as the reference indexes it (buffer.py:47: index = age in steps): i32
  * [E][25][row_stride] into caller-owned device memory, de-rotating the ring rows.  Asynchronous on `stream`. */
 int irs_read_buffers(irs_env* env, int32_t* out_dev, void* stream);
+/* No counterpart in the reference: added for callers that cannot allocate
+ * device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The error scan
+ * of irs_check_errors on caller-passed arrays, with its scratch in a file-scope static __device__ array of the library
+ * (16 KB: one i32 slot per 256 envs; every GPU that loads the library holds it until exit) instead of the state blob:
+ * err_dev = i32 [num_envs] error words (layout.err of a bound state blob, or any array of that shape); out_dev = i32 [2]
+ * in device memory <- (index of the first env with a non-zero word, that word), or (-1, 0) when there is none.
+ * Asynchronous on `stream`; allocates nothing (no cudaMalloc / cudaFree / allocating library call) and does not
+ * synchronise.  num_envs > IRS_NOALLOC_MAX_ENVS is rejected with IRS_ERR_ARG and a message in errbuf (optional, may be
+ * NULL).  The scratch is shared by every call on the device and keeps the last call's contents; a call overwrites every
+ * slot it reads, so nothing needs clearing between calls, but calls that OVERLAP on the GPU (different streams) race:
+ * serialise them. */
+int irs_check_errors_noalloc(const int32_t* err_dev, int32_t num_envs, int32_t* out_dev, void* stream, char* errbuf,
+                             size_t errbuf_len);
 const char* irs_last_error(const irs_env* env);
 int irs_version(void);
 

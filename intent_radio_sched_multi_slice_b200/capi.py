@@ -13,6 +13,7 @@ from . import build as _build
 MAX_UES, MAX_SLICES, NUM_RBS, WINDOW, OBS0, OBSI, NUM_METRICS = 25, 5, 135, 10, 50, 19, 16
 
 IRS_OK, IRS_ERR_ARG, IRS_ERR_UNBOUND, IRS_ERR_CUDA, IRS_ERR_ENV = 0, -1, -2, -3, -4
+IRS_NOALLOC_MAX_ENVS = 1048576  # irs_check_errors_noalloc: size of the library's static scratch (include/irs_b200.h)
 ERR_INTRA_ACTION, ERR_EPISODE_RANGE, ERR_RB_SUM, ERR_TRACE_EPISODE, ERR_RB_SHARED = 1, 2, 4, 8, 16
 
 METRIC_NAMES = [
@@ -90,6 +91,7 @@ SYMBOLS = {
     "irs_check_errors": (C.c_int, [_P, C.POINTER(C.c_int32), C.POINTER(C.c_int32), _P]),
     "irs_set_episode_order": (C.c_int, [_P, _P, C.c_int32, _P]),
     "irs_read_buffers": (C.c_int, [_P, _P, _P]),
+    "irs_check_errors_noalloc": (C.c_int, [_P, C.c_int32, _P, _P, C.c_char_p, C.c_size_t]),
     "irs_last_error": (C.c_char_p, [_P]),
 }
 

@@ -6,6 +6,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <limits.h>
+#include <mutex>
 #include <new>
 
 #include <nvtx3/nvToolsExt.h> // header-only; a no-op unless a profiler is attached
@@ -704,6 +706,98 @@ int irs_check_errors(irs_env* env, int32_t* first_env, int32_t* code, void* stre
     if (code) *code = h[1];
     snprintf(env->err, sizeof(env->err), "env %d error word %d", h[0], h[1]);
     return IRS_ERR_ENV;
+}
+
+// ---- irs_check_errors_noalloc: the error scan on a library-owned static scratch (no counterpart in the reference; added
+// for callers that cannot allocate: graph capture, serving loops) ------------------
+// One int per 256-env block (the block's first env with a non-zero error word, INT_MAX: none), then one block reduces the
+// slots.  Every slot a call reads is written by the same call, so nothing has to be cleared between calls; the array is
+// shared by every call on the device and keeps the last call's contents - calls that overlap on the GPU race.
+#define NOALLOC_SLOTS (IRS_NOALLOC_MAX_ENVS / 256)
+static __device__ __align__(256) int32_t g_noalloc_scratch[NOALLOC_SLOTS];
+
+__global__ void __launch_bounds__(256) k_err_scan_blocks(const int32_t* __restrict__ err, int num_envs, int32_t* __restrict__ slots)
+{
+    const int e = blockIdx.x * 256 + threadIdx.x;
+    const bool bad = e < num_envs && err[e] != 0;
+    const uint32_t b = __ballot_sync(FULL, bad);
+    __shared__ int first[8];
+    if ((threadIdx.x & 31) == 0) first[threadIdx.x >> 5] = b ? blockIdx.x * 256 + (int)(threadIdx.x & ~31u) + __ffs(b) - 1 : INT_MAX;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int m = first[0];
+#pragma unroll
+        for (int w = 1; w < 8; ++w) m = min(m, first[w]);
+        slots[blockIdx.x] = m;
+    }
+}
+__global__ void __launch_bounds__(256) k_err_first(const int32_t* __restrict__ err, int n_slots, const int32_t* __restrict__ slots,
+                                                  int32_t* __restrict__ out)
+{
+    __shared__ int part[256];
+    int m = INT_MAX;
+    for (int i = threadIdx.x; i < n_slots; i += 256) m = min(m, slots[i]);
+    part[threadIdx.x] = m;
+    __syncthreads();
+    for (int d = 128; d > 0; d >>= 1) {
+        if (threadIdx.x < d) part[threadIdx.x] = min(part[threadIdx.x], part[threadIdx.x + d]);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        const int e = part[0];
+        out[0] = e == INT_MAX ? -1 : e;
+        out[1] = e == INT_MAX ? 0 : err[e];
+    }
+}
+
+// device address of the static scratch: the symbol's name is a host-side stand-in in host code, so the address is asked
+// for once per device, with that device current
+static int32_t* noalloc_scratch_ptr(cudaError_t* ce)
+{
+    static std::mutex mu;
+    static int32_t* ptr[64] = {};
+    int dev = -1;
+    *ce = cudaGetDevice(&dev);
+    if (*ce != cudaSuccess) return nullptr;
+    if (dev < 0 || dev >= 64) { *ce = cudaErrorInvalidDevice; return nullptr; }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptr[dev]) {
+        void* q = nullptr;
+        *ce = cudaGetSymbolAddress(&q, g_noalloc_scratch);
+        if (*ce != cudaSuccess) return nullptr;
+        ptr[dev] = (int32_t*)q;
+    }
+    return ptr[dev];
+}
+
+int irs_check_errors_noalloc(const int32_t* err_dev, int32_t num_envs, int32_t* out_dev, void* stream, char* errbuf,
+                             size_t errbuf_len)
+{
+    auto say = [&](int code, const char* fmt, long long a, long long b) {
+        if (errbuf && errbuf_len) snprintf(errbuf, errbuf_len, fmt, a, b);
+        return code;
+    };
+    if (!err_dev || !out_dev) return say(IRS_ERR_ARG, "irs_check_errors_noalloc: null err_dev / out_dev", 0, 0);
+    if (num_envs < 1) return say(IRS_ERR_ARG, "irs_check_errors_noalloc: num_envs %lld < 1", num_envs, 0);
+    if (num_envs > IRS_NOALLOC_MAX_ENVS)
+        return say(IRS_ERR_ARG, "irs_check_errors_noalloc: num_envs %lld exceeds IRS_NOALLOC_MAX_ENVS (%lld): the static scratch "
+                                "holds one slot per 256 envs", num_envs, IRS_NOALLOC_MAX_ENVS);
+    cudaError_t ce;
+    int32_t* slots = noalloc_scratch_ptr(&ce);
+    if (!slots) {
+        if (errbuf && errbuf_len) snprintf(errbuf, errbuf_len, "irs_check_errors_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(ce));
+        return IRS_ERR_CUDA;
+    }
+    const int n_slots = (num_envs + 255) / 256;
+    cudaStream_t st = (cudaStream_t)stream;
+    k_err_scan_blocks<<<n_slots, 256, 0, st>>>(err_dev, num_envs, slots);
+    k_err_first<<<1, 256, 0, st>>>(err_dev, n_slots, slots, out_dev);
+    ce = cudaGetLastError();
+    if (ce != cudaSuccess) {
+        if (errbuf && errbuf_len) snprintf(errbuf, errbuf_len, "irs_check_errors_noalloc: launch: %s", cudaGetErrorString(ce));
+        return IRS_ERR_CUDA;
+    }
+    return IRS_OK;
 }
 
 #ifdef IRS_PHASE_CLOCK
