@@ -178,8 +178,8 @@ __device__ __forceinline__ void action_to_rb_core(const StepArgs& A, int e, cons
         for (int s = 0; s < S; ++s) a0_in[s] = __ldg(&sc->sl[s].n_ues) > 0 ? 1.0 : -1.0;
     } else if (cfg.policy == 2) { // agents/mapf.py:41-111
         const int n = G.n;
-        const double occ_mean = group_sum_ordered(occ, G) / (double)n;
-        const double snt_mean = group_sum_ordered((double)sum_sent / (double)win_len, G) / (double)n;
+        const double occ_mean = div_small(group_sum_ordered(occ, G), n);
+        const double snt_mean = div_small(group_sum_ordered(div_small((double)sum_sent, win_len), G), n);
         double occ_mbps[S], sent_mbps[S], w[S];
         double mx = 0;
 #pragma unroll
@@ -264,7 +264,7 @@ __device__ __forceinline__ void action_to_rb_core(const StepArgs& A, int e, cons
         double val = ta;
         if (__any_sync(FULL, member && algo == 1)) {
             const double tamax = group_max(ta, G);
-            double snt = ((double)sum_sent / (double)win_len) * up.pkt_bits;
+            double snt = div_small((double)sum_sent, win_len) * up.pkt_bits;
             if (isclose0(ta)) snt = 1;
             const double w = !isclose0(snt) ? ta / snt : 2 * tamax;
             if (algo == 1) val = w;

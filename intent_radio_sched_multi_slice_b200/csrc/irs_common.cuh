@@ -104,18 +104,15 @@ __device__ __forceinline__ double div_const(double x, double c, double y)
     return __fma_rn(__fma_rn(-q1, c, x), y, q1);
 }
 #define DIVC(x, c) div_const((x), (double)(c), 1.0 / (double)(c))
-// x / n for a member count n = 1..5 (UEs of a slice, slices of a reward term) the same way, the reciprocal picked from
-// constants.  A float64 division is ~500 cycles of dependent latency on the one-warp-per-env critical paths, this is
-// ~50.  n = 0 (np.mean of an empty selection; only ever computed on lanes whose result is not used) gives nan.
+// x / n for a small count n = 1..10 (UEs of a slice, slices of a reward term, frames of the observation window) the same
+// way, the reciprocal read from constant memory.  A float64 division is ~500 cycles of dependent latency on the per-env
+// critical paths, this is ~50.  n = 0 (np.mean of an empty selection: 0 / 0) gives nan.
+__constant__ double c_recip[W + 1] = {0.0, 1.0, 1.0 / 2, 1.0 / 3, 1.0 / 4, 1.0 / 5, 1.0 / 6, 1.0 / 7, 1.0 / 8, 1.0 / 9, 1.0 / 10};
 __device__ __forceinline__ double div_small(double x, int n)
 {
-    double y = 1.0;
-    y = n == 2 ? 0.5 : y;
-    y = n == 3 ? 1.0 / 3.0 : y;
-    y = n == 4 ? 0.25 : y;
-    y = n == 5 ? 0.2 : y;
-    const double q = div_const(x, (double)n, y);
-    return n >= 1 ? q : __longlong_as_double(0x7ff8000000000000ll);
+    const int i = n < 0 ? 0 : (n > W ? 0 : n);
+    const double q = div_const(x, (double)n, c_recip[i]);
+    return i >= 1 ? q : x / (double)n;
 }
 
 #ifdef IRS_PHASE_CLOCK /* debug builds only (scripts/phase_clock.py): SM clock at the phase boundaries of k_env_step */

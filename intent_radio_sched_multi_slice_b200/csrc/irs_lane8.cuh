@@ -108,9 +108,9 @@ __global__ void __launch_bounds__(L8_THREADS, L8_ACTION_MINB) k_action_8(const _
         for (int i = 0; i < n; ++i) {
             const int u = (list >> (5 * i)) & 31;
             so += st.ue_d[(eu0 + u) * UD_N + UD_OCC];
-            ss += (double)st.ue_i[(eu0 + u) * UI_N + UI_SUM_SENT] / (double)win_len;
+            ss += div_small((double)st.ue_i[(eu0 + u) * UI_N + UI_SUM_SENT], win_len);
         }
-        const double om = (0. + so) / (double)n, sm = (0. + ss) / (double)n; // n == 0: 0/0 = nan like np.mean([])
+        const double om = div_small(0. + so, n), sm = div_small(0. + ss, n); // n == 0: 0/0 = nan like np.mean([])
         const double bsz = __ldg(&sc->sl[s].buffer_size), msg = __ldg(&sc->sl[s].message_size);
         const double occ_m = active[s] ? DIVC((om * bsz) * msg, 1e6) : 0.0;
         const double sent_m = active[s] ? DIVC(sm * msg, 1e6) : 0.0;
@@ -246,7 +246,7 @@ __global__ void __launch_bounds__(L8_THREADS, L8_ACTION_MINB) k_action_8(const _
                     if (i < n) {
                         const int u = (list >> (5 * i)) & 31;
                         const double sebar = st.ue_d[(eu0 + u) * UD_N + UD_SEBAR];
-                        const double ta_a = (sebar * DIVC((double)rbs_s * cfg.bandwidth, R)) / (double)n;
+                        const double ta_a = div_small(sebar * DIVC((double)rbs_s * cfg.bandwidth, R), n);
                         const double ta_b = (occ[i] * max_pkts) * pkt_bits;
                         ta[i] = ta_a < ta_b ? ta_a : ta_b;
                         tamax = (i == 0 || ta[i] > tamax) ? ta[i] : tamax;
@@ -262,7 +262,7 @@ __global__ void __launch_bounds__(L8_THREADS, L8_ACTION_MINB) k_action_8(const _
                         w[i] = 0;
                         if (i < n) {
                             const int u = (list >> (5 * i)) & 31;
-                            double snt = ((double)st.ue_i[(eu0 + u) * UI_N + UI_SUM_SENT] / (double)win_len) * pkt_bits;
+                            double snt = div_small((double)st.ue_i[(eu0 + u) * UI_N + UI_SUM_SENT], win_len) * pkt_bits;
                             if (isclose0(ta[i])) snt = 1;
                             w[i] = !isclose0(snt) ? ta[i] / snt : 2 * tamax;
                             sw += w[i];
@@ -384,13 +384,13 @@ __global__ void __launch_bounds__(L8_THREADS, L8_TAIL_MINB) k_env_tail_8(const _
     const int fbit[3] = {IRS_F_THR, IRS_F_REL, IRS_F_LAT};
 #pragma unroll
     for (int k = 0; k < 3; ++k) { // common.py:371-373 np.mean over the slice's UEs; undeclared / empty -> -2
-        const double mean = (0. + sum_d[k]) / (double)n;
+        const double mean = div_small(0. + sum_d[k], n);
         const double d = (n > 0 && (fl & IRS_F_REQ) && (fl & fbit[k])) ? mean : -2.0;
         const bool close = fabs(d - (-2.0)) <= 1e-8 + 1e-5 * 2.0; // ib_sched.py:142-145 np.isclose(x, -2)
         act[k] = close ? 0 : 1;
         dsl[k] = close ? 0 : d;
     }
-    const double se_slice = n > 0 ? (0. + sum_se) / (double)n : 0.0;        // ib_sched.py:146-157
+    const double se_slice = n > 0 ? div_small(0. + sum_se, n) : 0.0;        // ib_sched.py:146-157
     const double traffic = (fl & IRS_F_ACTIVE) ? __ldg(&sl->traffic) : 0;    // :125-134
     const double prio_raw = __ldg(&sl->priority);
     const double prio = n != 0 ? prio_raw : 0;                               // :135-141
@@ -463,7 +463,7 @@ __global__ void __launch_bounds__(L8_THREADS, L8_TAIL_MINB) k_env_tail_8(const _
             const bool sel = nneg == 0 ? true : (npneg ? (Aa[j] * Pp[j] < 0) : (Aa[j] < 0));
             if (sel) { res += Aa[j]; ++m; }
         }
-        r0 = (0. + res) / (double)m - ((nneg != 0 && npneg) ? 1 : 0); // common.py:410-426
+        r0 = div_small(0. + res, m) - ((nneg != 0 && npneg) ? 1 : 0); // common.py:410-426
     }
     if (live && g == 0) st.out_reward[(size_t)e * 6] = r0;
     if (live && mine) st.out_reward[(size_t)e * 6 + 1 + s] = r_intra;

@@ -98,10 +98,10 @@ __global__ void __launch_bounds__(SERIAL_THREADS) k_action_t(const __grid_consta
             for (int u = 0; u < U; ++u) {
                 if (ue_slice_of(us, u) != s) continue;
                 so += st.ue_d[(eu0 + u) * UD_N + UD_OCC];
-                ss += (double)st.ue_i[(eu0 + u) * UI_N + UI_SUM_SENT] / (double)win_len;
+                ss += div_small((double)st.ue_i[(eu0 + u) * UI_N + UI_SUM_SENT], win_len);
                 ++n;
             }
-            double om = (0. + so) / (double)n, sm = (0. + ss) / (double)n; // n == 0: 0/0 = nan like np.mean([])
+            double om = div_small(0. + so, n), sm = div_small(0. + ss, n); // n == 0: 0/0 = nan like np.mean([])
             const double bsz = __ldg(&sc->sl[s].buffer_size), msg = __ldg(&sc->sl[s].message_size);
             occ_mbps[s] = active[s] ? DIVC((om * bsz) * msg, 1e6) : 0.0;
             sent_mbps[s] = active[s] ? DIVC(sm * msg, 1e6) : 0.0;
@@ -201,7 +201,7 @@ __global__ void __launch_bounds__(SERIAL_THREADS) k_action_t(const __grid_consta
                     ta[i] = 0;
                     if (i < n) {
                         const double sebar = st.ue_d[(eu0 + g.u[i]) * UD_N + UD_SEBAR];
-                        const double ta_a = (sebar * DIVC((double)rbs_s * cfg.bandwidth, R)) / (double)n;
+                        const double ta_a = div_small(sebar * DIVC((double)rbs_s * cfg.bandwidth, R), n);
                         const double ta_b = (occ[i] * max_pkts) * pkt_bits;
                         ta[i] = ta_a < ta_b ? ta_a : ta_b;
                         tamax = (i == 0 || ta[i] > tamax) ? ta[i] : tamax;
@@ -216,7 +216,7 @@ __global__ void __launch_bounds__(SERIAL_THREADS) k_action_t(const __grid_consta
                     for (int i = 0; i < NS; ++i) {
                         w[i] = 0;
                         if (i < n) {
-                            double snt = ((double)st.ue_i[(eu0 + g.u[i]) * UI_N + UI_SUM_SENT] / (double)win_len) * pkt_bits;
+                            double snt = div_small((double)st.ue_i[(eu0 + g.u[i]) * UI_N + UI_SUM_SENT], win_len) * pkt_bits;
                             if (isclose0(ta[i])) snt = 1;
                             w[i] = !isclose0(snt) ? ta[i] / snt : 2 * tamax;
                             sw += w[i];
@@ -352,13 +352,13 @@ __global__ void __launch_bounds__(SERIAL_THREADS, TAIL_T_MINB) k_env_tail_t(cons
         const int fl = flags[s], n = n_s[s];
 #pragma unroll
         for (int k = 0; k < 3; ++k) { // common.py:371-373 np.mean over the slice's UEs; undeclared / empty -> -2
-            const double mean = (0. + sum_d[s][k]) / (double)n;
+            const double mean = div_small(0. + sum_d[s][k], n);
             const double d = (n > 0 && (fl & IRS_F_REQ) && (fl & fbit[k])) ? mean : -2.0;
             const bool close = fabs(d - (-2.0)) <= 1e-8 + 1e-5 * 2.0; // ib_sched.py:142-145 np.isclose(x, -2)
             act[s][k] = close ? 0 : 1;
             dsl[s][k] = close ? 0 : d;
         }
-        se_slice[s] = n > 0 ? (0. + sum_se[s]) / (double)n : 0.0; // ib_sched.py:146-157
+        se_slice[s] = n > 0 ? div_small(0. + sum_se[s], n) : 0.0; // ib_sched.py:146-157
         traffic[s] = (fl & IRS_F_ACTIVE) ? __ldg(&sl->traffic) : 0; // :125-134
         prio[s] = n != 0 ? __ldg(&sl->priority) : 0;               // :135-141
         msg[s] = __ldg(&sl->message_size);
@@ -445,7 +445,7 @@ __global__ void __launch_bounds__(SERIAL_THREADS, TAIL_T_MINB) k_env_tail_t(cons
             const bool sel = nneg == 0 ? true : (npneg ? (Aa[s] * Pp[s] < 0) : (Aa[s] < 0));
             if (sel) { res += Aa[s]; ++m; }
         }
-        r0 = (0. + res) / (double)m - ((nneg != 0 && npneg) ? 1 : 0); // common.py:410-426
+        r0 = div_small(0. + res, m) - ((nneg != 0 && npneg) ? 1 : 0); // common.py:410-426
     }
     st.out_reward[(size_t)e * 6] = r0;
 #pragma unroll

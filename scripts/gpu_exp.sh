@@ -1,9 +1,18 @@
 #!/bin/bash
-# one-off experiment: parity of the warp-per-env cores, then the phase stamps of the one-launch step (debug build)
+# one-off: GPU suite, A/B of the table-driven small divisions, and the one-launch / three-launch crossover
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_gpu_fuzz.py -x -q -m gpu -k "one_launch or warp_per_env or not (lane8 or thread_per_env)" > gpurun_out/exp_tests.txt 2>&1
-tail -5 gpurun_out/exp_tests.txt
-IRS_LIB_PATH=$PWD/build_variants/lib_phaseclock.so python scripts/phase_clock.py 1024 > gpurun_out/phase_clock_cold.txt 2>&1
-cat gpurun_out/phase_clock_cold.txt
-python bench.py --workload cfg2 --no-cpu-baseline --no-e2e > gpurun_out/bench_cfg2_exp.json 2> gpurun_out/bench_cfg2_exp.err
-python scripts/show_bench.py gpurun_out/bench_cfg2_exp.json 2>/dev/null || tail -c 600 gpurun_out/bench_cfg2_exp.json
+timeout 2400 python -m pytest tests -x -q -m gpu > gpurun_out/exp_tests.txt 2>&1; tail -3 gpurun_out/exp_tests.txt
+for w in sweep mix; do
+  a=""; [ $w != sweep ] && a="--workload $w"
+  for v in new base; do
+    l=""; [ $v = base ] && l="$PWD/build_variants/lib_base.so"
+    IRS_LIB_PATH=$l python bench.py $a --no-cpu-baseline --no-e2e > gpurun_out/bench_${w}_$v.json 2> gpurun_out/bench_${w}_$v.err
+    python scripts/show_bench.py gpurun_out/bench_${w}_$v.json
+  done
+done
+for E in 1024 2368 4096 8192 16384; do
+  for m in 1000000 0; do
+    IRS_FUSED_MAX_ENVS=$m python bench.py --workload mix --envs $E --no-cpu-baseline --no-e2e > gpurun_out/bench_x_${E}_$m.json 2> gpurun_out/bench_x_${E}_$m.err
+    echo "E=$E fused_max=$m"; python scripts/show_bench.py gpurun_out/bench_x_${E}_$m.json
+  done
+done

@@ -10,7 +10,7 @@ import pytest
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "..", "intent_radio_sched_multi_slice_b200", "csrc")
-DIVISORS = ["1", "2", "3", "4", "5", "40", "100", "120", "135", "1e6"]
+DIVISORS = ["1", "2", "3", "4", "5", "6", "7", "8", "9", "10", "40", "100", "120", "135", "1e6"]
 
 
 @pytest.fixture(scope="module")
@@ -38,7 +38,7 @@ def test_numerator_set_is_adversarial(checker):
 
 
 def test_every_kernel_divisor_is_covered():
-    """every constant the kernels pass to DIVC (and div_small's 1..5) is in DIVISORS"""
+    """every constant the kernels pass to DIVC (and div_small's 1..10) is in DIVISORS"""
     consts = set()
     for f in os.listdir(CSRC):
         if f.endswith(".cuh"):
