@@ -229,29 +229,31 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
             acc_t = acc_t + __shfl_down_sync(FULL, acc_t, 2);
             acc_se = acc_se + __shfl_down_sync(FULL, acc_se, 4);
             acc_t = acc_t + __shfl_down_sync(FULL, acc_t, 4);
-            if (l16 == 8) { // second half: the 7-element tail is added serially after the tree
-                const double* tp = ws + 14 * uj;
-#pragma unroll
-                for (int k = 0; k < 7; ++k) {
-                    if (SPLIT_A) {
-                        const double xt = tp[k];
-                        acc_se += xt;
-                        acc_t += sched_at(sb, rs, rc, 128 + k) ? A.bw_rb * xt : 0.0;
-                    } else {
-                        const double2 xt = reinterpret_cast<const double2*>(tp)[k];
-                        acc_se += xt.x;
-                        acc_t += xt.y;
-                    }
-                }
-            }
-            const double res_se = 0. + (acc_se + __shfl_down_sync(FULL, acc_se, 8)); // valid on lanes 0, 16
-            const double res_t = 0. + (acc_t + __shfl_down_sync(FULL, acc_t, 8));
-            if (l16 == 0 && live) *reinterpret_cast<double2*>(ws + 352 + 4 * uj) = make_double2(res_t, res_se);
+            // the two half-row trees of the UE: (SE, term) of half l16 >> 3 at ws[352 + 4 u + 2 half]
+            if ((l16 & 7) == 0 && live) *reinterpret_cast<double2*>(ws + 352 + 4 * uj + (l16 >> 2)) = make_double2(acc_se, acc_t);
         }
         __syncwarp();
+        // lane = UE again: the 7-element tail is added serially to the second half's tree, then the halves, then the
+        // reduction identity - once for all UEs instead of once per pass on one lane of each side
         if (gen) {
-            const double2 r2 = *reinterpret_cast<const double2*>(ws + 352 + 4 * lane);
-            sum_t = r2.x; sum_se = r2.y;
+            const double2 h0 = *reinterpret_cast<const double2*>(ws + 352 + 4 * lane);
+            double2 h1 = *reinterpret_cast<const double2*>(ws + 352 + 4 * lane + 2);
+            const double* tp = ws + 14 * lane;
+            const uint32_t* sb = (RAWSE && A.sched_bits) ? A.sched_bits + eu * 5 : nullptr;
+#pragma unroll
+            for (int k = 0; k < 7; ++k) {
+                if (SPLIT_A) {
+                    const double xt = tp[k];
+                    h1.x += xt;
+                    h1.y += sched_at(sb, rb_s, rb_c, 128 + k) ? A.bw_rb * xt : 0.0;
+                } else {
+                    const double2 xt = reinterpret_cast<const double2*>(tp)[k];
+                    h1.x += xt.x;
+                    h1.y += xt.y;
+                }
+            }
+            sum_se = 0. + (h0.x + h1.x);
+            sum_t = 0. + (h0.y + h1.y);
         }
     } else if (cfg.channel_mode != 2) {
         // Rows that come from memory (injected frame, SE trace bank) or are constant (fixed_se):

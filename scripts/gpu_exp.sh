@@ -1,6 +1,12 @@
 #!/bin/bash
-# one-off: bulk L2 prefetch of the SE trace rows, prefetch distance 2 / 3 / 4 pairs against the line-wise prefetch (base)
+# one-off: serial tail of the native rows in a lane = UE epilogue: parity, then A/B on sweep / mix / cfg2
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_parity.py -x -q -m gpu > gpurun_out/exp_tests.txt 2>&1; tail -2 gpurun_out/exp_tests.txt
-bash scripts/gpu_variants.sh --workload trace --no-cpu-baseline --no-e2e
-python scripts/show_bench.py gpurun_out/bench_var_*.json
+timeout 1800 python -m pytest tests -x -q -m gpu > gpurun_out/exp_tests.txt 2>&1; tail -2 gpurun_out/exp_tests.txt
+for w in sweep mix cfg2; do
+  a=""; [ $w != sweep ] && a="--workload $w"
+  for v in new base new base; do
+    l=""; [ $v = base ] && l="$PWD/build_variants/lib_base.so"
+    IRS_LIB_PATH=$l python bench.py $a --no-cpu-baseline --no-e2e > gpurun_out/bench_${w}_$v.json 2> gpurun_out/bench_${w}_$v.err
+    python scripts/show_bench.py gpurun_out/bench_${w}_$v.json | cut -c1-200
+  done
+done
