@@ -301,18 +301,17 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
             const int rs = __shfl_sync(FULL, rb_s, uj), rc = __shfl_sync(FULL, rb_c, uj);
             const int l16 = lane & 15, base = ((l16 >> 3) << 6) + (l16 & 7);
             const double* rowp = frame_base ? frame_base + (size_t)uj * R : nullptr;
-            double x[8], xt[7];
+            double x[8];
 #pragma unroll
             for (int k = 0; k < 8; ++k) x[k] = rowp ? __ldg(rowp + base + 8 * k) : 2.0; // channels/fixed_se.py:26
-#pragma unroll
-            for (int k = 0; k < 7; ++k) xt[k] = (l16 == 8 || all_rows) ? (rowp ? __ldg(rowp + 128 + k) : 2.0) : 0.0;
             const uint32_t* sb = (RAWSE && A.sched_bits) ? A.sched_bits + ((size_t)e * U + uj) * 5 : nullptr;
+            // ((BW/R) * sched) * SE, ues.py:108-116; the + 0.0 of an unscheduled RB changes nothing (terms >= 0)
             double acc_se = x[0];
-            double acc_t = sched_at(sb, rs, rc, base) ? A.bw_rb * x[0] : 0.0; // ((BW/R) * sched) * SE, ues.py:108-116
+            double acc_t = sched_at(sb, rs, rc, base) ? A.bw_rb * x[0] : 0.0;
 #pragma unroll
             for (int k = 1; k < 8; ++k) {
                 acc_se += x[k];
-                acc_t += sched_at(sb, rs, rc, base + 8 * k) ? A.bw_rb * x[k] : 0.0;
+                if (sched_at(sb, rs, rc, base + 8 * k)) acc_t += A.bw_rb * x[k];
             }
             acc_se = acc_se + __shfl_down_sync(FULL, acc_se, 1);
             acc_t = acc_t + __shfl_down_sync(FULL, acc_t, 1);
@@ -320,28 +319,31 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
             acc_t = acc_t + __shfl_down_sync(FULL, acc_t, 2);
             acc_se = acc_se + __shfl_down_sync(FULL, acc_se, 4);
             acc_t = acc_t + __shfl_down_sync(FULL, acc_t, 4);
-            if (l16 == 8) { // second half: 7-element tail added serially after the tree
-#pragma unroll
-                for (int k = 0; k < 7; ++k) {
-                    acc_se += xt[k];
-                    acc_t += sched_at(sb, rs, rc, 128 + k) ? A.bw_rb * xt[k] : 0.0;
-                }
-            }
-            const double res_se = 0. + (acc_se + __shfl_down_sync(FULL, acc_se, 8)); // valid on lanes 0, 16
-            const double res_t = 0. + (acc_t + __shfl_down_sync(FULL, acc_t, 8));
-            if (l16 == 0 && live) *reinterpret_cast<double2*>(ws + 64 + 4 * uj) = make_double2(res_t, res_se);
+            // the two half-row trees of the UE: (SE, term) of half l16 >> 3 at ws[64 + 4 u + 2 half]
+            if ((l16 & 7) == 0 && live) *reinterpret_cast<double2*>(ws + 64 + 4 * uj + (l16 >> 2)) = make_double2(acc_se, acc_t);
             if (all_rows && live) {
                 double* se_out = A.raw.se_used + ((size_t)e * U + uj) * R;
 #pragma unroll
                 for (int k = 0; k < 8; ++k) se_out[base + 8 * k] = x[k];
-                if (l16 == 8)
-                    for (int k = 0; k < 7; ++k) se_out[128 + k] = xt[k];
             }
         }
         __syncwarp();
+        // lane = UE: the 7-element tail (RBs 128..134; its sectors were just read by the UE's pass) is added serially to
+        // the second half's tree, then the halves, then the reduction identity
         if (ue_lane && (s_mine >= 0 || all_rows)) {
-            const double2 r2 = *reinterpret_cast<const double2*>(ws + 64 + 4 * lane);
-            sum_t = r2.x; sum_se = r2.y;
+            const double2 h0 = *reinterpret_cast<const double2*>(ws + 64 + 4 * lane);
+            double2 h1 = *reinterpret_cast<const double2*>(ws + 64 + 4 * lane + 2);
+            const double* rowp = frame_base ? frame_base + (size_t)lane * R : nullptr;
+            const uint32_t* sb = (RAWSE && A.sched_bits) ? A.sched_bits + eu * 5 : nullptr;
+#pragma unroll
+            for (int k = 0; k < 7; ++k) {
+                const double xt = rowp ? __ldg(rowp + 128 + k) : 2.0;
+                h1.x += xt;
+                if (sched_at(sb, rb_s, rb_c, 128 + k)) h1.y += A.bw_rb * xt;
+                if (all_rows) A.raw.se_used[eu * R + 128 + k] = xt;
+            }
+            sum_se = 0. + (h0.x + h1.x);
+            sum_t = 0. + (h0.y + h1.y);
         }
     } else {
     uint32_t todo = __ballot_sync(FULL, ue_lane);
