@@ -312,10 +312,12 @@ static int launch_step(irs_env* env, const StepArgs& A, cudaStream_t st, bool pr
     const int E = A.env_end - A.env_begin;
     if (E <= 0) return IRS_OK;
     NvtxRange whole("irs_step");
+    const bool native_src = env->cfg.channel_mode == 2 && env->cfg.traffic_mode == 1, mem_src = env->cfg.channel_mode != 2;
     if (profile) CK(cudaEventRecord(env->ev[0], st));
     if (E <= env->fused_max && env->cfg.surface == 0 && !A.sched_bits && !A.raw.se_used) {
         if (profile) CK(cudaEventRecord(env->ev[1], st));
-        k_env_step<<<E, STEP_WARPS * 32, 0, st>>>(A); // one block per env
+        if (native_src) k_env_step<<<E, STEP_WARPS * 32, 0, st>>>(A); // one block per env
+        else k_env_step_any<<<E, STEP_WARPS * 32, 0, st>>>(A);
         if (profile) { CK(cudaEventRecord(env->ev[2], st)); CK(cudaEventRecord(env->ev[3], st)); }
         CK(cudaGetLastError());
         return IRS_OK;
@@ -334,8 +336,10 @@ static int launch_step(irs_env* env, const StepArgs& A, cudaStream_t st, bool pr
     StepArgs B2 = A; // small batches: 2 or 4 warps per env, so that the launch still puts ~32 warps on every SM
     B2.ue_split_log2 = env->ue_split >= 0 ? env->ue_split : (E <= 1184 ? 2 : (E <= 2368 ? 1 : 0));
     const unsigned env_warps = (unsigned)E << B2.ue_split_log2;
-    if (A.raw.se_used || A.sched_bits) k_ue_env_raw<<<(env_warps + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(B2);
-    else k_ue_env<<<(env_warps + FUSED_WARPS - 1) / FUSED_WARPS, FUSED_WARPS * 32, 0, st>>>(B2);
+    const unsigned ue_blocks = (env_warps + FUSED_WARPS - 1) / FUSED_WARPS;
+    if (A.raw.se_used || A.sched_bits || !(native_src || mem_src)) k_ue_env_raw<<<ue_blocks, FUSED_WARPS * 32, 0, st>>>(B2);
+    else if (native_src) k_ue_env<<<ue_blocks, FUSED_WARPS * 32, 0, st>>>(B2);
+    else k_ue_env_mem<<<ue_blocks, FUSED_WARPS * 32, 0, st>>>(B2);
     nvtxRangePop();
     if (profile) CK(cudaEventRecord(env->ev[2], st));
     NvtxRange tail("obs+reward+rollover");

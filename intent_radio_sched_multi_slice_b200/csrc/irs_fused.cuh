@@ -59,7 +59,10 @@ struct StepXchg { // hand-over between the warps of a k_env_step block
     int sent[32], sum_sent[32], sum_drop[32], dropped[32], inc[32], occ1z[32];
     double mu[32], traffic[32]; // pass A of every UE, by the block's last warp
 };
-template <bool FULL_STEP, bool RAWSE, int NW>
+// SRC = where the frame's SE rows and arrivals come from, fixed at compile time for the hot instantiations (each kernel
+//       then holds one of the three row paths): 1 native generators (channel_mode 2 + traffic_mode 1), 2 rows from
+//       memory or constant (channel_mode 0 / 1 / 3), 0 decided at run time (any combination; the raw-output kernel).
+template <bool FULL_STEP, bool RAWSE, int NW, int SRC>
 __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP][136], const float2* __restrict__ ntab,
                                             StepXchg* xc = nullptr)
 {
@@ -89,7 +92,8 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
     if (ue_lane && win_len == A.win_cap) evict = st.ring[eu * W + p];
     const int tot_prev = ue_lane ? rec_a.x : 0;
     const int frame = step + 1, gid = cfg.env_id_base + e;
-    const bool native = cfg.channel_mode == 2 && cfg.traffic_mode == 1;
+    const bool native = SRC == 1 ? true : (SRC == 2 ? false : (cfg.channel_mode == 2 && cfg.traffic_mode == 1));
+    const bool mem_rows = SRC == 2 ? true : (SRC == 1 ? false : cfg.channel_mode != 2);
     // In the one-launch step the generators' per-UE pass (pass A below) does not wait for the action: the block's last
     // warp runs it for ALL of the env's UEs while warp 0 turns the action into RB runs.
     constexpr bool SPLIT_A = FULL_STEP && NW > 1;
@@ -255,7 +259,7 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
             sum_se = 0. + (h0.x + h1.x);
             sum_t = 0. + (h0.y + h1.y);
         }
-    } else if (cfg.channel_mode != 2) {
+    } else if (mem_rows) {
         // Rows that come from memory (injected frame, SE trace bank) or are constant (fixed_se):
         // the same two-UEs-per-pass register reduction, each lane loading the 8 elements of its
         // accumulator straight from global memory (every 32-byte sector fully used).  Rows of
@@ -508,24 +512,32 @@ __device__ __forceinline__ void ue_env_body(const StepArgs& A, double (*sm)[GRP]
 #ifndef UE_ENV_MINB
 #define UE_ENV_MINB 8 /* 64 registers: 32 warps per SM measured fastest (profiles/r1_notes.md) */
 #endif
+// native generators (the default of the batched env)
 __global__ void __launch_bounds__(FUSED_WARPS * 32, UE_ENV_MINB) k_ue_env(const __grid_constant__ StepArgs A)
 {
     __shared__ __align__(16) double sm[FUSED_WARPS][GRP][136];
     __shared__ __align__(16) float2 ntab[IRS_NORMAL_TAB_N];
     normal_tab_request(ntab);
-    ue_env_body<false, false, FUSED_WARPS>(A, sm, ntab);
+    ue_env_body<false, false, FUSED_WARPS, 1>(A, sm, ntab);
 }
-// same kernel with the optional per-RB SE output (irs_raw_outputs.se_used; tests and trace dumps)
+// rows from memory (SE trace bank, injected frames) or constant: no generator table in shared memory
+__global__ void __launch_bounds__(FUSED_WARPS * 32, UE_ENV_MINB) k_ue_env_mem(const __grid_constant__ StepArgs A)
+{
+    __shared__ __align__(16) double sm[FUSED_WARPS][GRP][136];
+    ue_env_body<false, false, FUSED_WARPS, 2>(A, sm, nullptr);
+}
+// every combination, with the optional per-RB SE output (irs_raw_outputs.se_used; tests and trace dumps) and given
+// scheduling matrices
 __global__ void __launch_bounds__(FUSED_WARPS * 32, UE_ENV_MINB) k_ue_env_raw(const __grid_constant__ StepArgs A)
 {
     __shared__ __align__(16) double sm[FUSED_WARPS][GRP][136];
     __shared__ __align__(16) float2 ntab[IRS_NORMAL_TAB_N];
     normal_tab_request(ntab);
-    ue_env_body<false, true, FUSED_WARPS>(A, sm, ntab);
+    ue_env_body<false, true, FUSED_WARPS, 0>(A, sm, ntab);
 }
 
 // the whole step in one launch, one block of STEP_WARPS warps per env (small batches; IBSched-family surface, no per-RB
-// raw output)
+// raw output): native generators | any source
 #ifndef STEP_WARPS
 #define STEP_WARPS 2
 #endif
@@ -538,5 +550,13 @@ __global__ void __launch_bounds__(STEP_WARPS * 32, ENV_STEP_MINB) k_env_step(con
     __shared__ __align__(16) float2 ntab[IRS_NORMAL_TAB_N];
     __shared__ StepXchg xc;
     normal_tab_request(ntab);
-    ue_env_body<true, false, STEP_WARPS>(A, sm, ntab, &xc);
+    ue_env_body<true, false, STEP_WARPS, 1>(A, sm, ntab, &xc);
+}
+__global__ void __launch_bounds__(STEP_WARPS * 32, ENV_STEP_MINB) k_env_step_any(const __grid_constant__ StepArgs A)
+{
+    __shared__ __align__(16) double sm[STEP_WARPS][GRP][136];
+    __shared__ __align__(16) float2 ntab[IRS_NORMAL_TAB_N];
+    __shared__ StepXchg xc;
+    normal_tab_request(ntab);
+    ue_env_body<true, false, STEP_WARPS, 0>(A, sm, ntab, &xc);
 }

@@ -1,8 +1,8 @@
 #!/bin/bash
-# one-off: serial tail of the memory rows in a lane = UE epilogue: parity, then A/B on trace / sweep
+# one-off: row kernels specialised by SE source at compile time: parity, then A/B
 mkdir -p gpurun_out
 timeout 1800 python -m pytest tests -x -q -m gpu > gpurun_out/exp_tests.txt 2>&1; tail -2 gpurun_out/exp_tests.txt
-for w in trace sweep; do
+for w in sweep mix trace cfg2; do
   a=""; [ $w != sweep ] && a="--workload $w"
   for v in new base new base; do
     l=""; [ $v = base ] && l="$PWD/build_variants/lib_base.so"
