@@ -466,7 +466,7 @@ def run_b200(args):
                     "inst_per_launch": facts["inst_per_launch"], "ncu_issue_active_pct": facts.get("issue_active_pct"),
                     "ncu_source": facts.get("source"), "hbm": hbm}
     else:
-        roofline = dict(hbm, bound="hbm", kernel="k_ue_env")
+        roofline = dict(hbm, bound="hbm", kernel="k_ue_env_mem" if args.workload == "trace" else "k_ue_env")
     roofline.update({"kernel_ms": kms[1], "kernel_ms_all": {"k_action": kms[0], "k_ue_env": kms[1], "k_env_tail": kms[2]},
                      "row_paths": {"no_old_packets": path_frac[0], "window_cleared": path_frac[1], "lane_drain": path_frac[2],
                                    "warp_drain": path_frac[3]},
