@@ -20,10 +20,11 @@ __device__ __forceinline__ void round_int_equal_sum5(const double (&x)[S], int t
     for (int i = 0; i < S; ++i)
         if (x[i] != 0) { res += x[i]; ++cnt; }
     const double sum = 0. + res;
+    const Recip rsum = recip_of(sum); // all x zero: sum = 0 and no quotient is used
     int tot = 0;
 #pragma unroll
     for (int i = 0; i < S; ++i) {
-        out[i] = (x[i] != 0) ? (int)floor(((double)target * x[i]) / sum) : 0;
+        out[i] = (x[i] != 0) ? (int)floor(div_by((double)target * x[i], rsum)) : 0;
         tot += out[i];
     }
     const int adj = target - tot;
@@ -34,7 +35,7 @@ __device__ __forceinline__ void round_int_equal_sum5(const double (&x)[S], int t
 #pragma unroll
         for (int j = 0; j < S; ++j)
             if (x[j] != 0 && (x[j] > x[i] || (x[j] == x[i] && j > i))) ++rank;
-        if (adj > rank) out[i] += (adj - rank - 1) / cnt + 1;
+        if (adj > rank) out[i] += idiv_small(adj - rank - 1, cnt) + 1;
     }
 }
 
@@ -106,7 +107,7 @@ __device__ __forceinline__ void scores_to_rbs5_lanes(const double (&action)[S], 
         if (x[i] != 0 && (x[i] > x_mine || (x[i] == x_mine && i > s))) ++rank;
     }
     const int adj = total - tot;
-    if (x_mine != 0 && adj > rank) out_mine += (adj - rank - 1) / cnt + 1;
+    if (x_mine != 0 && adj > rank) out_mine += idiv_small(adj - rank - 1, cnt) + 1;
 #pragma unroll
     for (int i = 0; i < S; ++i) out[i] = __shfl_sync(FULL, out_mine, i);
 }
@@ -118,7 +119,8 @@ __device__ __forceinline__ int rr_share(uint32_t elmask, int rbs_s)
     if (!((elmask >> lane) & 1u)) return 0;
     const int m = __popc(elmask);
     const int i = __popc(elmask & ((1u << lane) - 1u));
-    return rbs_s / m + (i < rbs_s % m ? 1 : 0);
+    const int q = idiv_small(rbs_s, m);
+    return q + (i < rbs_s - q * m ? 1 : 0);
 }
 
 template <int N>

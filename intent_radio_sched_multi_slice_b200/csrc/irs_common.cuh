@@ -115,6 +115,18 @@ __device__ __forceinline__ double div_small(double x, int n)
     return i >= 1 ? q : x / (double)n;
 }
 
+// Several numerators over ONE run-time divisor (a sum of weights, an intent's threshold): y = 1 / c is the only IEEE
+// division, every quotient then takes the same five-operation sequence.  With y = RN(1 / c) the first correction leaves a
+// faithful quotient and the second rounds it correctly (Markstein's theorem); tests/divc_check.c "rand:N" checks random
+// divisors, among them the significands next to 1 and next to 2, with adversarial numerators.  c = 0 gives nan where the
+// division gives inf: only used where a zero divisor's quotients are discarded.
+struct Recip { double c, y; };
+__device__ __forceinline__ Recip recip_of(double c) { Recip r; r.c = c; r.y = 1.0 / c; return r; }
+__device__ __forceinline__ double div_by(double x, const Recip& r) { return div_const(x, r.c, r.y); }
+// x / m for 0 <= x < 13,000 and a count m = 1..7 (UEs of a slice, non-zero shares): multiply by ceil(2^16 / m)
+__constant__ unsigned c_imul[8] = {0u, 65536u, 32768u, 21846u, 16384u, 13108u, 10923u, 9363u};
+__device__ __forceinline__ int idiv_small(int x, int m) { return (int)(((unsigned)x * c_imul[m & 7]) >> 16); }
+
 #ifdef IRS_PHASE_CLOCK /* debug builds only (scripts/phase_clock.py): SM clock at the phase boundaries of k_env_step */
 __device__ long long g_phase_clock[4096][4][8]; // [block][warp 0 | warp 1 | action core | tail core][stamp]
 #define PHASE_STAMP(row, i) do { if (blockDim.x == 64 && (threadIdx.x & 31) == 0 && blockIdx.x < 4096) { long long t_; \
@@ -211,7 +223,7 @@ __device__ __forceinline__ int group_round_int_equal_sum(double x, const GroupId
 #pragma unroll
     for (int k = 0; k < NS; ++k)
         if (use[k] && (v[k] > x || (v[k] == x && G.src[k] > lane))) ++rank;
-    if (nz && adj > rank) p += (adj - rank - 1) / cnt + 1;
+    if (nz && adj > rank) p += idiv_small(adj - rank - 1, cnt) + 1;
     return p;
 }
 

@@ -17,10 +17,10 @@
 
 #define L8_THREADS 128 /* 16 envs per block */
 #ifndef L8_TAIL_MINB
-#define L8_TAIL_MINB 6 /* 80 registers: measured fastest (4: 0.128 ms, 6: 0.111, 8: 0.120 at 65,536 envs) */
+#define L8_TAIL_MINB 7 /* 72 registers: measured fastest (6: 0.100 ms, 7: 0.097, 8: 0.100 at 65,536 envs) */
 #endif
 #ifndef L8_ACTION_MINB
-#define L8_ACTION_MINB 8
+#define L8_ACTION_MINB 10 /* 48 registers (8: 0.062 ms, 10: 0.058, 12: 0.062) */
 #endif
 
 // UE indices of slice s (ascending, <= 5), 5 bits each; n = how many.  The 25 slice ids are compared four at a time
@@ -204,7 +204,7 @@ __global__ void __launch_bounds__(L8_THREADS, L8_ACTION_MINB) k_action_8(const _
             if (xs[j] != 0 && (xs[j] > x_mine || (xs[j] == x_mine && j > s))) ++rank;
         }
         const int adj = target - tot;
-        if (x_mine != 0 && adj > rank) out_mine += (adj - rank - 1) / cnt + 1;
+        if (x_mine != 0 && adj > rank) out_mine += idiv_small(adj - rank - 1, cnt) + 1;
 #pragma unroll
         for (int j = 0; j < S; ++j) rbs_per_slice[j] = __shfl_sync(FULL, out_mine, j, 8);
     }
@@ -270,15 +270,17 @@ __global__ void __launch_bounds__(L8_THREADS, L8_ACTION_MINB) k_action_8(const _
                     }
                     sw = 0. + sw;
                     ok = sw != 0;
+                    const Recip rsw = recip_of(sw); // one division for the slice's shares; sw = 0: shares not used
 #pragma unroll
                     for (int i = 0; i < NS; ++i)
-                        if (i < n) x[i] = ((double)rbs_s * w[i]) / sw;
+                        if (i < n) x[i] = div_by((double)rbs_s * w[i], rsw);
                 } else { // max throughput - common.py:639-701
                     stt = 0. + stt;
                     ok = stt != 0;
+                    const Recip rst = recip_of(stt);
 #pragma unroll
                     for (int i = 0; i < NS; ++i)
-                        if (i < n) x[i] = ((double)rbs_s * ta[i]) / stt;
+                        if (i < n) x[i] = div_by((double)rbs_s * ta[i], rst);
                 }
                 if (ok) {
                     round_int_equal_sum5(x, rbs_s, cnt);
@@ -358,6 +360,7 @@ __global__ void __launch_bounds__(L8_THREADS, L8_TAIL_MINB) k_env_tail_8(const _
     int rbs_alloc = 0;
     double* pi = st.out_obsi + ((size_t)e * S + s) * IRS_OBSI;
     const double rel_t = (fl & IRS_F_REL) ? rel_target(sl) : 0.0;
+    const DriftRecips dr = drift_recips(sl, (fl & IRS_F_REQ) ? fl : 0, rel_t); // the slice's divisors, once for its UEs
 #pragma unroll
     for (int j = 0; j < NS; ++j) {
         if (j >= n) continue;
@@ -370,7 +373,7 @@ __global__ void __launch_bounds__(L8_THREADS, L8_TAIL_MINB) k_env_tail_8(const _
         f.occ = d0.x; f.lat = d0.y; f.sebar = sebar; f.sent = lo.w; f.sum_sent = lo.y; f.sum_drop = lo.z;
         f.rb_count = st.rb[eu].y; f.occ1z = occ1z != 0;
         double drift[3] = {0, 0, 0};
-        if (fl & IRS_F_REQ) intent_drift_ue(sl, fl, f, win_len, A.win_mul, drift, &rel_t);
+        if (fl & IRS_F_REQ) intent_drift_ue(sl, fl, f, win_len, A.win_mul, drift, &rel_t, &dr);
         sum_d[0] += drift[0]; sum_d[1] += drift[1]; sum_d[2] += drift[2];
         sum_se += sebar;
         rbs_alloc += f.rb_count;

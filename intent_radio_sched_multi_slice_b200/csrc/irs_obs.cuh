@@ -37,8 +37,23 @@ struct SliceView { // valid on lanes 0..4 (slice = lane)
 // reliability target t = (100 - v) / 100 of a slice (common.py:188-233): a per-slice constant that a caller looping over
 // UEs computes once per slice
 __device__ __forceinline__ double rel_target(const irs_slice* sl) { return DIVC(100 - __ldg(&sl->rel_value), 100); }
+// The divisors that are constants of a slice - v r | v (throughput), t r (reliability met), v r (latency met) - as
+// reciprocals: a caller that walks several UEs of ONE slice (the eight-lanes-per-env tail) divides once per divisor and
+// takes the exact sequence of div_by per UE.  The violated branches of reliability and latency (rare) keep the division.
+struct DriftRecips { double thr_ok, thr_bad, rel_ok, lat_ok; }; // RN(1 / divisor); the divisor itself is recomputed per UE (one multiply)
+__device__ __forceinline__ DriftRecips drift_recips(const irs_slice* sl, int flags, double rel_t)
+{
+    const double r = 0.2;
+    DriftRecips d;
+    d.thr_ok = d.thr_bad = d.rel_ok = d.lat_ok = 1.0;
+    if (flags & IRS_F_THR) { const double v = __ldg(&sl->thr_value); d.thr_ok = 1.0 / (v * r); d.thr_bad = 1.0 / v; }
+    if (flags & IRS_F_REL) d.rel_ok = 1.0 / (rel_t * r);
+    if (flags & IRS_F_LAT) d.lat_ok = 1.0 / (__ldg(&sl->lat_value) * r);
+    return d;
+}
 __device__ __forceinline__ void intent_drift_ue(const irs_slice* sl, int flags, const UeFrame& f, int win_len, int mul,
-                                                double (&drift)[3], const double* rel_t = nullptr)
+                                                double (&drift)[3], const double* rel_t = nullptr,
+                                                const DriftRecips* dr = nullptr)
 {
     const double r = 0.2;
     drift[0] = drift[1] = drift[2] = 0;
@@ -49,7 +64,9 @@ __device__ __forceinline__ void intent_drift_ue(const irs_slice* sl, int flags, 
         if (win_len * mul > 1) zero = zero || (mul == 2 ? isclose0(f.occ) : f.occ1z);          // :108-116
         if (zero) m = v * (1.1 + r);                                                        // :117-119
         const bool ok = m >= v;
-        const double q = (ok ? m - v : v - m) / (ok ? v * r : v); // :154-162 (m - v) / (v r) | :172-181 (v - m) / v
+        const double num = ok ? m - v : v - m; // :154-162 (m - v) / (v r) | :172-181 (v - m) / v
+        const double den = ok ? v * r : v;
+        const double q = dr ? div_const(num, den, ok ? dr->thr_ok : dr->thr_bad) : num / den;
         drift[0] = ok ? (m > v * (1 + r) ? 1.0 : 0.0 + q) : 0.0 - q; // :164-168 capped at 1 (0 +- q: the reference's own signed zeros)
     }
     if (flags & IRS_F_REL) {
@@ -58,16 +75,22 @@ __device__ __forceinline__ void intent_drift_ue(const irs_slice* sl, int flags, 
         const double m = den != 0 ? (double)(f.sum_drop * mul) / den : 0.0;                                      // :48-53
         const double t = rel_t ? *rel_t : rel_target(sl);
         const bool ok = 100 * (1 - m) >= v;                        // :124-126
-        double den2 = t * r;
-        if (!ok) den2 = DIVC(v, 100);                                   // violated (rare): the other denominator
-        const double q = (ok ? t - m : m - t) / den2; // :188-220 (t - m) / (t r) | :223-233 (m - t) / (v / 100)
+        double q; // :188-220 (t - m) / (t r) | :223-233 (m - t) / (v / 100)
+        if (dr && ok) q = div_const(t - m, t * r, dr->rel_ok);
+        else {
+            double den2 = t * r;
+            if (!ok) den2 = DIVC(v, 100); // violated (rare): the other denominator
+            q = (ok ? t - m : m - t) / den2;
+        }
         drift[1] = ok ? (m < t * (1 - r) ? 1.0 : 0.0 + q) : 0.0 - q;
     }
     if (flags & IRS_F_LAT) {
         const double v = __ldg(&sl->lat_value);
         const double m = f.lat;
         const bool ok = m <= v;
-        const double q = (ok ? v - m : m - v) / (ok ? v * r : __ldg(&sl->buffer_latency) - v); // :290-319 | :322-335
+        double q; // :290-319 (v - m) / (v r) | :322-335 (m - v) / (buffer_latency - v)
+        if (dr && ok) q = div_const(v - m, v * r, dr->lat_ok);
+        else q = (ok ? v - m : m - v) / (ok ? v * r : __ldg(&sl->buffer_latency) - v);
         drift[2] = ok ? (m < v * (1 - r) ? 1.0 : 0.0 + q) : 0.0 - q;
     }
 }

@@ -52,7 +52,11 @@ __device__ __forceinline__ int ue_slice_of(const uint32_t (&w)[8], int u)
 }
 
 // agents/common.py:508-555 share of the i-th eligible UE
-__device__ __forceinline__ int rr_share_i(int rbs_s, int m, int i) { return rbs_s / m + (i < rbs_s % m ? 1 : 0); }
+__device__ __forceinline__ int rr_share_i(int rbs_s, int m, int i)
+{
+    const int q = idiv_small(rbs_s, m);
+    return q + (i < rbs_s - q * m ? 1 : 0);
+}
 
 __global__ void __launch_bounds__(SERIAL_THREADS) k_action_t(const __grid_constant__ StepArgs A)
 {
@@ -224,15 +228,17 @@ __global__ void __launch_bounds__(SERIAL_THREADS) k_action_t(const __grid_consta
                     }
                     sw = 0. + sw;
                     ok = sw != 0;
+                    const Recip rsw = recip_of(sw);
 #pragma unroll
                     for (int i = 0; i < NS; ++i)
-                        if (i < n) x[i] = ((double)rbs_s * w[i]) / sw;
+                        if (i < n) x[i] = div_by((double)rbs_s * w[i], rsw);
                 } else { // max throughput - common.py:639-701
                     stt = 0. + stt;
                     ok = stt != 0;
+                    const Recip rst = recip_of(stt);
 #pragma unroll
                     for (int i = 0; i < NS; ++i)
-                        if (i < n) x[i] = ((double)rbs_s * ta[i]) / stt;
+                        if (i < n) x[i] = div_by((double)rbs_s * ta[i], rst);
                 }
                 if (ok) {
                     round_int_equal_sum5(x, rbs_s, cnt);

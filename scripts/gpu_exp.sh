@@ -1,12 +1,7 @@
 #!/bin/bash
-# one-off: row kernels specialised by SE source at compile time: parity, then A/B
-mkdir -p gpurun_out
-timeout 1800 python -m pytest tests -x -q -m gpu > gpurun_out/exp_tests.txt 2>&1; tail -2 gpurun_out/exp_tests.txt
-for w in sweep mix trace cfg2; do
-  a=""; [ $w != sweep ] && a="--workload $w"
-  for v in new base new base; do
-    l=""; [ $v = base ] && l="$PWD/build_variants/lib_base.so"
-    IRS_LIB_PATH=$l python bench.py $a --no-cpu-baseline --no-e2e > gpurun_out/bench_${w}_$v.json 2> gpurun_out/bench_${w}_$v.err
-    python scripts/show_bench.py gpurun_out/bench_${w}_$v.json | cut -c1-200
-  done
-done
+# one-off: final pass - bench part of the round plus the lane8 ncu capture
+bash scripts/gpu_round.sh bench > /dev/null 2>&1
+ncu --set full --clock-control none --import-source on -k regex:"k_action_8|k_env_tail_8" -s 1030 -c 2 -f -o gpurun_out/k_per_env_mix \
+    python bench.py --workload mix --fill 512 --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu_full_perenv.log 2>&1
+tail -3 gpurun_out/pytest_gpu.log; tail -2 gpurun_out/smoke.log
+python scripts/show_bench.py gpurun_out/bench.json gpurun_out/bench_mix.json gpurun_out/bench_trace.json gpurun_out/bench_cfg2.json gpurun_out/bench_d401.json gpurun_out/bench_d4096.json | cut -c1-200

@@ -52,6 +52,40 @@ int main(int argc, char** argv)
     s_weak = getenv("DIVC_WEAK") != NULL;
     long bad_total = 0;
     for (int a = 2; a < argc; ++a) {
+        if (strncmp(argv[a], "rand:", 5) == 0) {
+            /* run-time divisors (a sum of weights, a mean sent rate, an intent's threshold): y = 1 / c is one IEEE
+             * division, every further numerator over the same c takes the sequence.  Random divisors over 70 binades,
+             * among them the significands next to 1 and next to 2 (all ones), each with adversarial numerators. */
+            const long nd = atol(argv[a] + 5);
+            long bad = 0, tested = 0;
+            for (long d = 0; d < nd; ++d) {
+                uint64_t mant = next_u64() >> 12;
+                const int kind = (int)(next_u64() % 8);
+                if (kind == 0) mant = 0xFFFFFFFFFFFFFull - (next_u64() % 4);       /* 1.11...1x */
+                else if (kind == 1) mant = next_u64() % 4;                           /* 1.00...0x */
+                else if (kind == 2) mant &= ~((1ull << (int)(next_u64() % 52)) - 1); /* short significands */
+                const int ex = (int)(next_u64() % 70) - 30;
+                double c = ldexp(1.0 + (double)mant * 0x1p-52, ex);
+                if (next_u64() & 1) c = (double)(int64_t)(1 + next_u64() % 100000); /* integers: counts, Mbit sizes */
+                const double y = 1.0 / c;
+                for (long i = 0; i < n; ++i) {
+                    const int e2 = (int)(next_u64() % 60) - 30;
+                    const double m = ldexp(1.0 + (double)(next_u64() >> 11) * 0x1p-53, e2);
+                    uint64_t b = to_bits(m * c);
+                    for (int k = -2; k <= 2; ++k) { bad += check(from_bits(b + (uint64_t)(int64_t)k), c, y); ++tested; }
+                    const long double mid = (long double)m + (long double)ldexp(0x1p-53, e2);
+                    b = to_bits((double)(mid * (long double)c));
+                    for (int k = -2; k <= 2; ++k) { bad += check(from_bits(b + (uint64_t)(int64_t)k), c, y); ++tested; }
+                    bad += check(ldexp(1.0 + (double)(next_u64() >> 11) * 0x1p-53, e2), c, y); ++tested;
+                    bad += check((double)(int64_t)(next_u64() % 1000000), c, y); ++tested;
+                    bad += check(-m, c, y); ++tested;
+                }
+                bad += check(0.0, c, y); ++tested;
+            }
+            printf("random divisors (%ld): %ld mismatches in %ld numerators\n", nd, bad, tested);
+            bad_total += bad;
+            continue;
+        }
         const double c = atof(argv[a]), y = 1.0 / c;
         long bad = 0, tested = 0;
         for (long i = 0; i < n; ++i) {

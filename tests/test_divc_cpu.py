@@ -28,6 +28,23 @@ def test_sequence_matches_division(checker):
     assert out.stdout.count(" 0 mismatches") == len(DIVISORS)
 
 
+def test_sequence_matches_division_for_runtime_divisors(checker):
+    """Recip / div_by and the per-slice drift reciprocals: one IEEE division 1 / c, then the sequence per numerator"""
+    out = subprocess.run([checker, "40", "rand:60000"], capture_output=True, text=True)
+    assert out.returncode == 0, out.stdout
+    assert " 0 mismatches" in out.stdout
+
+
+def test_small_integer_division_by_multiplication():
+    """idiv_small (irs_common.cuh): (x * ceil(2^16 / m)) >> 16 == x // m for 0 <= x < 13,000 and m = 1..7"""
+    import numpy as np
+    c = np.array([0, 65536, 32768, 21846, 16384, 13108, 10923, 9363], np.uint64)
+    x = np.arange(13000, dtype=np.uint64)
+    for m in range(1, 8):
+        assert c[m] == -(-65536 // m)
+        assert np.array_equal((x * c[m]) >> np.uint64(16), x // np.uint64(m)), m
+
+
 def test_numerator_set_is_adversarial(checker):
     """the bare product x * RN(1/c) must fail on the same numerators (otherwise the set proves nothing)"""
     out = subprocess.run([checker, "50000", "3", "5", "135", "1e6"], capture_output=True, text=True,
