@@ -1,12 +1,16 @@
 // irs_fused.cuh - k_ue_env: the per-UE middle of CommunicationEnv.step (channel, traffic, throughput,
 // buffers, per-UE window push; comm_env.py:302-326, ues.py:149-243) of one env in ONE warp, between the
-// action and the tail kernels; and k_env_step: the whole step of a small batch in one launch.
+// action and the tail kernels; and k_env_step: the whole step of a small batch in one launch.  One body
+// (ue_env_body), instantiated per source of the SE rows: k_ue_env / k_env_step native generators, k_ue_env_mem rows
+// from memory or constant, k_ue_env_raw / k_env_step_any chosen at run time.
 //
 // Lane u = UE u for everything that is per-UE scalar work (closed-form buffer arithmetic, ring-row
 // update, window push, and - native generators - the per-episode mean, the serial tail of the SE row and
 // the Poisson arrival).  The warp-wide stage is the 128 leading SE values of every associated UE: pair
 // passes (lanes 0..15 one UE, lanes 16..31 another; a lane draws one Philox quad = eight table normals =
-// the 8 elements of one accumulator of NumPy's pairwise sum, and adds them up in registers).
+// the 8 elements of one accumulator of NumPy's pairwise sum, and adds them up in registers; the 8-lane tree
+// of each row half leaves its sums in shared memory), then a lane = UE epilogue that adds the 7-element
+// serial tail to the second half, the halves, and the reduction identity.
 // Unassociated UEs are skipped entirely.  Buffer rows are rings (irs_ue.cuh): a UE lane loads the expiring
 // slot and its 4 oldest slots in the prologue, before the generators run, and resolves the step's drain on
 // them after the closed form; only a drain that reaches further, or a window of more than 4 slots that
