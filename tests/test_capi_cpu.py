@@ -93,3 +93,19 @@ def test_scenario_bank_compiles_the_reference_scenarios(bank):
     assert ((arr["ue_slice"][:, :25] >= 0).sum(axis=1) == arr["sl"]["n_ues"].sum(axis=1)).all()
     cdf = bank.poisson_cdf()
     assert cdf.shape[1] == 512 and np.all(np.diff(cdf, axis=1) >= 0) and np.allclose(cdf[:, -1], 1.0)
+
+
+def test_noalloc_entry_point_rejects_bad_sizes_before_touching_the_device():
+    """irs_check_errors_noalloc validates its arguments first (no CUDA call is made for a rejected request): null
+    arrays, num_envs < 1 and num_envs beyond the static scratch's IRS_NOALLOC_MAX_ENVS, with a message in errbuf."""
+    lib = capi.load()
+    hdr = open(os.path.join(ROOT, "include", "irs_b200.h")).read()
+    assert int(re.search(r"#define IRS_NOALLOC_MAX_ENVS (\d+)", hdr).group(1)) == capi.IRS_NOALLOC_MAX_ENVS
+    msg = C.create_string_buffer(256)
+    fake = C.c_void_p(256)  # never dereferenced: every call below is rejected before a launch
+    assert lib.irs_check_errors_noalloc(None, 16, fake, None, msg, 256) == capi.IRS_ERR_ARG
+    assert lib.irs_check_errors_noalloc(fake, 16, None, None, msg, 256) == capi.IRS_ERR_ARG
+    assert lib.irs_check_errors_noalloc(fake, 0, fake, None, msg, 256) == capi.IRS_ERR_ARG
+    assert lib.irs_check_errors_noalloc(fake, capi.IRS_NOALLOC_MAX_ENVS + 1, fake, None, msg, 256) == capi.IRS_ERR_ARG
+    assert b"IRS_NOALLOC_MAX_ENVS" in msg.value and str(capi.IRS_NOALLOC_MAX_ENVS + 1).encode() in msg.value
+    assert lib.irs_check_errors_noalloc(fake, capi.IRS_NOALLOC_MAX_ENVS + 1, fake, None, None, 0) == capi.IRS_ERR_ARG
